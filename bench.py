@@ -1,0 +1,316 @@
+#!/usr/bin/env python
+"""Benchmark of the commit hot path (BASELINE.json configs[1]): coset LDE + Poseidon2 Merkle commitment of a
+synthetic 2^24-row x 256-column BabyBear trace at log_blowup 1, one such trace ("segment") per GPU.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b2stark|reference]
+                    [--log-height 24] [--width 256] [--log-blowup 1]
+
+Prints ONE JSON line (rank 0). `value` = algorithmic LDE+commit bytes per second over all GPUs, inputs
+resident in HBM; `e2e` = the same through the C ABI from pinned host memory (H2D inside the timed region).
+`--impl reference` times the CPU oracle (the reference's own CPU prover cannot be built here: no Rust
+toolchain, dependencies not vendored -- DESIGN.md) on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "lde_commit_throughput"
+UNIT = "GB/s"
+
+
+def algorithmic_bytes(log_h, width, b):
+    """A_commit = (1 + 2^b) N W 4 + 2^(b+1) N 32   (SURVEY.md 8d / BASELINE.md 3)."""
+    n = 1 << log_h
+    return (1 + (1 << b)) * n * width * 4 + (2 << b) * n * 32
+
+
+def permutations(log_h, width, b):
+    rows = (1 << log_h) << b
+    return rows * ((width + 7) // 8) + rows - 1
+
+
+def workload_name(log_h, width, b):
+    return f"synthetic standalone commit: 2^{log_h}-row x {width}-col BabyBear trace, coset LDE + Poseidon2 Merkle, log_blowup {b}"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nme, val in zip(names, f[4:8]):
+                if val.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_oracle_sample(log_h, width, b, threads, repeats=1):
+    """Time the CPU oracle's commit on a bounded sample (same column count, fewer rows)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_binding
+    orc = oracle_binding.load()
+    m = orc.fill_synthetic(1 << log_h, width, 0xB200000000000001)
+    best = None
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        orc.commit([m], b, threads=threads)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return best
+
+
+def run_reference(args):
+    """--impl reference: the CPU oracle on the host cores (rank 0 only)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    s_log_h = args.cpu_sample_log_height
+    a_bytes = algorithmic_bytes(s_log_h, args.width, args.log_blowup)
+    for _ in range(args.warmup if args.warmup < 2 else 1):
+        cpu_oracle_sample(s_log_h, args.width, args.log_blowup, threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_oracle_sample(s_log_h, args.width, args.log_blowup, threads)
+    dt = (time.perf_counter() - t0) / args.steps
+    val = a_bytes / dt / 1e9
+    sample = f"2^{s_log_h} x {args.width} rows of the same synthetic trace per step (full workload is 2^{args.log_height})"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": {"workload": workload_name(args.log_height, args.width, args.log_blowup), "sample": sample},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b2stark", choices=["b2stark", "reference"])
+    ap.add_argument("--log-height", type=int, default=24)
+    ap.add_argument("--width", type=int, default=256)
+    ap.add_argument("--log-blowup", type=int, default=1)
+    ap.add_argument("--cpu-sample-log-height", type=int, default=16)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from openvm_b200 import B2Engine, FriParameters
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    log_h, width, b = args.log_height, args.width, args.log_blowup
+    H = 1 << log_h
+    eng = B2Engine.new(FriParameters.standard_with_100_bits_conjectured_security(b), local_rank)
+    dev = eng.device()
+    stream = torch.cuda.ExternalStream(eng.stream, device=local_rank)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # one independent trace ("segment") per GPU: weak scaling, no data-path collective
+    trace = dev.alloc_matrix(H, width)
+    dev.fill_synthetic(trace, 0xB200000000000001 + rank)
+    eng.synchronize()
+
+    def step():
+        root, pcs = dev.commit([trace])
+        pcs.free()
+        return root
+
+    for _ in range(args.warmup):
+        step()
+    eng.reset_metrics()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(args.steps):
+        root = step()
+    ev1.record(stream)
+    barrier()
+    clocks = sampler.stop()
+    ms_total = ev0.elapsed_time(ev1)
+    met = eng.metrics()
+    if world > 1:
+        t = torch.tensor([ms_total], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_step = ms_total / args.steps
+    a_bytes = algorithmic_bytes(log_h, width, b)
+    value = world * a_bytes / (ms_step * 1e-3) / 1e9
+
+    # ---- end to end through the C ABI from pinned host memory
+    e2e = None
+    if not args.no_e2e:
+        nbytes = H * width * 4
+        try:
+            host = torch.empty(H * width, dtype=torch.int32, pin_memory=True)
+        except RuntimeError:
+            host = torch.empty(H * width, dtype=torch.int32)
+        # host copy of the trace in the reference's in-memory form (column-major DeviceMatrix, Montgomery words)
+        dev.download_raw(trace, host.data_ptr(), layout="col", repr="monty")
+
+        def e2e_step():
+            m = dev.upload_raw(host.data_ptr(), H, width, layout="col", repr="monty")
+            r, pcs = dev.commit([m])  # root comes back to the host inside commit (32 B D2H)
+            pcs.free()
+            m.free()
+            return r
+
+        r0 = e2e_step()
+        assert list(r0) == list(root), "e2e root differs from device-resident root"
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(args.steps):
+            e2e_step()
+        e1.record(stream)
+        barrier()
+        ems = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ems], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ems = float(t.item())
+        e2e = {"value": world * a_bytes / (ems / args.steps * 1e-3) / 1e9, "unit": UNIT,
+               "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": 32, "ms_per_step": ems / args.steps,
+               "pinned": bool(host.is_pinned())}
+        del host
+
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        steps = args.steps
+        rows = H << b
+        leaf_ms = met["leaf_hash_ms"] / max(1, met["leaf_hash_launches"])
+        leaf_bytes = rows * width * 4 + rows * 32
+        lde_bytes = (1 + (1 << b)) * H * width * 4
+        lde_ms_step = met["lde_ms"] / steps
+        perms = permutations(log_h, width, b)
+        roofline = {
+            "kernel": "row_hash_kernel (Poseidon2 leaf sponge; integer-pipe bound, reported against HBM as the contract asks)",
+            "bound": "hbm", "achieved": leaf_bytes / (leaf_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+            "frac": leaf_bytes / (leaf_ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+            "ms_per_launch": leaf_ms, "share_of_step": met["leaf_hash_ms"] / steps / ms_step,
+        }
+        roofline_lde = {
+            "kernel": "ntt_pass_kernel x passes (iNTT + coset NTT)", "bound": "hbm",
+            "achieved": lde_bytes / (lde_ms_step * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+            "frac": lde_bytes / (lde_ms_step * 1e-3) / 1e9 / peak, "ms_per_step": lde_ms_step,
+            "launches_per_step": met["lde_launches"] / steps, "share_of_step": lde_ms_step / ms_step,
+        }
+        # integer-pipe view of the hashing: permutations/s vs the register-resident micro-benchmark
+        nthreads = 148 * 2048
+        pms = eng.bench_poseidon2(nthreads, 64)
+        perm_peak = nthreads * 64 / (pms * 1e-3)
+        mms = eng.bench_modmul(nthreads, 4096, 8)
+        int_pipe = {
+            "poseidon2_perm_per_s": perms / ((met["leaf_hash_ms"] + met["compress_ms"]) / steps * 1e-3),
+            "poseidon2_perm_per_s_register_peak": perm_peak,
+            "modmul_per_s_peak": nthreads * 4096 * 8 / (mms * 1e-3),
+        }
+        cpu = None
+        if not args.no_cpu:
+            threads = os.cpu_count() or 1
+            s = args.cpu_sample_log_height
+            dt = cpu_oracle_sample(s, width, b, threads)
+            cpu = {"value": algorithmic_bytes(s, width, b) / dt / 1e9, "unit": UNIT, "cores": threads, "kind": "port",
+                   "sample": f"2^{s} x {width} rows of the same synthetic trace, one commit, {dt:.2f} s"}
+        launches = met["lde_launches"] + met["leaf_hash_launches"] + met["compress_launches"] + met["other_launches"]
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
+            "data": "synthetic",
+            "config": {"workload": workload_name(log_h, width, b), "segments_per_gpu": 1,
+                       "l2": "inputs (16 GiB trace, 32 GiB LDE) are far larger than the 126 MB L2; no flush needed",
+                       "fri": {"log_blowup": b}},
+            "roofline": roofline, "roofline_lde": roofline_lde, "int_pipe": int_pipe, "cpu_baseline": cpu,
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "stage_ms_per_step": {"main_trace_commit_time_ms": met["commit_total_ms"] / steps,
+                                  "lde_ms": lde_ms_step, "leaf_hash_ms": met["leaf_hash_ms"] / steps,
+                                  "compress_ms": met["compress_ms"] / steps},
+            "root": [int(x) for x in root],
+        }
+        print(json.dumps(line), flush=True)
+    trace.free()
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

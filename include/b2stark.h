@@ -1,0 +1,158 @@
+/* b2stark — C ABI of the B200-native STARK proving backend (hot path of OpenVM's stark-backend).
+ *
+ * This header is the drop-in boundary. The reference selects its prover backend at compile time through
+ * Rust generics (E: StarkFriEngine, E::PD: ProverDevice = TraceCommitter + QuotientCommitter +
+ * OpeningProver + DeviceDataTransporter; /root/reference crates/sdk/src/lib.rs:71-83,127-131;
+ * crates/vm/src/arch/vm.rs:334-349). The traits themselves live in the un-vendored dependency
+ * openvm-stark-backend @ 002f52e (Cargo.toml:113-117); every entry point below cites the in-tree call
+ * site of the trait method it stands in for. A Rust shim forwards those methods here.
+ *
+ * Conventions
+ *   - every function returns int32_t: 0 = OK, negative = b2s_status, positive = raw cudaError_t;
+ *     no C++ exception crosses the ABI; b2s_last_error() gives a message.
+ *   - field elements are 32-bit words. `repr` says how a buffer crossing the ABI encodes them:
+ *       B2S_REPR_CANONICAL  value in [0,p)                       (wire format, codec.rs:309-313)
+ *       B2S_REPR_MONTY      value*2^32 mod p, in [0,p)           (Plonky3 BabyBear's in-memory form)
+ *     Device memory is always Montgomery form, column-major (element (r,c) at c*height + r), the layout
+ *     of the reference's DeviceMatrix (crates/circuits/primitives/cuda/include/primitives/trace_access.h:6-22).
+ *   - handles are opaque, library-allocated, released with the matching *_free; an engine is not
+ *     thread-safe; distinct engines are independent (one per GPU / per worker thread).
+ *   - there is no CPU fallback: every compute entry point runs CUDA kernels on the engine's device.
+ */
+#ifndef B2STARK_H
+#define B2STARK_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b2s_engine b2s_engine;
+typedef struct b2s_matrix b2s_matrix;     /* device matrix, column-major, Montgomery form */
+typedef struct b2s_pcs_data b2s_pcs_data; /* Merkle tree + retained LDE matrices of one commitment */
+
+typedef enum {
+    B2S_OK = 0,
+    B2S_ERR_BAD_ARG = -1,
+    B2S_ERR_SHAPE = -2,
+    B2S_ERR_OOM = -3,
+    B2S_ERR_NO_DEVICE = -4,
+    B2S_ERR_CONSTRAINT_DEGREE = -5,
+    B2S_ERR_VERIFY_FAILED = -6,
+    B2S_ERR_INTERNAL = -7
+} b2s_status;
+
+enum { B2S_LAYOUT_ROW_MAJOR = 0, B2S_LAYOUT_COL_MAJOR = 1 };
+enum { B2S_REPR_CANONICAL = 0, B2S_REPR_MONTY = 1 };
+
+/* FriParameters {log_blowup, log_final_poly_len, num_queries, proof_of_work_bits}
+ * (openvm_stark_sdk::config::FriParameters; defaults crates/sdk/src/config/mod.rs:15-18,
+ *  docs/vocs/docs/pages/specs/security/security-model.mdx:47-53). */
+typedef struct {
+    uint32_t log_blowup;
+    uint32_t log_final_poly_len;
+    uint32_t num_queries;
+    uint32_t proof_of_work_bits;
+} b2s_fri_params;
+
+/* Stage gauges, named after the reference's metrics (crates/prof/data/metrics.example.json). Times are
+ * device milliseconds accumulated since the last b2s_reset_metrics, measured with CUDA events on the
+ * engine's stream; *_launches count kernels launched by this library. */
+typedef struct {
+    double lde_ms;              /* iNTT + coset NTT passes                      */
+    double leaf_hash_ms;        /* Poseidon2 sponge over LDE rows                */
+    double compress_ms;         /* Poseidon2 2-to-1 layers                       */
+    double commit_total_ms;     /* = main_trace_commit_time_ms for one commit    */
+    double quotient_ms;         /* quotient_poly_compute_time_ms                 */
+    double opening_ms;          /* pcs_opening_time_ms                           */
+    double prove_total_ms;      /* stark_prove_excluding_trace_time_ms           */
+    uint64_t lde_launches;
+    uint64_t leaf_hash_launches;
+    uint64_t compress_launches;
+    uint64_t other_launches;
+    uint64_t poseidon2_permutations; /* permutations executed on the device */
+} b2s_metrics;
+
+/* ---- engine ------------------------------------------------------------------------------------------
+ * E::new(fri_params)            crates/sdk/src/prover/vm/mod.rs:22, crates/vm/src/utils/stark_utils.rs:115 */
+int32_t b2s_engine_new(const b2s_fri_params* params, int32_t cuda_device, b2s_engine** out);
+void b2s_engine_free(b2s_engine* e);
+/* engine.fri_params()           crates/sdk/src/prover/app.rs:139 */
+int32_t b2s_engine_fri_params(const b2s_engine* e, b2s_fri_params* out);
+/* message for the last non-zero status returned on this engine (or globally when e == NULL) */
+const char* b2s_last_error(const b2s_engine* e);
+/* the CUDA stream all work of this engine is ordered on (cudaStream_t as void*); set lets a caller that
+ * already owns a stream (e.g. the reference's tracegen) share it. */
+void* b2s_engine_stream(const b2s_engine* e);
+int32_t b2s_engine_set_stream(b2s_engine* e, void* cuda_stream);
+int32_t b2s_engine_synchronize(b2s_engine* e);
+int32_t b2s_reset_metrics(b2s_engine* e);
+int32_t b2s_get_metrics(b2s_engine* e, b2s_metrics* out); /* synchronises the stream */
+/* bytes currently held by this engine's handles / high-water mark */
+int32_t b2s_device_memory(const b2s_engine* e, uint64_t* in_use, uint64_t* peak);
+
+/* ---- matrices (DeviceDataTransporter) ----------------------------------------------------------------
+ * transport_matrix_to_device(&Arc<RowMajorMatrix>)      crates/vm/src/arch/vm.rs:731-734
+ * transport_matrix_from_device_to_host                  crates/vm/src/arch/vm.rs:1307-1312 */
+int32_t b2s_matrix_upload(b2s_engine* e, const uint32_t* host, uint64_t height, uint64_t width,
+                          int32_t layout, int32_t repr, b2s_matrix** out);
+int32_t b2s_matrix_download(b2s_engine* e, const b2s_matrix* m, uint32_t* host, int32_t layout, int32_t repr);
+/* zero-copy adoption of a caller-owned column-major Montgomery-form device buffer (the reference's
+ * DeviceMatrix{buffer,height,width}; crates/vm/src/system/cuda/program.rs:60,119). Not freed by us. */
+int32_t b2s_matrix_adopt_device(b2s_engine* e, void* device_ptr, uint64_t height, uint64_t width, b2s_matrix** out);
+/* uninitialised device matrix owned by the library */
+int32_t b2s_matrix_alloc(b2s_engine* e, uint64_t height, uint64_t width, b2s_matrix** out);
+/* deterministic synthetic contents generated on the device: element(r,c) =
+ * splitmix64(seed ^ ((c << 32) | r)) mod p; same generator in oracle/. */
+int32_t b2s_matrix_fill_synthetic(b2s_engine* e, b2s_matrix* m, uint64_t seed);
+uint64_t b2s_matrix_height(const b2s_matrix* m);
+uint64_t b2s_matrix_width(const b2s_matrix* m);
+void* b2s_matrix_device_ptr(const b2s_matrix* m);
+void b2s_matrix_free(b2s_matrix* m);
+
+/* ---- commitment (TraceCommitter) ---------------------------------------------------------------------
+ * device.commit(&[matrix]) -> (Com, PcsData)            crates/vm/src/arch/vm.rs:735,
+ *                                                       crates/vm/src/system/cuda/program.rs:80
+ * = TwoAdicFriPcs::commit: per matrix iDFT -> coset DFT on GENERATOR*H_{N*2^b}, rows bit-reversed
+ *   (extensions/native/recursion/src/fri/two_adic_pcs.rs:178-186), then one mixed-height Poseidon2
+ *   Merkle tree over all LDEs (extensions/native/circuit/src/poseidon2/README.md:9-17).
+ * root8 receives the commitment as 8 canonical words. The PcsData retains the LDE matrices. */
+int32_t b2s_commit(b2s_engine* e, const b2s_matrix* const* mats, size_t n_mats, uint32_t root8[8],
+                   b2s_pcs_data** out);
+/* the two halves of commit, exposed for parity tests and for the quotient / FRI commit-phase callers:
+ * coset LDE of evaluations over shift_in*H_N (shift_in canonical; 1 for traces) ... */
+int32_t b2s_coset_lde(b2s_engine* e, const b2s_matrix* in, uint32_t log_blowup, uint32_t shift_in,
+                      b2s_matrix** out);
+/* ... and the MMCS tree over already-extended matrices of power-of-two heights (not consumed). */
+int32_t b2s_mmcs_commit(b2s_engine* e, const b2s_matrix* const* mats, size_t n_mats, uint32_t root8[8],
+                        b2s_pcs_data** out);
+
+size_t b2s_pcs_num_matrices(const b2s_pcs_data* d);
+uint32_t b2s_pcs_log_max_height(const b2s_pcs_data* d);
+/* borrowed view of the i-th retained (LDE) matrix, valid while `d` lives */
+const b2s_matrix* b2s_pcs_matrix(const b2s_pcs_data* d, size_t i);
+/* Mmcs::open_batch(index): rows of every matrix (caller order, row index >> (log_max - log_h)),
+ * concatenated into rows_out (sum of widths words), and log_max_height sibling digests bottom-up into
+ * proof_out (8 words each); canonical words. (verifier side: fri/mod.rs:185-299) */
+int32_t b2s_pcs_open(b2s_engine* e, const b2s_pcs_data* d, uint64_t index, uint32_t* rows_out,
+                     uint32_t* proof_out);
+/* digest layer `level` (0 = leaves), n*8 canonical words, node-major; for tests */
+int32_t b2s_pcs_layer(b2s_engine* e, const b2s_pcs_data* d, uint32_t level, uint32_t* out);
+void b2s_pcs_free(b2s_pcs_data* d);
+
+/* ---- primitives run on the device, for known-answer / parity tests ------------------------------------ */
+/* n states of 16 canonical words, permuted in place on the GPU */
+int32_t b2s_poseidon2_permute(b2s_engine* e, uint32_t* host_states, size_t n_states);
+/* integer-pipe micro-benchmark: `iters` dependent Montgomery multiplications per thread on
+ * `threads` threads; returns device ms (the measured modmul/s is the IMAD "peak" of DESIGN.md) */
+int32_t b2s_bench_modmul(b2s_engine* e, uint64_t threads, uint32_t iters, int32_t ilp, double* ms_out);
+/* Poseidon2 permutations/s with state in registers and no memory traffic */
+int32_t b2s_bench_poseidon2(b2s_engine* e, uint64_t threads, uint32_t iters, double* ms_out);
+
+void b2s_free(void* p); /* releases host buffers returned by the library */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2STARK_H */

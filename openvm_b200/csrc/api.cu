@@ -1,0 +1,444 @@
+// C ABI of libb2stark.so (include/b2stark.h). Every entry point converts internal failures into status codes;
+// there is no CPU fallback behind any of them.
+#include "common.cuh"
+
+#include <mutex>
+
+using namespace b2;
+
+namespace b2 {
+void free_scales(b2s_engine* e);
+static std::string g_last_error;
+static std::mutex g_err_mu;
+}  // namespace b2
+
+// ---- engine internals ------------------------------------------------------------------------------------
+void* b2s_engine::dmalloc(size_t bytes) {
+    if (bytes == 0) bytes = 4;
+    void* p = nullptr;
+    cudaError_t err = cudaMallocAsync(&p, bytes, stream);
+    if (err == cudaErrorMemoryAllocation) {
+        cudaGetLastError();
+        fail(B2S_ERR_OOM, "device allocation of " + std::to_string(bytes) + " bytes failed");
+    }
+    B2_CUDA(err);
+    mem_in_use += bytes;
+    if (mem_in_use > mem_peak) mem_peak = mem_in_use;
+    return p;
+}
+void b2s_engine::dfree(void* p, size_t bytes) {
+    if (!p) return;
+    if (bytes == 0) bytes = 4;
+    cudaFreeAsync(p, stream);
+    mem_in_use -= bytes;
+}
+cudaEvent_t b2s_engine::get_event() {
+    if (!event_pool.empty()) {
+        cudaEvent_t ev = event_pool.back();
+        event_pool.pop_back();
+        return ev;
+    }
+    cudaEvent_t ev;
+    B2_CUDA(cudaEventCreate(&ev));
+    return ev;
+}
+void b2s_engine::stage_begin(Stage s) {
+    if (!metrics_enabled) return;
+    cudaEvent_t a = get_event();
+    B2_CUDA(cudaEventRecord(a, stream));
+    timers[s].pending.push_back({a, nullptr});
+}
+void b2s_engine::stage_end(Stage s) {
+    if (!metrics_enabled) return;
+    // close the innermost open interval of this stage
+    for (auto it = timers[s].pending.rbegin(); it != timers[s].pending.rend(); ++it) {
+        if (it->second == nullptr) {
+            cudaEvent_t b = get_event();
+            if (cudaEventRecord(b, stream) == cudaSuccess) it->second = b;
+            return;
+        }
+    }
+}
+void b2s_engine::collect_timers() {
+    B2_CUDA(cudaStreamSynchronize(stream));
+    for (int s = 0; s < ST_COUNT; s++) {
+        for (auto& pr : timers[s].pending) {
+            if (pr.first && pr.second) {
+                float ms = 0;
+                if (cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) timers[s].ms += ms;
+            }
+            if (pr.first) event_pool.push_back(pr.first);
+            if (pr.second) event_pool.push_back(pr.second);
+        }
+        timers[s].pending.clear();
+    }
+}
+
+namespace {
+
+template <typename F>
+int32_t guarded(const b2s_engine* e_const, F&& fn) {
+    b2s_engine* e = const_cast<b2s_engine*>(e_const);
+    try {
+        if (e) B2_CUDA(cudaSetDevice(e->device));
+        fn();
+        return B2S_OK;
+    } catch (const StatusError& se) {
+        if (e) e->last_error = se.msg;
+        std::lock_guard<std::mutex> lk(g_err_mu);
+        g_last_error = se.msg;
+        return se.code;
+    } catch (const std::bad_alloc&) {
+        if (e) e->last_error = "host allocation failed";
+        return B2S_ERR_OOM;
+    } catch (const std::exception& ex) {
+        if (e) e->last_error = ex.what();
+        return B2S_ERR_INTERNAL;
+    } catch (...) {
+        if (e) e->last_error = "unknown failure";
+        return B2S_ERR_INTERNAL;
+    }
+}
+
+b2s_matrix* new_matrix(b2s_engine* e, uint64_t height, uint64_t width) {
+    b2s_matrix* m = new b2s_matrix();
+    m->eng = e;
+    m->height = height;
+    m->width = width;
+    m->owned = true;
+    m->d = (uint32_t*)e->dmalloc(m->bytes());
+    return m;
+}
+
+void free_pcs(b2s_pcs_data* d) {
+    if (!d) return;
+    b2s_engine* e = d->eng;
+    for (size_t i = 0; i < d->layers.size(); i++) e->dfree(d->layers[i], d->layer_nodes[i] * 32);
+    for (size_t i = 0; i < d->mats.size(); i++)
+        if (d->owns[i]) b2s_matrix_free(d->mats[i]);
+    delete d;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t b2s_engine_new(const b2s_fri_params* params, int32_t cuda_device, b2s_engine** out) {
+    if (!params || !out) return B2S_ERR_BAD_ARG;
+    *out = nullptr;
+    return guarded(nullptr, [&] {
+        int count = 0;
+        cudaError_t err = cudaGetDeviceCount(&count);
+        if (err != cudaSuccess || count == 0) {
+            cudaGetLastError();
+            fail(B2S_ERR_NO_DEVICE, "no CUDA device available: b2stark has no CPU fallback");
+        }
+        B2_REQUIRE(cuda_device >= 0 && cuda_device < count, B2S_ERR_BAD_ARG, "cuda_device out of range");
+        B2_REQUIRE(params->log_blowup >= 1 && params->log_blowup <= 4, B2S_ERR_BAD_ARG, "log_blowup must be in [1,4]");
+        B2_CUDA(cudaSetDevice(cuda_device));
+        cudaDeviceProp prop;
+        B2_CUDA(cudaGetDeviceProperties(&prop, cuda_device));
+        B2_REQUIRE(prop.major >= 10, B2S_ERR_NO_DEVICE,
+                   std::string("device ") + prop.name + " is not sm_100-class; this library is built for sm_100a only");
+        b2s_engine* e = new b2s_engine();
+        e->device = cuda_device;
+        e->params = *params;
+        B2_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+        e->own_stream = true;
+        cudaMemPool_t pool;
+        B2_CUDA(cudaDeviceGetDefaultMemPool(&pool, cuda_device));
+        uint64_t thresh = UINT64_MAX;
+        B2_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
+        *out = e;
+    });
+}
+
+void b2s_engine_free(b2s_engine* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    cudaStreamSynchronize(e->stream);
+    try {
+        e->collect_timers();
+        free_twiddles(e);
+        free_scales(e);
+    } catch (...) {
+    }
+    for (auto ev : e->event_pool) cudaEventDestroy(ev);
+    cudaStreamSynchronize(e->stream);
+    if (e->own_stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+int32_t b2s_engine_fri_params(const b2s_engine* e, b2s_fri_params* out) {
+    if (!e || !out) return B2S_ERR_BAD_ARG;
+    *out = e->params;
+    return B2S_OK;
+}
+
+const char* b2s_last_error(const b2s_engine* e) {
+    if (e) return e->last_error.c_str();
+    return g_last_error.c_str();
+}
+
+void* b2s_engine_stream(const b2s_engine* e) { return e ? (void*)e->stream : nullptr; }
+
+int32_t b2s_engine_set_stream(b2s_engine* e, void* cuda_stream) {
+    if (!e) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] {
+        B2_CUDA(cudaStreamSynchronize(e->stream));
+        if (e->own_stream) B2_CUDA(cudaStreamDestroy(e->stream));
+        e->stream = (cudaStream_t)cuda_stream;
+        e->own_stream = false;
+    });
+}
+
+int32_t b2s_engine_synchronize(b2s_engine* e) {
+    if (!e) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] { B2_CUDA(cudaStreamSynchronize(e->stream)); });
+}
+
+int32_t b2s_reset_metrics(b2s_engine* e) {
+    if (!e) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] {
+        e->collect_timers();
+        for (int s = 0; s < ST_COUNT; s++) e->timers[s].ms = 0;
+        for (auto& l : e->launches) l = 0;
+        e->permutations = 0;
+    });
+}
+
+int32_t b2s_get_metrics(b2s_engine* e, b2s_metrics* out) {
+    if (!e || !out) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] {
+        e->collect_timers();
+        memset(out, 0, sizeof(*out));
+        out->lde_ms = e->timers[ST_LDE].ms;
+        out->leaf_hash_ms = e->timers[ST_LEAF].ms;
+        out->compress_ms = e->timers[ST_COMPRESS].ms;
+        out->commit_total_ms = e->timers[ST_COMMIT].ms;
+        out->quotient_ms = e->timers[ST_QUOTIENT].ms;
+        out->opening_ms = e->timers[ST_OPENING].ms;
+        out->prove_total_ms = e->timers[ST_PROVE].ms;
+        out->lde_launches = e->launches[0];
+        out->leaf_hash_launches = e->launches[1];
+        out->compress_launches = e->launches[2];
+        out->other_launches = e->launches[3];
+        out->poseidon2_permutations = e->permutations;
+    });
+}
+
+int32_t b2s_device_memory(const b2s_engine* e, uint64_t* in_use, uint64_t* peak) {
+    if (!e) return B2S_ERR_BAD_ARG;
+    if (in_use) *in_use = e->mem_in_use;
+    if (peak) *peak = e->mem_peak;
+    return B2S_OK;
+}
+
+// ---- matrices ------------------------------------------------------------------------------------------------
+int32_t b2s_matrix_upload(b2s_engine* e, const uint32_t* host, uint64_t height, uint64_t width, int32_t layout,
+                          int32_t repr, b2s_matrix** out) {
+    if (!e || !out || (!host && height * width)) return B2S_ERR_BAD_ARG;
+    *out = nullptr;
+    return guarded(e, [&] {
+        B2_REQUIRE(layout == B2S_LAYOUT_ROW_MAJOR || layout == B2S_LAYOUT_COL_MAJOR, B2S_ERR_BAD_ARG, "bad layout");
+        B2_REQUIRE(repr == B2S_REPR_CANONICAL || repr == B2S_REPR_MONTY, B2S_ERR_BAD_ARG, "bad repr");
+        b2s_matrix* m = new_matrix(e, height, width);
+        size_t bytes = m->bytes();
+        if (bytes) {
+            if (layout == B2S_LAYOUT_COL_MAJOR) {
+                B2_CUDA(cudaMemcpyAsync(m->d, host, bytes, cudaMemcpyHostToDevice, e->stream));
+                if (repr == B2S_REPR_CANONICAL) convert_repr(e, m->d, (size_t)height * width, true);
+            } else {
+                uint32_t* tmp = (uint32_t*)e->dmalloc(bytes);
+                B2_CUDA(cudaMemcpyAsync(tmp, host, bytes, cudaMemcpyHostToDevice, e->stream));
+                transpose_to_colmajor(e, tmp, m->d, height, width, repr == B2S_REPR_CANONICAL);
+                e->dfree(tmp, bytes);
+            }
+        }
+        *out = m;
+    });
+}
+
+int32_t b2s_matrix_download(b2s_engine* e, const b2s_matrix* m, uint32_t* host, int32_t layout, int32_t repr) {
+    if (!e || !m || !host) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] {
+        size_t bytes = m->bytes();
+        if (!bytes) return;
+        uint32_t* tmp = (uint32_t*)e->dmalloc(bytes);
+        if (layout == B2S_LAYOUT_ROW_MAJOR) {
+            transpose_to_rowmajor(e, m->d, tmp, m->height, m->width, repr == B2S_REPR_CANONICAL);
+        } else {
+            B2_CUDA(cudaMemcpyAsync(tmp, m->d, bytes, cudaMemcpyDeviceToDevice, e->stream));
+            if (repr == B2S_REPR_CANONICAL) convert_repr(e, tmp, (size_t)m->height * m->width, false);
+        }
+        B2_CUDA(cudaMemcpyAsync(host, tmp, bytes, cudaMemcpyDeviceToHost, e->stream));
+        B2_CUDA(cudaStreamSynchronize(e->stream));
+        e->dfree(tmp, bytes);
+    });
+}
+
+int32_t b2s_matrix_adopt_device(b2s_engine* e, void* device_ptr, uint64_t height, uint64_t width, b2s_matrix** out) {
+    if (!e || !out || !device_ptr) return B2S_ERR_BAD_ARG;
+    b2s_matrix* m = new b2s_matrix();
+    m->eng = e;
+    m->d = (uint32_t*)device_ptr;
+    m->height = height;
+    m->width = width;
+    m->owned = false;
+    *out = m;
+    return B2S_OK;
+}
+
+int32_t b2s_matrix_alloc(b2s_engine* e, uint64_t height, uint64_t width, b2s_matrix** out) {
+    if (!e || !out) return B2S_ERR_BAD_ARG;
+    *out = nullptr;
+    return guarded(e, [&] { *out = new_matrix(e, height, width); });
+}
+
+int32_t b2s_matrix_fill_synthetic(b2s_engine* e, b2s_matrix* m, uint64_t seed) {
+    if (!e || !m) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] { fill_synthetic(e, m->d, m->height, m->width, seed); });
+}
+
+uint64_t b2s_matrix_height(const b2s_matrix* m) { return m ? m->height : 0; }
+uint64_t b2s_matrix_width(const b2s_matrix* m) { return m ? m->width : 0; }
+void* b2s_matrix_device_ptr(const b2s_matrix* m) { return m ? (void*)m->d : nullptr; }
+
+void b2s_matrix_free(b2s_matrix* m) {
+    if (!m) return;
+    if (m->owned && m->d) {
+        cudaSetDevice(m->eng->device);
+        m->eng->dfree(m->d, m->bytes());
+    }
+    delete m;
+}
+
+// ---- commitment --------------------------------------------------------------------------------------------
+int32_t b2s_coset_lde(b2s_engine* e, const b2s_matrix* in, uint32_t log_blowup, uint32_t shift_in, b2s_matrix** out) {
+    if (!e || !in || !out) return B2S_ERR_BAD_ARG;
+    *out = nullptr;
+    return guarded(e, [&] {
+        B2_REQUIRE(is_pow2(in->height), B2S_ERR_SHAPE, "lde: height must be a power of two");
+        B2_REQUIRE(shift_in > 0 && shift_in < P, B2S_ERR_BAD_ARG, "lde: shift must be a non-zero canonical element");
+        unsigned logn = log2_exact(in->height);
+        b2s_matrix* m = new_matrix(e, in->height << log_blowup, in->width);
+        try {
+            StageScope sc(e, ST_LDE);
+            lde_columns(e, in->d, in->height, logn, in->width, log_blowup, Fp::from_canonical(shift_in), m->d, m->height);
+        } catch (...) {
+            b2s_matrix_free(m);
+            throw;
+        }
+        *out = m;
+    });
+}
+
+static void root_to_host(b2s_engine* e, b2s_pcs_data* d, uint32_t root8[8]) {
+    uint32_t raw[8];
+    B2_CUDA(cudaMemcpyAsync(raw, d->layers.back(), 32, cudaMemcpyDeviceToHost, e->stream));
+    B2_CUDA(cudaStreamSynchronize(e->stream));
+    for (int i = 0; i < 8; i++) root8[i] = Fp::raw(raw[i]).to_canonical();
+}
+
+int32_t b2s_mmcs_commit(b2s_engine* e, const b2s_matrix* const* mats, size_t n_mats, uint32_t root8[8],
+                        b2s_pcs_data** out) {
+    if (!e || !mats || !n_mats || !root8 || !out) return B2S_ERR_BAD_ARG;
+    *out = nullptr;
+    return guarded(e, [&] {
+        b2s_pcs_data* d = new b2s_pcs_data();
+        d->eng = e;
+        for (size_t i = 0; i < n_mats; i++) {
+            B2_REQUIRE(mats[i] != nullptr, B2S_ERR_BAD_ARG, "null matrix");
+            b2s_matrix* view = new b2s_matrix(*mats[i]);
+            view->owned = false;
+            d->mats.push_back(view);
+            d->owns.push_back(true);  // frees the view object only (owned == false keeps the buffer)
+        }
+        try {
+            mmcs_build(e, d);
+            root_to_host(e, d, root8);
+        } catch (...) {
+            free_pcs(d);
+            throw;
+        }
+        *out = d;
+    });
+}
+
+int32_t b2s_commit(b2s_engine* e, const b2s_matrix* const* mats, size_t n_mats, uint32_t root8[8], b2s_pcs_data** out) {
+    if (!e || !mats || !n_mats || !root8 || !out) return B2S_ERR_BAD_ARG;
+    *out = nullptr;
+    return guarded(e, [&] {
+        StageScope total(e, ST_COMMIT);
+        b2s_pcs_data* d = new b2s_pcs_data();
+        d->eng = e;
+        try {
+            const uint32_t lb = e->params.log_blowup;
+            for (size_t i = 0; i < n_mats; i++) {
+                const b2s_matrix* in = mats[i];
+                B2_REQUIRE(in != nullptr, B2S_ERR_BAD_ARG, "null matrix");
+                B2_REQUIRE(is_pow2(in->height), B2S_ERR_SHAPE, "commit: trace height must be a power of two");
+                B2_REQUIRE(in->width > 0, B2S_ERR_SHAPE, "commit: zero-width trace");
+                b2s_matrix* lde = new_matrix(e, in->height << lb, in->width);
+                d->mats.push_back(lde);
+                d->owns.push_back(true);
+                StageScope sc(e, ST_LDE);
+                lde_columns(e, in->d, in->height, log2_exact(in->height), in->width, lb, Fp::one(), lde->d, lde->height);
+            }
+            mmcs_build(e, d);
+            root_to_host(e, d, root8);
+        } catch (...) {
+            free_pcs(d);
+            throw;
+        }
+        *out = d;
+    });
+}
+
+size_t b2s_pcs_num_matrices(const b2s_pcs_data* d) { return d ? d->mats.size() : 0; }
+uint32_t b2s_pcs_log_max_height(const b2s_pcs_data* d) { return d ? d->log_max_height : 0; }
+const b2s_matrix* b2s_pcs_matrix(const b2s_pcs_data* d, size_t i) { return (d && i < d->mats.size()) ? d->mats[i] : nullptr; }
+
+int32_t b2s_pcs_open(b2s_engine* e, const b2s_pcs_data* d, uint64_t index, uint32_t* rows_out, uint32_t* proof_out) {
+    if (!e || !d) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] { gather_open(e, d, index, rows_out, proof_out); });
+}
+
+int32_t b2s_pcs_layer(b2s_engine* e, const b2s_pcs_data* d, uint32_t level, uint32_t* out) {
+    if (!e || !d || !out) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] { download_layer(e, d, level, out); });
+}
+
+void b2s_pcs_free(b2s_pcs_data* d) {
+    if (!d) return;
+    cudaSetDevice(d->eng->device);
+    free_pcs(d);
+}
+
+// ---- primitives ----------------------------------------------------------------------------------------------
+int32_t b2s_poseidon2_permute(b2s_engine* e, uint32_t* host_states, size_t n_states) {
+    if (!e || (!host_states && n_states)) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] {
+        if (!n_states) return;
+        size_t bytes = n_states * 64;
+        uint32_t* d = (uint32_t*)e->dmalloc(bytes);
+        B2_CUDA(cudaMemcpyAsync(d, host_states, bytes, cudaMemcpyHostToDevice, e->stream));
+        poseidon2_permute_states(e, d, n_states);
+        B2_CUDA(cudaMemcpyAsync(host_states, d, bytes, cudaMemcpyDeviceToHost, e->stream));
+        B2_CUDA(cudaStreamSynchronize(e->stream));
+        e->dfree(d, bytes);
+    });
+}
+
+int32_t b2s_bench_modmul(b2s_engine* e, uint64_t threads, uint32_t iters, int32_t ilp, double* ms_out) {
+    if (!e || !ms_out) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] { *ms_out = bench_modmul(e, threads, iters, ilp); });
+}
+int32_t b2s_bench_poseidon2(b2s_engine* e, uint64_t threads, uint32_t iters, double* ms_out) {
+    if (!e || !ms_out) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] { *ms_out = bench_poseidon2(e, threads, iters); });
+}
+
+void b2s_free(void* p) { free(p); }
+
+}  // extern "C"

@@ -1,0 +1,133 @@
+// Internal definitions shared by the translation units of libb2stark.so (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <map>
+#include <stdexcept>
+
+#include "../../include/b2stark.h"
+#include "field.cuh"
+
+namespace b2 {
+
+constexpr int NUM_SMS_B200 = 148;
+
+struct StatusError {
+    int32_t code;
+    std::string msg;
+};
+
+[[noreturn]] inline void fail(int32_t code, const std::string& msg) { throw StatusError{code, msg}; }
+
+#define B2_CUDA(expr)                                                                                   \
+    do {                                                                                                \
+        cudaError_t _e = (expr);                                                                        \
+        if (_e != cudaSuccess) {                                                                        \
+            ::b2::fail((int32_t)_e, std::string(#expr) + ": " + cudaGetErrorString(_e) + " (" + __FILE__ + \
+                                        ":" + std::to_string(__LINE__) + ")");                          \
+        }                                                                                               \
+    } while (0)
+
+#define B2_CHECK_LAUNCH() B2_CUDA(cudaGetLastError())
+
+#define B2_REQUIRE(cond, code, msg)                      \
+    do {                                                 \
+        if (!(cond)) ::b2::fail((code), std::string(msg)); \
+    } while (0)
+
+struct TwiddleSet;
+struct ScaleSet;
+
+enum Stage { ST_LDE = 0, ST_LEAF, ST_COMPRESS, ST_COMMIT, ST_QUOTIENT, ST_OPENING, ST_PROVE, ST_COUNT };
+
+struct StageTimer {
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending;
+    double ms = 0;
+};
+
+}  // namespace b2
+
+struct b2s_engine {
+    int device = 0;
+    b2s_fri_params params{};
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string last_error;
+    uint64_t mem_in_use = 0, mem_peak = 0;
+    bool metrics_enabled = true;
+    b2::StageTimer timers[b2::ST_COUNT];
+    std::vector<cudaEvent_t> event_pool;
+    uint64_t launches[4] = {0, 0, 0, 0};  // lde, leaf, compress, other
+    uint64_t permutations = 0;
+    std::map<unsigned, b2::TwiddleSet*> twiddles;  // by log size
+    std::map<uint64_t, b2::ScaleSet*> scales;      // by (logn, log_blowup, shift_in)
+
+    void* dmalloc(size_t bytes);
+    void dfree(void* p, size_t bytes);
+    cudaEvent_t get_event();
+    void stage_begin(b2::Stage s);
+    void stage_end(b2::Stage s);
+    void collect_timers();
+};
+
+struct b2s_matrix {
+    b2s_engine* eng = nullptr;
+    uint32_t* d = nullptr;  // column-major, Montgomery form
+    uint64_t height = 0, width = 0;
+    bool owned = true;
+    size_t bytes() const { return (size_t)height * width * 4; }
+};
+
+struct b2s_pcs_data {
+    b2s_engine* eng = nullptr;
+    std::vector<b2s_matrix*> mats;      // caller order; LDE matrices
+    std::vector<bool> owns;             // whether mats[i] is freed with the tree
+    unsigned log_max_height = 0;
+    // digest layers, level 0 = leaves; each layer is 8 word-planes of n nodes: word w of node i at [w*n + i]
+    std::vector<uint32_t*> layers;
+    std::vector<uint64_t> layer_nodes;
+};
+
+namespace b2 {
+
+inline unsigned log2_exact(uint64_t x) {
+    unsigned l = 0;
+    while (((uint64_t)1 << l) < x) l++;
+    return l;
+}
+inline bool is_pow2(uint64_t x) { return x && !(x & (x - 1)); }
+
+// RAII stage scope
+struct StageScope {
+    b2s_engine* e;
+    Stage s;
+    StageScope(b2s_engine* e_, Stage s_) : e(e_), s(s_) { e->stage_begin(s); }
+    ~StageScope() { e->stage_end(s); }
+};
+
+// ---- kernels' host entry points (defined in the .cu files) ---------------------------------------------
+// ntt.cu
+void lde_columns(b2s_engine* e, const uint32_t* in, uint64_t in_col_stride, unsigned logn, uint64_t width,
+                 unsigned log_blowup, Fp shift_in, uint32_t* out, uint64_t out_col_stride);
+void free_twiddles(b2s_engine* e);
+void free_scales(b2s_engine* e);
+// merkle.cu
+void mmcs_build(b2s_engine* e, b2s_pcs_data* d);
+void poseidon2_permute_states(b2s_engine* e, uint32_t* d_states, size_t n);
+void convert_repr(b2s_engine* e, uint32_t* d, size_t n, bool to_monty);
+void transpose_to_colmajor(b2s_engine* e, const uint32_t* d_rowmajor, uint32_t* d_colmajor, uint64_t height,
+                           uint64_t width, bool to_monty);
+void transpose_to_rowmajor(b2s_engine* e, const uint32_t* d_colmajor, uint32_t* d_rowmajor, uint64_t height,
+                           uint64_t width, bool to_canonical);
+void fill_synthetic(b2s_engine* e, uint32_t* d, uint64_t height, uint64_t width, uint64_t seed);
+void gather_open(b2s_engine* e, const b2s_pcs_data* d, uint64_t index, uint32_t* h_rows, uint32_t* h_proof);
+void download_layer(b2s_engine* e, const b2s_pcs_data* d, uint32_t level, uint32_t* h_out);
+double bench_modmul(b2s_engine* e, uint64_t threads, uint32_t iters, int ilp);
+double bench_poseidon2(b2s_engine* e, uint64_t threads, uint32_t iters);
+
+}  // namespace b2

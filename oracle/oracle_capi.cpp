@@ -1,0 +1,142 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see babybear.hpp header). C ABI for ctypes (tests/, bench cpu_baseline).
+#include "babybear.hpp"
+#include "poseidon2.hpp"
+#include "mmcs.hpp"
+#include "dft.hpp"
+#include <cstring>
+
+using namespace orc;
+
+static inline EF load_ef(const uint32_t* a) { return EF{F(a[0]), F(a[1]), F(a[2]), F(a[3])}; }
+
+extern "C" {
+
+// ---- constants -------------------------------------------------------------------------------
+// out: 4*16 ext_init, 13 partial, 4*16 ext_term, 16 diag  (canonical u32) = 157 words
+void orc_poseidon2_constants(uint32_t* out) {
+    const Poseidon2Constants& c = poseidon2_constants();
+    size_t k = 0;
+    for (int r = 0; r < 4; r++) for (int i = 0; i < 16; i++) out[k++] = c.ext_init[r][i].v;
+    for (int r = 0; r < 13; r++) out[k++] = c.partial[r].v;
+    for (int r = 0; r < 4; r++) for (int i = 0; i < 16; i++) out[k++] = c.ext_term[r][i].v;
+    for (int i = 0; i < 16; i++) out[k++] = c.diag[i].v;
+}
+uint32_t orc_two_adic_generator(uint32_t bits) { return two_adic_generator(bits).v; }
+
+// ---- field ------------------------------------------------------------------------------------
+void orc_ef_mul(const uint32_t* a, const uint32_t* b, uint32_t* out) {
+    EF x = load_ef(a), y = load_ef(b);
+    EF r = x * y;
+    for (int i = 0; i < 4; i++) out[i] = r.c[i].v;
+}
+void orc_ef_inv(const uint32_t* a, uint32_t* out) {
+    EF x = load_ef(a);
+    EF r = einv(x);
+    for (int i = 0; i < 4; i++) out[i] = r.c[i].v;
+}
+
+// ---- poseidon2 --------------------------------------------------------------------------------
+void orc_poseidon2_permute(uint32_t* state, size_t n_states) {
+    for (size_t k = 0; k < n_states; k++) {
+        F s[16];
+        for (int i = 0; i < 16; i++) s[i] = F(state[16 * k + i]);
+        poseidon2_permute(s);
+        for (int i = 0; i < 16; i++) state[16 * k + i] = s[i].v;
+    }
+}
+void orc_hash_slice(const uint32_t* x, size_t n, uint32_t* out8) {
+    Digest d = hash_slice(reinterpret_cast<const F*>(x), n);
+    for (int i = 0; i < 8; i++) out8[i] = d[i].v;
+}
+void orc_compress(const uint32_t* l, const uint32_t* r, uint32_t* out8) {
+    Digest a, b;
+    for (int i = 0; i < 8; i++) { a[i] = F(l[i]); b[i] = F(r[i]); }
+    Digest d = compress(a, b);
+    for (int i = 0; i < 8; i++) out8[i] = d[i].v;
+}
+
+// ---- dft / lde --------------------------------------------------------------------------------
+void orc_dft(uint32_t* a, uint32_t logn, int inverse) {
+    if (inverse) idft(reinterpret_cast<F*>(a), logn); else dft(reinterpret_cast<F*>(a), logn);
+}
+// column-major in (height 2^logn) -> column-major out (height 2^(logn+b)), bit-reversed rows
+void orc_coset_lde(const uint32_t* in, uint32_t logn, uint32_t width, uint32_t log_blowup, uint32_t shift_in,
+                   uint32_t* out, int threads) {
+    size_t n = (size_t)1 << logn, m = n << log_blowup;
+    parallel_for(width, threads, [&](size_t lo, size_t hi) {
+        for (size_t c = lo; c < hi; c++)
+            coset_lde_column(reinterpret_cast<const F*>(in) + c * n, logn, log_blowup, F(shift_in),
+                             reinterpret_cast<F*>(out) + c * m);
+    });
+}
+uint32_t orc_eval_naive(const uint32_t* evals, uint32_t logn, uint32_t shift_in, uint32_t x) {
+    return eval_poly_from_evals_naive(reinterpret_cast<const F*>(evals), logn, F(shift_in), F(x)).v;
+}
+
+// ---- mmcs -------------------------------------------------------------------------------------
+// n matrices (column-major, canonical u32). Returns root; if layers_out != NULL it receives all digest
+// layers concatenated bottom-up (hmax + hmax/2 + ... + 1 digests of 8 words).
+void orc_mmcs_commit(const uint32_t* const* mats, const uint64_t* heights, const uint64_t* widths, size_t n,
+                     uint32_t* root8, uint32_t* layers_out, int threads) {
+    std::vector<MatView> ms(n);
+    for (size_t i = 0; i < n; i++) ms[i] = MatView{reinterpret_cast<const F*>(mats[i]), (size_t)heights[i], (size_t)widths[i]};
+    MerkleTree t;
+    t.build(ms, threads);
+    Digest r = t.root();
+    for (int i = 0; i < 8; i++) root8[i] = r[i].v;
+    if (layers_out) {
+        size_t k = 0;
+        for (auto& L : t.layers) for (auto& d : L) for (int i = 0; i < 8; i++) layers_out[k++] = d[i].v;
+    }
+}
+
+// open + verify round trip at `index`; returns 1 if the oracle verifier accepts the oracle opening
+int orc_mmcs_open_verify(const uint32_t* const* mats, const uint64_t* heights, const uint64_t* widths, size_t n,
+                         uint64_t index, uint32_t* proof_out /* log_max_height*8 */, int corrupt) {
+    std::vector<MatView> ms(n);
+    std::vector<size_t> hs(n);
+    for (size_t i = 0; i < n; i++) { ms[i] = MatView{reinterpret_cast<const F*>(mats[i]), (size_t)heights[i], (size_t)widths[i]}; hs[i] = heights[i]; }
+    MerkleTree t;
+    t.build(ms, 1);
+    std::vector<std::vector<F>> rows;
+    std::vector<Digest> proof;
+    t.open(index, rows, proof);
+    if (proof_out) { size_t k = 0; for (auto& d : proof) for (int i = 0; i < 8; i++) proof_out[k++] = d[i].v; }
+    if (corrupt && !rows.empty() && !rows[0].empty()) rows[0][0] += F(1);
+    return mmcs_verify_batch(t.root(), hs, index, rows, proof) ? 1 : 0;
+}
+
+// Full commit of one or more trace matrices (all on the trivial coset, shift 1):
+// LDE each, then MMCS over the LDEs. lde_out[i] may be NULL.
+void orc_commit(const uint32_t* const* mats, const uint64_t* log_heights, const uint64_t* widths, size_t n,
+                uint32_t log_blowup, uint32_t* root8, uint32_t* const* lde_out, int threads) {
+    std::vector<std::vector<F>> ldes(n);
+    std::vector<MatView> ms(n);
+    for (size_t i = 0; i < n; i++) {
+        size_t h = (size_t)1 << log_heights[i], m = h << log_blowup;
+        ldes[i].resize(m * widths[i]);
+        orc_coset_lde(mats[i], (uint32_t)log_heights[i], (uint32_t)widths[i], log_blowup, 1,
+                      reinterpret_cast<uint32_t*>(ldes[i].data()), threads);
+        ms[i] = MatView{ldes[i].data(), m, (size_t)widths[i]};
+        if (lde_out && lde_out[i]) memcpy(lde_out[i], ldes[i].data(), m * widths[i] * 4);
+    }
+    MerkleTree t;
+    t.build(ms, threads);
+    Digest r = t.root();
+    for (int i = 0; i < 8; i++) root8[i] = r[i].v;
+}
+
+// ---- synthetic input (same generator as b2s_matrix_fill_synthetic) ---------
+static inline uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+// column-major canonical output
+void orc_fill_synthetic(uint32_t* out, uint64_t height, uint64_t width, uint64_t seed) {
+    for (uint64_t c = 0; c < width; c++)
+        for (uint64_t r = 0; r < height; r++) out[c * height + r] = (uint32_t)(splitmix64(seed ^ ((c << 32) | r)) % P);
+}
+
+}  // extern "C"
