@@ -6,10 +6,11 @@
 //   extensions/native/recursion/src/fri/mod.rs:185-299 (verify_batch).
 //
 // Kernels (all integer-pipe bound; one Poseidon2 permutation chain per thread, state in registers):
-//   row_hash_kernel   sponge over one LDE row across every matrix of a height group (coalesced: adjacent
-//                     threads read adjacent rows of the same column), optionally fused with the
-//                     compress-and-inject step of the level the group joins the tree at
-//   compress_kernel   2-to-1 compression of one digest layer
+//   tree_level_kernel one node per thread: sponge over one LDE row across every matrix of a height group
+//                     (coalesced: adjacent threads read adjacent rows of the same column), optionally fused with
+//                     the compress-and-inject step of the level the group joins the tree at; or a plain 2-to-1
+//                     compression of the previous digest layer
+//   tree_tail_kernel  all levels of <= 256 nodes in one launch
 // Digest layers are stored as 8 word-planes (word w of node i at [w*n + i]) so both kernels read and
 // write fully coalesced.
 #include "common.cuh"
@@ -18,75 +19,95 @@
 namespace b2 {
 
 constexpr int HASH_THREADS = 128;
+constexpr int HASH_MIN_BLOCKS = 8;  // 1024 threads/SM -> <= 64 registers/thread
 
-// absorb the row `row` of `ncols` columns (pointer per column) in overwrite mode, rate 8
-B2_D void sponge_row(const uint32_t* const* __restrict__ cols, uint32_t ncols, uint64_t row, Fp (&s)[16]) {
-#pragma unroll
-    for (int i = 0; i < 16; i++) s[i] = Fp::zero();
-    uint32_t c = 0;
-    for (; c + 8 <= ncols; c += 8) {
-        uint32_t v[8];
-#pragma unroll
-        for (int k = 0; k < 8; k++) v[k] = __ldg(cols[c + k] + row);
-#pragma unroll
-        for (int k = 0; k < 8; k++) s[k] = Fp::raw(v[k]);
-        poseidon2_permute(s);
-    }
-    if (c < ncols) {
-        uint32_t rem = ncols - c;
-#pragma unroll
-        for (int k = 0; k < 8; k++)
-            if ((uint32_t)k < rem) s[k] = Fp::raw(__ldg(cols[c + k] + row));
-        poseidon2_permute(s);
-    }
-}
-
-// mode 0: out[node] = rowhash(node)
-// mode 1: out[node] = compress(compress(prev[2node], prev[2node+1]), rowhash(node))
-__global__ void __launch_bounds__(HASH_THREADS) row_hash_kernel(const uint32_t* const* __restrict__ cols,
-                                                                uint32_t ncols, uint64_t n,
-                                                                const uint32_t* __restrict__ prev,
-                                                                uint32_t* __restrict__ out, int mode) {
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+// One thread produces one node of a tree level. All Poseidon2 work of a node -- the sponge over its row
+// (ceil(ncols/8) permutations, overwrite mode, rate 8, no padding) and, when the row group is injected below the
+// leaves, the two compressions  compress(compress(prev[2i], prev[2i+1]), rowhash(i))  -- runs through ONE
+// permutation call site inside a rolled loop, so the kernel holds a single ~9 KB copy of the permutation.
+// The next chunk's eight words are fetched before the current permutation starts (latency hidden behind
+// ~6 k integer instructions).
+//   mode 0: out[i] = rowhash(i)
+//   mode 1: out[i] = compress(compress(prev[2i], prev[2i+1]), rowhash(i))
+//   mode 2: out[i] = compress(prev[2i], prev[2i+1])                       (ncols == 0)
+B2_D void hash_node(const uint32_t* const* __restrict__ cols, uint32_t ncols, uint64_t n,
+                    const uint32_t* prev, uint32_t* out, int mode, uint64_t i) {
     Fp s[16];
-    sponge_row(cols, ncols, i, s);
-    if (mode == 1) {
-        Fp t[16];
-        const uint64_t np = 2 * n;
 #pragma unroll
-        for (int w = 0; w < 8; w++) {
-            uint2 lr = *reinterpret_cast<const uint2*>(prev + (uint64_t)w * np + 2 * i);
-            t[w] = Fp::raw(lr.x);
-            t[8 + w] = Fp::raw(lr.y);
+    for (int k = 0; k < 16; k++) s[k] = Fp::zero();
+    const uint32_t chunks = (ncols + 7) >> 3;
+    const uint32_t total = chunks + (mode == 0 ? 0u : (mode == 1 ? 2u : 1u));
+    uint32_t nxt[8];
+    Fp keep[8];
+    auto fetch = [&](uint32_t chunk) {
+        const uint32_t c = chunk << 3;
+#pragma unroll
+        for (int k = 0; k < 8; k++) nxt[k] = (c + k < ncols) ? __ldg(cols[c + k] + i) : 0u;
+    };
+    if (chunks) fetch(0);
+#pragma unroll 1
+    for (uint32_t it = 0; it < total; it++) {
+        if (it < chunks) {
+            const uint32_t c = it << 3;
+            if (c + 8 <= ncols) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) s[k] = Fp::raw(nxt[k]);
+            } else {
+#pragma unroll
+                for (int k = 0; k < 8; k++)
+                    if (c + k < ncols) s[k] = Fp::raw(nxt[k]);
+            }
+            if (it + 1 < chunks) fetch(it + 1);
+        } else if (it == chunks && mode != 0) {
+            const uint64_t np = 2 * n;
+#pragma unroll
+            for (int w = 0; w < 8; w++) {
+                keep[w] = s[w];
+                // L2-coherent load: in the tail kernel `prev` was written by this block one barrier earlier
+                uint2 lr = __ldcg(reinterpret_cast<const uint2*>(prev + (uint64_t)w * np + 2 * i));
+                s[w] = Fp::raw(lr.x);
+                s[8 + w] = Fp::raw(lr.y);
+            }
+        } else {
+#pragma unroll
+            for (int w = 0; w < 8; w++) s[8 + w] = keep[w];
         }
-        poseidon2_permute(t);
-#pragma unroll
-        for (int w = 0; w < 8; w++) { t[8 + w] = s[w]; }
-        poseidon2_permute(t);
-#pragma unroll
-        for (int w = 0; w < 8; w++) out[(uint64_t)w * n + i] = t[w].v;
-    } else {
-#pragma unroll
-        for (int w = 0; w < 8; w++) out[(uint64_t)w * n + i] = s[w].v;
+        poseidon2_permute(s);
     }
+#pragma unroll
+    for (int w = 0; w < 8; w++) out[(uint64_t)w * n + i] = s[w].v;
 }
 
-__global__ void __launch_bounds__(HASH_THREADS) compress_kernel(const uint32_t* __restrict__ prev,
-                                                                uint32_t* __restrict__ out, uint64_t n) {
+__global__ void __launch_bounds__(HASH_THREADS, HASH_MIN_BLOCKS)
+    tree_level_kernel(const uint32_t* const* __restrict__ cols, uint32_t ncols, uint64_t n,
+                      const uint32_t* __restrict__ prev, uint32_t* __restrict__ out, int mode) {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    Fp t[16];
-    const uint64_t np = 2 * n;
-#pragma unroll
-    for (int w = 0; w < 8; w++) {
-        uint2 lr = *reinterpret_cast<const uint2*>(prev + (uint64_t)w * np + 2 * i);
-        t[w] = Fp::raw(lr.x);
-        t[8 + w] = Fp::raw(lr.y);
+    hash_node(cols, ncols, n, prev, out, mode, i);
+}
+
+// The top of the tree (levels of <= TAIL_NODES nodes) in one launch: one block walks the levels with a block
+// barrier in between, instead of one ~3 us launch per level.
+constexpr int TAIL_THREADS = 256;
+constexpr int TAIL_MAX_LEVELS = 12;
+struct TailParams {
+    const uint32_t* const* cols[TAIL_MAX_LEVELS];
+    uint32_t ncols[TAIL_MAX_LEVELS];
+    uint32_t* out[TAIL_MAX_LEVELS];
+    const uint32_t* prev0;
+    uint64_t n0;        // nodes of the first level handled here
+    uint32_t levels;
+};
+__global__ void __launch_bounds__(TAIL_THREADS, 1) tree_tail_kernel(TailParams p) {
+    const uint32_t* prev = p.prev0;
+    uint64_t n = p.n0;
+#pragma unroll 1
+    for (uint32_t l = 0; l < p.levels; l++) {
+        if (threadIdx.x < n) hash_node(p.cols[l], p.ncols[l], n, prev, p.out[l], p.ncols[l] ? 1 : 2, threadIdx.x);
+        __syncthreads();
+        prev = p.out[l];
+        n >>= 1;
     }
-    poseidon2_permute(t);
-#pragma unroll
-    for (int w = 0; w < 8; w++) out[(uint64_t)w * n + i] = t[w].v;
 }
 
 static inline unsigned grid_for(uint64_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
@@ -126,8 +147,8 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d) {
         StageScope sc(e, ST_LEAF);
         uint32_t* leaf = (uint32_t*)e->dmalloc(hmax * 32);
         uint32_t nc = (uint32_t)groups[hmax].size();
-        row_hash_kernel<<<grid_for(hmax, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(group_dev[hmax], nc, hmax,
-                                                                                        nullptr, leaf, 0);
+        tree_level_kernel<<<grid_for(hmax, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(group_dev[hmax], nc, hmax,
+                                                                                          nullptr, leaf, 0);
         B2_CHECK_LAUNCH();
         e->launches[1]++;
         e->permutations += hmax * ((nc + 7) / 8);
@@ -137,19 +158,44 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d) {
     uint64_t h = hmax;
     while (h > 1) {
         uint64_t nh = h / 2;
+        if (nh <= TAIL_THREADS) {
+            // all remaining levels in one launch
+            StageScope sc(e, ST_COMPRESS);
+            TailParams tp{};
+            tp.prev0 = d->layers.back();
+            tp.n0 = nh;
+            uint32_t l = 0;
+            for (uint64_t m = nh; m >= 1; m >>= 1, l++) {
+                B2_REQUIRE(l < TAIL_MAX_LEVELS, B2S_ERR_INTERNAL, "mmcs: tail too deep");
+                auto it = groups.find(m);
+                tp.cols[l] = it != groups.end() ? group_dev[m] : nullptr;
+                tp.ncols[l] = it != groups.end() ? (uint32_t)it->second.size() : 0u;
+                tp.out[l] = (uint32_t*)e->dmalloc(m * 32);
+                d->layers.push_back(tp.out[l]);
+                d->layer_nodes.push_back(m);
+                e->permutations += m * (tp.ncols[l] ? (tp.ncols[l] + 7) / 8 + 2 : 1);
+                if (m == 1) { l++; break; }
+            }
+            tp.levels = l;
+            tree_tail_kernel<<<1, TAIL_THREADS, 0, e->stream>>>(tp);
+            B2_CHECK_LAUNCH();
+            e->launches[2]++;
+            break;
+        }
         uint32_t* next = (uint32_t*)e->dmalloc(nh * 32);
         auto it = groups.find(nh);
         if (it != groups.end()) {
             StageScope sc(e, ST_LEAF);
             uint32_t nc = (uint32_t)it->second.size();
-            row_hash_kernel<<<grid_for(nh, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(group_dev[nh], nc, nh,
-                                                                                          d->layers.back(), next, 1);
+            tree_level_kernel<<<grid_for(nh, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(group_dev[nh], nc, nh,
+                                                                                            d->layers.back(), next, 1);
             B2_CHECK_LAUNCH();
             e->launches[1]++;
             e->permutations += nh * ((nc + 7) / 8 + 2);
         } else {
             StageScope sc(e, ST_COMPRESS);
-            compress_kernel<<<grid_for(nh, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(d->layers.back(), next, nh);
+            tree_level_kernel<<<grid_for(nh, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(nullptr, 0, nh,
+                                                                                            d->layers.back(), next, 2);
             B2_CHECK_LAUNCH();
             e->launches[2]++;
             e->permutations += nh;

@@ -14,9 +14,10 @@
 namespace b2 {
 
 #if defined(__CUDACC__)
-static __constant__ uint32_t P2C_EXT_INIT[4][16] = B2_P2_EXT_INIT;
+// round constants: rows 0-3 initial full rounds, rows 4-7 terminal full rounds (one table so a single looped
+// code body serves all eight full rounds; indexed by the loop counter -> LDC with a register index)
+static __constant__ uint32_t P2C_EXT[8][16] = B2_P2_EXT_ALL;
 static __constant__ uint32_t P2C_PARTIAL[13] = B2_P2_PARTIAL;
-static __constant__ uint32_t P2C_EXT_TERM[4][16] = B2_P2_EXT_TERM;
 static __constant__ uint32_t P2C_DIAG[16] = B2_P2_DIAG;
 
 B2_D Fp sbox7(Fp x) {
@@ -51,7 +52,15 @@ B2_D void p2_external(Fp (&s)[16]) {
     for (int i = 0; i < 16; i++) s[i] += sums[i & 3];
 }
 
+// halve: x/2 mod p without a Montgomery product
+B2_D Fp fp_halve(Fp a) {
+    uint32_t odd = a.v & 1u;
+    return Fp::raw((a.v >> 1) + odd * ((P + 1) >> 1));
+}
+
 // internal layer: s_i <- sum(s) + d_i * s_i   with d = (-2, 1, 2, 1/2, 3, 4, -1/2, -3, -4, 2^-8, 1/4, 1/8, 2^-27, -2^-8, -1/16, -2^-27)
+// The small-integer and 1/2 multiples are done with additions/shifts on the ALU pipe (the fmaheavy pipe, which
+// carries the Montgomery products, is the busier one); the negative-power-of-two entries use Montgomery products.
 B2_D void p2_internal(Fp (&s)[16]) {
     Fp part = ((s[1] + s[2]) + (s[3] + s[4])) + ((s[5] + s[6]) + (s[7] + s[8])) +
               (((s[9] + s[10]) + (s[11] + s[12])) + ((s[13] + s[14]) + s[15]));
@@ -59,28 +68,41 @@ B2_D void p2_internal(Fp (&s)[16]) {
     s[0] = part - s[0];
     s[1] = full + s[1];
     s[2] = full + fp_double(s[2]);
+    {
+        Fp h3 = fp_halve(s[3]);
+        Fp d4 = fp_double(s[4]), d5 = fp_double(s[5]);
+        Fp h6 = fp_halve(s[6]);
+        Fp d7 = fp_double(s[7]), d8 = fp_double(s[8]);
+        s[3] = full + h3;
+        s[4] = full + (d4 + s[4]);
+        s[5] = full + fp_double(d5);
+        s[6] = full - h6;
+        s[7] = full - (d7 + s[7]);
+        s[8] = full - fp_double(d8);
+    }
 #pragma unroll
-    for (int i = 3; i < 16; i++) s[i] = full + s[i] * Fp::raw(P2C_DIAG[i]);
+    for (int i = 9; i < 16; i++) s[i] = full + s[i] * Fp::raw(P2C_DIAG[i]);
 }
 
+// The whole permutation as  E S0 E S1 E S2 E S3 E [P x 13] S4 E S5 E S6 E S7 E  with one code body per layer type
+// (E external layer, S_r add-constants + x^7 on all lanes, P partial round). Loops are kept rolled on purpose:
+// fully unrolled, one permutation is ~100 KB of SASS, which thrashes the instruction cache (ncu: stall
+// no_instruction dominant, profiles/r1a_ncu_full_summary.md); rolled it is ~9 KB.
 B2_D void poseidon2_permute(Fp (&s)[16]) {
-    p2_external(s);
-#pragma unroll
-    for (int r = 0; r < 4; r++) {
-#pragma unroll
-        for (int i = 0; i < 16; i++) s[i] = sbox7(s[i] + Fp::raw(P2C_EXT_INIT[r][i]));
+#pragma unroll 1
+    for (int r = 0; r < 9; r++) {
         p2_external(s);
-    }
+        if (r == 4) {
+#pragma unroll 1
+            for (int q = 0; q < 13; q++) {
+                s[0] = sbox7(s[0] + Fp::raw(P2C_PARTIAL[q]));
+                p2_internal(s);
+            }
+        }
+        if (r < 8) {
 #pragma unroll
-    for (int r = 0; r < 13; r++) {
-        s[0] = sbox7(s[0] + Fp::raw(P2C_PARTIAL[r]));
-        p2_internal(s);
-    }
-#pragma unroll
-    for (int r = 0; r < 4; r++) {
-#pragma unroll
-        for (int i = 0; i < 16; i++) s[i] = sbox7(s[i] + Fp::raw(P2C_EXT_TERM[r][i]));
-        p2_external(s);
+            for (int i = 0; i < 16; i++) s[i] = sbox7(s[i] + Fp::raw(P2C_EXT[r][i]));
+        }
     }
 }
 #endif  // __CUDACC__
