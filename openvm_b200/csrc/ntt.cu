@@ -1,4 +1,4 @@
-// BabyBear coset low-degree extension: inverse NTT -> coset scaling -> forward NTT with bit-reversed rows.
+// BabyBear coset low-degree extension: inverse NTT -> forward NTT on each coset, rows bit-reversed.
 //
 // Replaces (reference, external): the per-matrix part of Plonky3 `TwoAdicFriPcs::commit`
 // (p3-fri / p3-dft `Radix2DitParallel::coset_lde_batch`), reached from
@@ -6,359 +6,106 @@
 // in-tree: leaf i of an LDE of height 2^h is the evaluation at GENERATOR * w_h^{bitrev_h(i)}
 // (extensions/native/recursion/src/fri/two_adic_pcs.rs:178-186; domain: fri/domain.rs:142-154).
 //
-// Design (B200): a column of N = 2^n evaluations is transformed in at most three HBM passes per transform.
-// n is split into digits of <= 9 bits; each pass stages a D x T tile (8192 words) in shared memory with
-// >= 64-byte coalesced runs, runs the D-point transform as radix-16 register butterflies with shared-memory
-// exchanges, applies the inter-digit twiddle from a two-level table and stores coalesced.
-//   inverse:  A (strided)  ->  B (strided, in place)  ->  C (transposing; emits natural-order coefficients)
-//   forward:  F1 (strided; fused coset scaling s_j^i / N, one launch for all 2^b cosets)
-//             -> F2 (strided, in place) -> F3 (contiguous, in place); decimation-in-frequency, so the
-//             result lands in bit-reversed order with no separate permutation pass. Coset j of the
-//             2^b*N-point domain is exactly output block bitrev_b(j) (rows [blk*N, (blk+1)*N)).
+// Design (B200). On this part the transform is bound by the integer-multiply pipe, not by HBM: a Montgomery
+// product is three 4-cycle IMADs on fmaheavy (profiles/r1a_ncu_full_summary.md), so the kernels are built to
+// execute exactly one product per butterfly and nothing else:
+//   * every stage is a Cooley-Tukey butterfly (a, b) -> (a + z*b, a - z*b), natural-order input, bit-reversed
+//     output, with the stage twiddle AND the coset shift merged into one table entry z = Z[2^t + q]
+//     (t = depth, q = sub-problem): no inter-digit twiddle products, no separate coset-scaling product;
+//     the only extra product is the 1/N factor, applied once per coefficient;
+//   * tables: ZI (inverse, N words) and ZF (forward, one N-word table per coset), built on the device once per
+//     (log N, log_blowup, input shift) and cached in the engine; early depths (shared by all tiles) stay in L1,
+//     late depths stream through L2 with 8/16-byte vector loads;
+//   * passes: [strided]* -> contiguous for the inverse (coefficients land bit-reversed), then
+//     gather -> [strided]* -> contiguous for the forward transform of each coset. The gather pass reads the
+//     bit-reversed coefficients as contiguous runs and writes natural slots, so no separate permutation pass
+//     exists and the final output is in place in bit-reversed order. Coset j of the 2^b*N-point domain is
+//     output block bitrev_b(j).
+//   * strided / gather passes: 2^D x 32 tile in shared memory, a warp lane owns one of 32 adjacent positions,
+//     radix-16 register blocks, twiddle index uniform per warp; contiguous pass: one run of 2^D <= 8192 words
+//     per tile (several runs per block for small D), 1-in-32 padded shared memory, radix-16 register blocks.
 #include "common.cuh"
 
 namespace b2 {
 
-constexpr int NTT_THREADS = 256;
-constexpr int LOG_TILE = 13;  // words per tile
-constexpr int MAX_DIGIT = 9;
+constexpr int K1_THREADS = 256;
+constexpr int K1_MAX_D = 9;    // 2^9 x 32 words = 64 KB tile
+constexpr int K2_MAX_D = 13;   // 8192-word run
 
-// w_16^e and w_16^-e, e = 0..7, Montgomery form
-static __constant__ uint32_t W16_FWD[8];
-static __constant__ uint32_t W16_INV[8];
-
-struct TwoLevel {       // x^e = lo[e & ((1<<h1)-1)] * hi[e >> h1]
-    const uint32_t* lo;
-    const uint32_t* hi;
-    uint32_t h1;
+// ---- tables ---------------------------------------------------------------------------------------------
+struct TabParams {
+    uint32_t s[28];  // s[t] = base^(N / 2^(t+1))        (Montgomery)
+    uint32_t g[28];  // g[t] = generator of order 2^(t+1) (forward or inverse)
 };
-B2_D Fp two_level(const TwoLevel& t, uint32_t e) {
-    return Fp::raw(__ldg(t.lo + (e & ((1u << t.h1) - 1)))) * Fp::raw(__ldg(t.hi + (e >> t.h1)));
+
+__global__ void build_table_kernel(uint32_t* z, uint32_t n, TabParams p) {
+    uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n) return;
+    if (idx == 0) { z[0] = 0; return; }
+    const uint32_t t = 31 - __clz(idx);
+    const uint32_t q = idx - (1u << t);
+    const uint32_t e = t ? (__brev(q) >> (32 - t)) : 0u;
+    z[idx] = (Fp::raw(p.s[t]) * fp_pow(Fp::raw(p.g[t]), e)).v;
 }
 
-enum { MODE_STRIDED = 0, MODE_CONTIG = 1, MODE_TRANSPOSE = 2 };
-
-struct PassParams {
-    const uint32_t* in;
-    uint32_t* out;
-    uint64_t in_col_stride, out_col_stride;
-    uint32_t width;       // columns
-    uint32_t mode;
-    uint32_t logT;
-    uint32_t logL;        // strided: log2 of the run length below the digit; transpose: log2 E1 (middle digit)
-    uint32_t logE0;       // transpose: log2 of the leading digit (becomes the lowest coefficient digit)
-    uint32_t log_len;     // log2 of the per-column length covered by this launch
-    uint32_t out_brev;    // 1: frequency k stored at slot bitrev(k) (DIF order); 0: at slot k
-    uint32_t inverse;     // selects W16_INV
-    TwoLevel tw;          // root table of order 2^tw_logn (forward or inverse)
-    uint32_t tw_logn;
-    uint32_t tw_shift;    // strided: exponent = (lo*k) << tw_shift
-    uint32_t has_scale;   // multiply loaded element i (index in column, mod 2^sc_logn) by scale^i
-    TwoLevel sc;          // tables for coset blockIdx.z start at sc.lo + z*sc_lo_stride etc.
-    uint32_t sc_lo_stride, sc_hi_stride;
-    uint32_t log_blowup;  // out block of coset z is bitrev_b(z), block length 2^log_len
-};
-
-template <int R>
-B2_D void reg_ntt(Fp (&v)[1 << R], const uint32_t* __restrict__ w16) {
-    // decimation in frequency, natural in, bit-reversed out; twiddles w_{2^R}^x = w_16^{x * 16 / 2^R}
-#pragma unroll
-    for (int s = 0; s < R; s++) {
-        const int half = 1 << (R - 1 - s);
-#pragma unroll
-        for (int blk = 0; blk < (1 << R); blk += 2 * half) {
-#pragma unroll
-            for (int j = 0; j < half; j++) {
-                Fp u = v[blk + j], w = v[blk + j + half];
-                v[blk + j] = u + w;
-                const int e = (j << s) * (16 >> R);  // exponent of w_16
-                if (e == 0) {
-                    v[blk + j + half] = u - w;
-                } else {
-                    // (u - w + p) in (0, 2p): valid lazy input to the Montgomery product
-                    uint32_t d = u.v - w.v + P;
-                    v[blk + j + half] = Fp::raw(monty_reduce((uint64_t)d * w16[e]));
-                }
-            }
-        }
-    }
-}
-
-template <int LOG_D, int REM>
-struct Rounds {
-    static B2_D void run(uint32_t* x, const uint32_t* wd, uint32_t logT, uint32_t pitch, const uint32_t* w16) {
-        constexpr int R = REM >= 4 ? 4 : REM;
-        constexpr int SH = REM - R;
-        const uint32_t T = 1u << logT;
-        const uint32_t items = (1u << (LOG_D - R)) << logT;
-        for (uint32_t id = threadIdx.x; id < items; id += NTT_THREADS) {
-            uint32_t t = id & (T - 1);
-            uint32_t g = id >> logT;
-            uint32_t r = g & ((1u << SH) - 1);
-            uint32_t d0 = ((g >> SH) << (SH + R)) + r;
-            uint32_t* px = x + d0 * pitch + t;
-            Fp v[1 << R];
-#pragma unroll
-            for (int a = 0; a < (1 << R); a++) v[a] = Fp::raw(px[(a << SH) * pitch]);
-            reg_ntt<R>(v, w16);
-            if (SH > 0) {
-                // slot a holds sub-frequency ka = bitrev_R(a); twiddle w_{2^(SH+R)}^{r*ka}
-#pragma unroll
-                for (int a = 1; a < (1 << R); a++) {
-                    const uint32_t ka = __brev((uint32_t)a) >> (32 - R);
-                    v[a] = v[a] * Fp::raw(wd[(r * ka) << (LOG_D - SH - R)]);
-                }
-            }
-#pragma unroll
-            for (int a = 0; a < (1 << R); a++) px[(a << SH) * pitch] = v[a].v;
-        }
-        __syncthreads();
-        Rounds<LOG_D, SH>::run(x, wd, logT, pitch, w16);
-    }
-};
-template <int LOG_D>
-struct Rounds<LOG_D, 0> {
-    static B2_D void run(uint32_t*, const uint32_t*, uint32_t, uint32_t, const uint32_t*) {}
-};
-
-template <int LOG_D>
-__global__ void __launch_bounds__(NTT_THREADS) ntt_pass_kernel(PassParams p) {
-    extern __shared__ uint32_t sm[];
-    constexpr uint32_t D = 1u << LOG_D;
-    const uint32_t logT = p.logT, T = 1u << logT;
-    const uint32_t pitch = T == 1 ? 1 : T + 1;
-    uint32_t* x = sm;
-    uint32_t* wd = sm + D * pitch;
-    const uint32_t* w16 = p.inverse ? W16_INV : W16_FWD;
-    const uint32_t tid = threadIdx.x;
-
-    for (uint32_t e = tid; e < D; e += NTT_THREADS) wd[e] = two_level(p.tw, e << (p.tw_logn - LOG_D)).v;
-
-    // ---- tile coordinates ----
-    const uint64_t tile = blockIdx.x;
-    const uint32_t z = blockIdx.z;
-    uint64_t in_base = 0, out_base = 0;       // word offsets of element (d=0, t=0)
-    uint64_t in_sd = 1, in_st = 1, out_sd = 1, out_st = 1;
-    uint32_t lo0 = 0;                         // strided: index within the run of the tile's t = 0
-    uint64_t sub0 = 0, total_subs = 0;        // contiguous: first sub-array of the tile, count over all columns
-    const uint32_t logS = p.log_len - LOG_D;  // sub-arrays per column (contiguous mode)
-    if (p.mode == MODE_STRIDED) {
-        const uint32_t col = blockIdx.y;
-        const uint32_t chunks = 1u << (p.logL - logT);          // chunks of T per run
-        const uint64_t hi = tile >> (p.logL - logT);
-        lo0 = (uint32_t)(tile & (chunks - 1)) << logT;
-        uint64_t pos = (hi << (LOG_D + p.logL)) + lo0;
-        in_base = (uint64_t)col * p.in_col_stride + pos;
-        out_base = (uint64_t)col * p.out_col_stride + pos;
-        in_sd = out_sd = (uint64_t)1 << p.logL;
-    } else if (p.mode == MODE_TRANSPOSE) {
-        // in (i0, i1, d) -> out (k, i1, i0); tile = (chunk of T values of i0, i1)
-        const uint32_t col = blockIdx.y;
-        const uint32_t logE1 = p.logL;
-        const uint64_t i1 = tile & ((1u << logE1) - 1);
-        const uint64_t i0 = (tile >> logE1) << logT;
-        in_base = (uint64_t)col * p.in_col_stride + (i0 << (logE1 + LOG_D)) + (i1 << LOG_D);
-        in_st = (uint64_t)1 << (logE1 + LOG_D);
-        out_base = (uint64_t)col * p.out_col_stride + (i1 << p.logE0) + i0;
-        out_sd = (uint64_t)1 << (p.logE0 + logE1);
-    } else {
-        sub0 = tile << logT;
-        total_subs = (uint64_t)p.width << logS;
-    }
-    // coset z of the extended domain is output block bitrev_b(z)
-    const uint64_t blk_off = (p.has_scale && p.log_blowup) ? ((uint64_t)(__brev(z) >> (32 - p.log_blowup)) << p.log_len) : 0;
-    out_base += blk_off;
-    TwoLevel sc = p.sc;
-    if (p.has_scale) { sc.lo += (uint64_t)z * p.sc_lo_stride; sc.hi += (uint64_t)z * p.sc_hi_stride; }
-    const uint32_t len_mask = (p.log_len >= 32) ? 0xFFFFFFFFu : ((1u << p.log_len) - 1);
-
-    // ---- load ----
-    const uint32_t E = D << logT;
-    if (p.mode == MODE_STRIDED) {
-        for (uint32_t e = tid; e < E; e += NTT_THREADS) {
-            uint32_t t = e & (T - 1), d = e >> logT;
-            uint64_t off = (uint64_t)d * in_sd + t;
-            Fp v = Fp::raw(p.in[in_base + off]);
-            if (p.has_scale) {
-                uint32_t i = (uint32_t)(((tile >> (p.logL - logT)) << (LOG_D + p.logL)) + lo0 + off) & len_mask;
-                v = v * two_level(sc, i);
-            }
-            x[d * pitch + t] = v.v;
-        }
-    } else if (p.mode == MODE_TRANSPOSE) {
-        for (uint32_t e = tid; e < E; e += NTT_THREADS) {
-            uint32_t d = e & (D - 1), t = e >> LOG_D;
-            x[d * pitch + t] = p.in[in_base + (uint64_t)t * in_st + d];
-        }
-    } else {
-        for (uint32_t e = tid; e < E; e += NTT_THREADS) {
-            uint32_t d = e & (D - 1), t = e >> LOG_D;
-            uint64_t g = sub0 + t;
-            uint32_t v = 0;
-            if (g < total_subs) {
-                uint64_t col = g >> logS, sub = g & (((uint64_t)1 << logS) - 1);
-                uint64_t i = (sub << LOG_D) + d;
-                Fp f = Fp::raw(p.in[col * p.in_col_stride + i]);
-                if (p.has_scale) f = f * two_level(sc, (uint32_t)i & len_mask);
-                v = f.v;
-            }
-            x[d * pitch + t] = v;
-        }
-    }
-    __syncthreads();
-
-    Rounds<LOG_D, LOG_D>::run(x, wd, logT, pitch, w16);
-
-    // ---- store: smem position q holds frequency bitrev(q) ----
-    if (p.mode == MODE_CONTIG) {
-        for (uint32_t e = tid; e < E; e += NTT_THREADS) {
-            uint32_t slot = e & (D - 1), t = e >> LOG_D;
-            uint64_t g = sub0 + t;
-            if (g >= total_subs) continue;
-            uint32_t q = p.out_brev ? slot : (LOG_D ? (__brev(slot) >> (32 - LOG_D)) : 0);
-            uint64_t col = g >> logS, sub = g & (((uint64_t)1 << logS) - 1);
-            p.out[col * p.out_col_stride + blk_off + (sub << LOG_D) + slot] = x[q * pitch + t];
-        }
-    } else {
-        for (uint32_t e = tid; e < E; e += NTT_THREADS) {
-            uint32_t t = e & (T - 1), slot = e >> logT;
-            uint32_t b = LOG_D ? (__brev(slot) >> (32 - LOG_D)) : 0;
-            uint32_t q = p.out_brev ? slot : b;
-            uint32_t k = p.out_brev ? b : slot;
-            Fp v = Fp::raw(x[q * pitch + t]);
-            if (p.mode == MODE_STRIDED && k) v = v * two_level(p.tw, ((lo0 + t) * k) << p.tw_shift);
-            p.out[out_base + (uint64_t)slot * out_sd + (uint64_t)t * out_st] = v.v;
-        }
-    }
-}
-
-struct TwiddleSet {
+struct TwiddleSet {  // inverse table for one log size
     unsigned logn;
-    uint32_t h1;
-    uint32_t *fw_lo, *fw_hi, *inv_lo, *inv_hi;
-    size_t bytes;
+    uint32_t* zi;
+};
+struct ScaleSet {    // forward tables (one per coset) for (logn, log_blowup, shift_in)
+    unsigned logn, log_blowup;
+    uint32_t* zf;    // [2^b][N]
+    uint32_t ninv;   // 1/N, Montgomery
 };
 
-// scale tables for (logn, log_blowup, shift_in): for coset j: (GENERATOR/shift_in * w_M^j)^i / N
-struct ScaleSet {
-    uint32_t h1;
-    uint32_t* lo;  // [2^b][2^h1]
-    uint32_t* hi;  // [2^b][2^(logn-h1)]
-    size_t bytes;
-};
-
-static void build_two_level(Fp base, unsigned logn, uint32_t h1, Fp hi_factor, std::vector<uint32_t>& lo,
-                            std::vector<uint32_t>& hi) {
-    uint32_t nlo = 1u << h1, nhi = 1u << (logn - h1);
-    lo.resize(nlo);
-    hi.resize(nhi);
-    Fp a = Fp::one();
-    for (uint32_t i = 0; i < nlo; i++) { lo[i] = a.v; a *= base; }
-    Fp step = a;  // base^(2^h1)
-    Fp b = hi_factor;
-    for (uint32_t i = 0; i < nhi; i++) { hi[i] = b.v; b *= step; }
-}
-
-static uint32_t* upload(b2s_engine* e, const std::vector<uint32_t>& v) {
-    uint32_t* d = (uint32_t*)e->dmalloc(v.size() * 4);
-    B2_CUDA(cudaMemcpyAsync(d, v.data(), v.size() * 4, cudaMemcpyHostToDevice, e->stream));
-    B2_CUDA(cudaStreamSynchronize(e->stream));
-    return d;
+static void fill_table(b2s_engine* e, uint32_t* z, unsigned logn, Fp base, bool inverse) {
+    TabParams p{};
+    for (unsigned t = 0; t < logn; t++) {
+        Fp g = two_adic_generator(t + 1);
+        p.g[t] = (inverse ? fp_inv(g) : g).v;
+        p.s[t] = fp_pow(base, (uint64_t)1 << (logn - t - 1)).v;
+    }
+    const uint32_t n = 1u << logn;
+    build_table_kernel<<<(n + 255) / 256, 256, 0, e->stream>>>(z, n, p);
+    B2_CHECK_LAUNCH();
+    e->launches[3]++;
 }
 
 static TwiddleSet* get_twiddles(b2s_engine* e, unsigned logn) {
     auto it = e->twiddles.find(logn);
     if (it != e->twiddles.end()) return it->second;
-    if (e->twiddles.empty()) {
-        uint32_t f[8], g[8];
-        Fp w = two_adic_generator(4), wi = fp_inv(w), a = Fp::one(), b = Fp::one();
-        for (int i = 0; i < 8; i++) { f[i] = a.v; g[i] = b.v; a *= w; b *= wi; }
-        B2_CUDA(cudaMemcpyToSymbol(W16_FWD, f, sizeof(f)));
-        B2_CUDA(cudaMemcpyToSymbol(W16_INV, g, sizeof(g)));
-    }
     TwiddleSet* t = new TwiddleSet();
     t->logn = logn;
-    t->h1 = (logn + 1) / 2;
-    std::vector<uint32_t> lo, hi;
-    Fp w = two_adic_generator(logn);
-    build_two_level(w, logn, t->h1, Fp::one(), lo, hi);
-    t->fw_lo = upload(e, lo);
-    t->fw_hi = upload(e, hi);
-    build_two_level(fp_inv(w), logn, t->h1, Fp::one(), lo, hi);
-    t->inv_lo = upload(e, lo);
-    t->inv_hi = upload(e, hi);
-    t->bytes = (lo.size() + hi.size()) * 8;
+    t->zi = (uint32_t*)e->dmalloc((size_t)4 << logn);
+    fill_table(e, t->zi, logn, Fp::one(), true);
     e->twiddles[logn] = t;
     return t;
 }
 
 void free_twiddles(b2s_engine* e) {
     for (auto& kv : e->twiddles) {
-        TwiddleSet* t = kv.second;
-        size_t nlo = (size_t)4 << t->h1, nhi = (size_t)4 << (t->logn - t->h1);
-        e->dfree(t->fw_lo, nlo); e->dfree(t->fw_hi, nhi); e->dfree(t->inv_lo, nlo); e->dfree(t->inv_hi, nhi);
-        delete t;
+        e->dfree(kv.second->zi, (size_t)4 << kv.second->logn);
+        delete kv.second;
     }
     e->twiddles.clear();
 }
-
-template <int LOG_D>
-static void launch_pass_t(b2s_engine* e, const PassParams& p, dim3 grid) {
-    const uint32_t D = 1u << LOG_D, T = 1u << p.logT;
-    const uint32_t pitch = T == 1 ? 1 : T + 1;
-    size_t smem = (size_t)(D * pitch + D) * 4;
-    ntt_pass_kernel<LOG_D><<<grid, NTT_THREADS, smem, e->stream>>>(p);
-    B2_CHECK_LAUNCH();
-    e->launches[0]++;
-}
-
-static void launch_pass(b2s_engine* e, unsigned logD, const PassParams& p, dim3 grid) {
-    switch (logD) {
-        case 0: launch_pass_t<0>(e, p, grid); break;
-        case 1: launch_pass_t<1>(e, p, grid); break;
-        case 2: launch_pass_t<2>(e, p, grid); break;
-        case 3: launch_pass_t<3>(e, p, grid); break;
-        case 4: launch_pass_t<4>(e, p, grid); break;
-        case 5: launch_pass_t<5>(e, p, grid); break;
-        case 6: launch_pass_t<6>(e, p, grid); break;
-        case 7: launch_pass_t<7>(e, p, grid); break;
-        case 8: launch_pass_t<8>(e, p, grid); break;
-        case 9: launch_pass_t<9>(e, p, grid); break;
-        default: fail(B2S_ERR_INTERNAL, "ntt: unsupported digit size");
-    }
-}
-
-// split n into k = ceil(n/9) digits, as even as possible, largest first
-static std::vector<unsigned> split_digits(unsigned n) {
-    if (n == 0) return {0};
-    unsigned k = (n + MAX_DIGIT - 1) / MAX_DIGIT;
-    std::vector<unsigned> d(k, n / k);
-    for (unsigned i = 0; i < n % k; i++) d[i]++;
-    return d;
-}
-
 
 static ScaleSet* get_scales(b2s_engine* e, unsigned logn, unsigned log_blowup, Fp shift_in) {
     uint64_t key = ((uint64_t)logn << 40) | ((uint64_t)log_blowup << 32) | shift_in.v;
     auto it = e->scales.find(key);
     if (it != e->scales.end()) return it->second;
     ScaleSet* s = new ScaleSet();
-    s->h1 = (logn + 1) / 2;
-    const uint32_t B = 1u << log_blowup, nlo = 1u << s->h1, nhi = 1u << (logn - s->h1);
-    std::vector<uint32_t> lo_all((size_t)B * nlo), hi_all((size_t)B * nhi), lo, hi;
+    s->logn = logn;
+    s->log_blowup = log_blowup;
+    const uint32_t B = 1u << log_blowup;
+    s->zf = (uint32_t*)e->dmalloc(((size_t)4 << logn) * B);
     Fp base = Fp::raw(M_GENERATOR) * fp_inv(shift_in);
     Fp wm = two_adic_generator(logn + log_blowup);
-    Fp ninv = fp_inv(Fp::from_canonical((uint32_t)(((uint64_t)1 << logn) % P)));
-    Fp sj = base;
     for (uint32_t j = 0; j < B; j++) {
-        build_two_level(sj, logn, s->h1, ninv, lo, hi);
-        memcpy(&lo_all[(size_t)j * nlo], lo.data(), (size_t)nlo * 4);
-        memcpy(&hi_all[(size_t)j * nhi], hi.data(), (size_t)nhi * 4);
-        sj *= wm;
+        fill_table(e, s->zf + ((size_t)j << logn), logn, base, false);
+        base *= wm;
     }
-    s->lo = upload(e, lo_all);
-    s->hi = upload(e, hi_all);
-    s->bytes = (lo_all.size() + hi_all.size()) * 4;
+    s->ninv = fp_inv(Fp::from_canonical((uint32_t)(((uint64_t)1 << logn) % P))).v;
     e->scales[key] = s;
     return s;
 }
@@ -366,17 +113,355 @@ static ScaleSet* get_scales(b2s_engine* e, unsigned logn, unsigned log_blowup, F
 void free_scales(b2s_engine* e) {
     for (auto& kv : e->scales) {
         ScaleSet* s = kv.second;
-        unsigned logn = (unsigned)(kv.first >> 40), lb = (unsigned)((kv.first >> 32) & 0xFF);
-        e->dfree(s->lo, ((size_t)4 << s->h1) << lb);
-        e->dfree(s->hi, ((size_t)4 << (logn - s->h1)) << lb);
+        e->dfree(s->zf, ((size_t)4 << s->logn) << s->log_blowup);
         delete s;
     }
     e->scales.clear();
 }
 
-static uint32_t pick_logT(unsigned logD, unsigned log_run) {
-    unsigned t = LOG_TILE - logD;
-    return t < log_run ? t : log_run;
+// ---- register butterfly block -----------------------------------------------------------------------------
+// 2^E consecutive table words starting at z (aligned to 4 * 2^E bytes)
+template <int E>
+B2_D void load_tw(const uint32_t* __restrict__ z, uint32_t (&w)[1 << E]) {
+    if constexpr (E == 0) {
+        w[0] = __ldg(z);
+    } else if constexpr (E == 1) {
+        uint2 a = __ldg(reinterpret_cast<const uint2*>(z));
+        w[0] = a.x; w[1] = a.y;
+    } else if constexpr (E == 2) {
+        uint4 a = __ldg(reinterpret_cast<const uint4*>(z));
+        w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w;
+    } else {
+        uint4 a = __ldg(reinterpret_cast<const uint4*>(z));
+        uint4 b = __ldg(reinterpret_cast<const uint4*>(z) + 1);
+        w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w;
+        w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
+    }
+}
+
+template <int R, int E>
+B2_D void ct_stage(Fp (&v)[1 << R], const uint32_t* __restrict__ z, uint32_t idx0) {
+    constexpr int half = 1 << (R - 1 - E);
+    uint32_t w[1 << E];
+    load_tw<E>(z + ((size_t)idx0 << E), w);
+#pragma unroll
+    for (int j = 0; j < (1 << E); j++) {
+#pragma unroll
+        for (int k = 0; k < half; k++) {
+            const int ia = j * 2 * half + k, ib = ia + half;
+            Fp t = v[ib] * Fp::raw(w[j]);
+            Fp a = v[ia];
+            v[ia] = a + t;
+            v[ib] = a - t;
+        }
+    }
+}
+
+// R depths on 2^R values; depth e pairs indices differing in bit R-1-e; idx0 = 2^depth + sub-problem
+template <int R>
+B2_D void ct_block(Fp (&v)[1 << R], const uint32_t* __restrict__ z, uint32_t idx0) {
+    ct_stage<R, 0>(v, z, idx0);
+    if constexpr (R >= 2) ct_stage<R, 1>(v, z, idx0);
+    if constexpr (R >= 3) ct_stage<R, 2>(v, z, idx0);
+    if constexpr (R >= 4) ct_stage<R, 3>(v, z, idx0);
+}
+
+template <int R>
+B2_D constexpr int brev_c(int m) {
+    int r = 0;
+    for (int i = 0; i < R; i++) r |= ((m >> i) & 1) << (R - 1 - i);
+    return r;
+}
+
+constexpr int first_radix(int D) { return D == 0 ? 0 : ((D & 3) ? (D & 3) : 4); }
+
+// ---- strided / gather pass ----------------------------------------------------------------------------------
+struct PassParams {
+    const uint32_t* in;
+    uint32_t* out;
+    uint64_t in_col_stride, out_col_stride;
+    const uint32_t* z;        // table; coset c uses z + c * 2^log_len
+    uint32_t width;           // columns covered by the launch (contiguous pass: for the run -> column map)
+    uint32_t log_len;         // log2 of the transform length n
+    uint32_t t0;              // global depth of the first stage of this pass
+    uint32_t log_blowup;      // coset c writes (and, when in_block, reads) block bitrev_b(c) of 2^log_len words
+    uint32_t coset;           // 1: blockIdx.z is the coset index
+    uint32_t in_block;        // 1: the input is offset by the coset block as well (in-place passes on the LDE)
+    uint32_t scale;           // != 0: multiply loaded words by this (1/N; first forward pass)
+    uint32_t reverse_load;    // contiguous pass with D == log_len: word p of the run is stored at slot bitrev_D(p)
+};
+
+template <int D, int U, bool GATHER>
+struct K1Rounds {
+    static B2_D void run(uint32_t* x, const uint32_t* __restrict__ z, uint32_t sub0) {
+        constexpr int R = (U == 0) ? first_radix(D) : 4;
+        constexpr int PITCH = GATHER ? 33 : 32;
+        constexpr uint32_t NBLK = 1u << (D - R);
+        const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        for (uint32_t blk = warp; blk < NBLK; blk += K1_THREADS / 32) {
+            Fp v[1 << R];
+            uint32_t row0, rs, idx0;
+            if constexpr (GATHER) {
+                // depths U..U+R-1 pair slots at distance 2^U, 2^(U+1), ...: slot m of the block is register bitrev_R(m)
+                const uint32_t lo = blk & ((1u << U) - 1), hi = blk >> U;
+                row0 = (hi << (R + U)) + lo;
+                rs = 1u << U;
+                idx0 = (1u << U) + (U ? (__brev(lo) >> (32 - U)) : 0u);
+#pragma unroll
+                for (int m = 0; m < (1 << R); m++) v[brev_c<R>(m)] = Fp::raw(x[(row0 + m * rs) * PITCH + lane]);
+            } else {
+                constexpr int LS = D - U - R;  // log2 of the row stride inside a block
+                const uint32_t lo = blk & ((1u << LS) - 1), hi = blk >> LS;
+                row0 = (hi << (R + LS)) + lo;
+                rs = 1u << LS;
+                idx0 = (sub0 << U) + hi;
+#pragma unroll
+                for (int m = 0; m < (1 << R); m++) v[m] = Fp::raw(x[(row0 + m * rs) * PITCH + lane]);
+            }
+            ct_block<R>(v, z, idx0);
+            if constexpr (GATHER) {
+#pragma unroll
+                for (int m = 0; m < (1 << R); m++) x[(row0 + m * rs) * PITCH + lane] = v[brev_c<R>(m)].v;
+            } else {
+#pragma unroll
+                for (int m = 0; m < (1 << R); m++) x[(row0 + m * rs) * PITCH + lane] = v[m].v;
+            }
+        }
+        __syncthreads();
+        K1Rounds<D, U + R, GATHER>::run(x, z, sub0);
+    }
+};
+template <int D, bool GATHER>
+struct K1Rounds<D, D, GATHER> {
+    static B2_D void run(uint32_t*, const uint32_t* __restrict__, uint32_t) {}
+};
+
+// Tile: rows r in [0, 2^D) at stride 2^(n - t0 - D) inside sub-problem `top` of depth t0, 32 adjacent positions.
+// GATHER (first forward pass, t0 = 0): the input holds coefficient i at slot bitrev_n(i); row r / lane t of the tile
+// is read from run bitrev_{n-D}(32*chunk + t), word r, and the result of slot r goes to natural row bitrev_D(r).
+template <int D, bool GATHER>
+__global__ void __launch_bounds__(K1_THREADS) ntt_strided_kernel(PassParams p) {
+    extern __shared__ uint32_t x[];
+    constexpr int PITCH = GATHER ? 33 : 32;
+    const uint32_t n = p.log_len;
+    const uint32_t low_bits = n - p.t0 - D;            // >= 5
+    const uint32_t chunk = blockIdx.x & ((1u << (low_bits - 5)) - 1);
+    const uint32_t top = blockIdx.x >> (low_bits - 5);
+    const uint32_t col = blockIdx.y;
+    const uint32_t cz = p.coset ? blockIdx.z : 0;
+    const uint64_t blk_off = p.coset && p.log_blowup ? ((uint64_t)(__brev(cz) >> (32 - p.log_blowup)) << n) : 0;
+    const uint32_t* __restrict__ z = p.z + ((size_t)cz << n);
+    const uint32_t tid = threadIdx.x;
+    const uint32_t* in = p.in + (uint64_t)col * p.in_col_stride + (p.in_block ? blk_off : 0);
+    uint32_t* out = p.out + (uint64_t)col * p.out_col_stride + blk_off;
+
+    if constexpr (GATHER) {
+        const Fp sc = Fp::raw(p.scale);
+        for (uint32_t e = tid; e < (32u << D); e += K1_THREADS) {
+            const uint32_t r = e & ((1u << D) - 1), t = e >> D;
+            const uint32_t ilo = (chunk << 5) + t;
+            const uint64_t run = (uint64_t)(__brev(ilo) >> (32 - low_bits)) << D;
+            x[r * PITCH + t] = (Fp::raw(in[run + r]) * sc).v;
+        }
+    } else {
+        const uint64_t base = ((uint64_t)top << (n - p.t0)) + ((uint64_t)chunk << 5);
+        for (uint32_t e = tid; e < (32u << D); e += K1_THREADS) {
+            const uint32_t t = e & 31, r = e >> 5;
+            x[r * PITCH + t] = in[base + ((uint64_t)r << low_bits) + t];
+        }
+    }
+    __syncthreads();
+    K1Rounds<D, 0, GATHER>::run(x, z, (1u << p.t0) + top);
+    if constexpr (GATHER) {
+        const uint64_t base = (uint64_t)chunk << 5;
+        for (uint32_t e = tid; e < (32u << D); e += K1_THREADS) {
+            const uint32_t t = e & 31, r = e >> 5;
+            const uint32_t row = D ? (__brev(r) >> (32 - D)) : 0u;
+            out[base + ((uint64_t)row << low_bits) + t] = x[r * PITCH + t];
+        }
+    } else {
+        const uint64_t base = ((uint64_t)top << (n - p.t0)) + ((uint64_t)chunk << 5);
+        for (uint32_t e = tid; e < (32u << D); e += K1_THREADS) {
+            const uint32_t t = e & 31, r = e >> 5;
+            out[base + ((uint64_t)r << low_bits) + t] = x[r * PITCH + t];
+        }
+    }
+}
+
+// ---- contiguous pass ------------------------------------------------------------------------------------------
+template <int D>
+struct K2Cfg {
+    static constexpr int TPR = D >= 4 ? (1 << (D - 4)) : 1;          // threads per run
+    static constexpr int THREADS = TPR > 256 ? TPR : 256;
+    static constexpr int RPC = THREADS / TPR;                          // runs per block
+    static constexpr int PITCH = (1 << D) + (D >= 5 ? (1 << (D - 5)) : 1);
+};
+B2_D uint32_t phys(uint32_t l) { return l + (l >> 5); }
+template <int LS, int R>
+B2_D constexpr int pad_off(int m) {
+    return (m << LS) + (LS >= 5 ? (m << (LS >= 5 ? LS - 5 : 0)) : (LS + R >= 5 ? (m >> (LS >= 5 ? 0 : 5 - LS)) : 0));
+}
+
+template <int D, int U>
+struct K2Rounds {
+    static B2_D void run(uint32_t* xr, const uint32_t* __restrict__ z, uint32_t sub0, uint32_t tr, bool live) {
+        constexpr int R = (U == 0) ? first_radix(D) : 4;
+        constexpr int LS = D - U - R;
+        constexpr uint32_t NBLK = 1u << (D - R);
+        if (live) {
+            for (uint32_t blk = tr; blk < NBLK; blk += K2Cfg<D>::TPR) {
+                const uint32_t lo = blk & ((1u << LS) - 1);
+                uint32_t hi = blk >> LS;
+                // row stride 16: take lane bit 4 from hi bit 1 so that the 32 lanes fall into 32 different banks
+                if (LS == 4 && U >= 2) hi = (hi & ~3u) | ((hi & 1u) << 1) | ((hi >> 1) & 1u);
+                const uint32_t l0 = (hi << (R + LS)) + lo;
+                // phys(l0 + (m << LS)) = phys(l0) + a compile-time offset: bits [LS, LS+R) of l0 are zero
+                uint32_t* xb = xr + phys(l0);
+                Fp v[1 << R];
+#pragma unroll
+                for (int m = 0; m < (1 << R); m++) v[m] = Fp::raw(xb[pad_off<LS, R>(m)]);
+                ct_block<R>(v, z, (sub0 << U) + hi);
+#pragma unroll
+                for (int m = 0; m < (1 << R); m++) xb[pad_off<LS, R>(m)] = v[m].v;
+            }
+        }
+        __syncthreads();
+        K2Rounds<D, U + R>::run(xr, z, sub0, tr, live);
+    }
+};
+template <int D>
+struct K2Rounds<D, D> {
+    static B2_D void run(uint32_t*, const uint32_t* __restrict__, uint32_t, uint32_t, bool) {}
+};
+
+// One run = 2^D consecutive words of a column = sub-problem `rho` of depth t0 = n - D. Runs are numbered across
+// the columns of the launch, so tiny heights still fill a block.
+template <int D>
+__global__ void __launch_bounds__(K2Cfg<D>::THREADS) ntt_contig_kernel(PassParams p) {
+    extern __shared__ uint32_t x[];
+    using C = K2Cfg<D>;
+    const uint32_t n = p.log_len;
+    const uint32_t log_rpc = n - D;  // runs per column
+    const uint64_t total_runs = (uint64_t)p.width << log_rpc;
+    const uint32_t cz = p.coset ? blockIdx.z : 0;
+    const uint64_t blk_off = p.coset && p.log_blowup ? ((uint64_t)(__brev(cz) >> (32 - p.log_blowup)) << n) : 0;
+    const uint64_t in_off = p.in_block ? blk_off : 0;
+    const uint32_t* __restrict__ z = p.z + ((size_t)cz << n);
+    const uint32_t tid = threadIdx.x;
+    const uint64_t run0 = (uint64_t)blockIdx.x * C::RPC;
+    const Fp sc = Fp::raw(p.scale);
+
+    for (uint32_t e = tid; e < ((uint32_t)C::RPC << D); e += C::THREADS) {
+        const uint32_t rs = e >> D, w = e & ((1u << D) - 1);
+        const uint64_t g = run0 + rs;
+        if (g >= total_runs) break;
+        const uint64_t col = g >> log_rpc, rho = g & (((uint64_t)1 << log_rpc) - 1);
+        Fp v = Fp::raw(p.in[col * p.in_col_stride + in_off + (rho << D) + w]);
+        if (p.scale) v = v * sc;
+        const uint32_t slot = (p.reverse_load && D) ? (__brev(w) >> (32 - D)) : w;
+        x[rs * C::PITCH + phys(slot)] = v.v;
+    }
+    __syncthreads();
+    {
+        const uint32_t rs = tid / C::TPR, tr = tid % C::TPR;
+        const uint64_t g = run0 + rs;
+        const uint32_t rho = (uint32_t)(g & (((uint64_t)1 << log_rpc) - 1));
+        K2Rounds<D, 0>::run(x + rs * C::PITCH, z, (1u << p.t0) + rho, tr, g < total_runs);
+    }
+    for (uint32_t e = tid; e < ((uint32_t)C::RPC << D); e += C::THREADS) {
+        const uint32_t rs = e >> D, w = e & ((1u << D) - 1);
+        const uint64_t g = run0 + rs;
+        if (g >= total_runs) break;
+        const uint64_t col = g >> log_rpc, rho = g & (((uint64_t)1 << log_rpc) - 1);
+        p.out[col * p.out_col_stride + blk_off + (rho << D) + w] = x[rs * C::PITCH + phys(w)];
+    }
+}
+
+// height-1 matrices: the polynomial is the constant; every extended row equals the single input row
+__global__ void replicate_kernel(const uint32_t* in, uint64_t in_col_stride, uint32_t* out, uint64_t out_col_stride,
+                                 uint32_t width, uint32_t rows) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= width * rows) return;
+    uint32_t c = i / rows, r = i % rows;
+    out[(uint64_t)c * out_col_stride + r] = in[(uint64_t)c * in_col_stride];
+}
+
+// ---- host side --------------------------------------------------------------------------------------------------
+template <int D, bool GATHER>
+static void launch_strided_t(b2s_engine* e, const PassParams& p, dim3 grid) {
+    constexpr size_t smem = ((size_t)1 << D) * (GATHER ? 33 : 32) * 4;
+    static bool configured[64] = {};  // per device
+    if (smem > 48 * 1024 && !configured[e->device & 63]) {
+        B2_CUDA(cudaFuncSetAttribute(ntt_strided_kernel<D, GATHER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[e->device & 63] = true;
+    }
+    ntt_strided_kernel<D, GATHER><<<grid, K1_THREADS, smem, e->stream>>>(p);
+    B2_CHECK_LAUNCH();
+    e->launches[0]++;
+}
+template <bool GATHER>
+static void launch_strided(b2s_engine* e, unsigned D, const PassParams& p, dim3 grid) {
+    switch (D) {
+        case 1: launch_strided_t<1, GATHER>(e, p, grid); break;
+        case 2: launch_strided_t<2, GATHER>(e, p, grid); break;
+        case 3: launch_strided_t<3, GATHER>(e, p, grid); break;
+        case 4: launch_strided_t<4, GATHER>(e, p, grid); break;
+        case 5: launch_strided_t<5, GATHER>(e, p, grid); break;
+        case 6: launch_strided_t<6, GATHER>(e, p, grid); break;
+        case 7: launch_strided_t<7, GATHER>(e, p, grid); break;
+        case 8: launch_strided_t<8, GATHER>(e, p, grid); break;
+        case 9: launch_strided_t<9, GATHER>(e, p, grid); break;
+        default: fail(B2S_ERR_INTERNAL, "ntt: unsupported strided digit");
+    }
+}
+template <int D>
+static void launch_contig_t(b2s_engine* e, const PassParams& p, unsigned cosets) {
+    using C = K2Cfg<D>;
+    const uint64_t total_runs = (uint64_t)p.width << (p.log_len - D);
+    const uint64_t blocks = (total_runs + C::RPC - 1) / C::RPC;
+    B2_REQUIRE(blocks <= 0x7FFFFFFFull, B2S_ERR_SHAPE, "ntt: too many runs in one launch");
+    ntt_contig_kernel<D><<<dim3((unsigned)blocks, 1, cosets), C::THREADS, (size_t)C::RPC * C::PITCH * 4, e->stream>>>(p);
+    B2_CHECK_LAUNCH();
+    e->launches[0]++;
+}
+static void launch_contig(b2s_engine* e, unsigned D, const PassParams& p, unsigned cosets) {
+    switch (D) {
+        case 1: launch_contig_t<1>(e, p, cosets); break;
+        case 2: launch_contig_t<2>(e, p, cosets); break;
+        case 3: launch_contig_t<3>(e, p, cosets); break;
+        case 4: launch_contig_t<4>(e, p, cosets); break;
+        case 5: launch_contig_t<5>(e, p, cosets); break;
+        case 6: launch_contig_t<6>(e, p, cosets); break;
+        case 7: launch_contig_t<7>(e, p, cosets); break;
+        case 8: launch_contig_t<8>(e, p, cosets); break;
+        case 9: launch_contig_t<9>(e, p, cosets); break;
+        case 10: launch_contig_t<10>(e, p, cosets); break;
+        case 11: launch_contig_t<11>(e, p, cosets); break;
+        case 12: launch_contig_t<12>(e, p, cosets); break;
+        case 13: launch_contig_t<13>(e, p, cosets); break;
+        default: fail(B2S_ERR_INTERNAL, "ntt: unsupported contiguous digit");
+    }
+}
+
+// split the n depths into strided digits (<= 9 bits, top of the index) and one contiguous digit (<= 13 bits)
+struct Plan {
+    std::vector<unsigned> strided;
+    unsigned contig;
+};
+static Plan make_plan(unsigned n) {
+    Plan pl;
+    if (n <= 12) {
+        pl.contig = n;
+    } else if (n <= 22) {
+        unsigned d1 = std::min<unsigned>(K1_MAX_D, n / 2);
+        pl.strided = {d1};
+        pl.contig = n - d1;
+    } else {
+        unsigned rest = n - 12;
+        pl.strided = {(rest + 1) / 2, rest / 2};
+        pl.contig = 12;
+    }
+    return pl;
 }
 
 // LDE of `width` columns: in = evaluations over shift_in*H_N, natural order (column stride in_col_stride);
@@ -387,89 +472,78 @@ void lde_columns(b2s_engine* e, const uint32_t* in, uint64_t in_col_stride, unsi
     if (width == 0) return;
     const uint64_t N = (uint64_t)1 << logn;
     const uint32_t B = 1u << log_blowup;
+    if (logn == 0) {
+        for (uint64_t c0 = 0; c0 < width; c0 += 1u << 20) {
+            uint32_t g = (uint32_t)std::min<uint64_t>(width - c0, 1u << 20);
+            replicate_kernel<<<(g * B + 255) / 256, 256, 0, e->stream>>>(in + c0 * in_col_stride, in_col_stride,
+                                                                         out + c0 * out_col_stride, out_col_stride, g, B);
+            B2_CHECK_LAUNCH();
+            e->launches[0]++;
+        }
+        return;
+    }
     TwiddleSet* tw = get_twiddles(e, logn);
     ScaleSet* sc = get_scales(e, logn, log_blowup, shift_in);
-    std::vector<unsigned> dg = split_digits(logn);
-    const size_t k = dg.size();
-    TwoLevel tw_f{tw->fw_lo, tw->fw_hi, tw->h1}, tw_i{tw->inv_lo, tw->inv_hi, tw->h1};
+    const Plan pl = make_plan(logn);
 
-    // column group size: bounded workspace (two N-word buffers per column in flight)
-    uint64_t group_elems = (uint64_t)1 << 25;
+    // column group: bounded coefficient workspace (256 MiB), large enough that every launch fills the chip several
+    // times over (the passes are multiply-bound, not HBM-bound, so L2 residency of the group does not matter)
+    uint64_t group_elems = (uint64_t)1 << 26;
     if (const char* env = getenv("B2S_LDE_GROUP_ELEMS")) group_elems = strtoull(env, nullptr, 10);
     uint64_t G = group_elems / N;
     if (G < 1) G = 1;
     if (G > width) G = width;
     if (G > 65535) G = 65535;
-    uint32_t* ws1 = k > 1 ? (uint32_t*)e->dmalloc(G * N * 4) : nullptr;
     uint32_t* coef = (uint32_t*)e->dmalloc(G * N * 4);
 
     for (uint64_t c0 = 0; c0 < width; c0 += G) {
         const uint32_t g = (uint32_t)std::min<uint64_t>(G, width - c0);
         const uint32_t* gin = in + c0 * in_col_stride;
         uint32_t* gout = out + c0 * out_col_stride;
+        // ---------------- inverse: evaluations (natural) -> coefficients at bit-reversed slots, unscaled
         PassParams p{};
         p.width = g;
-        p.tw_logn = logn;
-        // ---------------- inverse: evaluations -> natural-order coefficients (unscaled; 1/N is in the scale table)
-        p.inverse = 1;
-        p.tw = tw_i;
-        p.has_scale = 0;
-        p.out_brev = 0;
-        if (k == 1) {
-            p.mode = MODE_CONTIG; p.in = gin; p.out = coef; p.in_col_stride = in_col_stride; p.out_col_stride = N;
-            p.log_len = logn; p.logT = LOG_TILE - dg[0];
-            uint64_t subs = (uint64_t)g;  // one sub-array per column
-            launch_pass(e, dg[0], p, dim3((unsigned)((subs + (1u << p.logT) - 1) >> p.logT), 1, 1));
-        } else {
-            // pass A
-            p.mode = MODE_STRIDED; p.in = gin; p.out = ws1; p.in_col_stride = in_col_stride; p.out_col_stride = N;
-            p.log_len = logn; p.logL = logn - dg[0]; p.logT = pick_logT(dg[0], p.logL); p.tw_shift = 0;
-            launch_pass(e, dg[0], p, dim3((unsigned)(N >> (dg[0] + p.logT)), g, 1));
-            if (k == 3) {
-                p.in = ws1; p.in_col_stride = N;
-                p.logL = dg[2]; p.logT = pick_logT(dg[1], p.logL); p.tw_shift = dg[0];
-                launch_pass(e, dg[1], p, dim3((unsigned)(N >> (dg[1] + p.logT)), g, 1));
-            }
-            // pass C
-            p.mode = MODE_TRANSPOSE; p.in = ws1; p.out = coef; p.in_col_stride = N; p.out_col_stride = N;
-            p.logE0 = dg[0]; p.logL = (k == 3) ? dg[1] : 0;
-            p.logT = pick_logT(dg[k - 1], dg[0]);
-            launch_pass(e, dg[k - 1], p, dim3((unsigned)(N >> (dg[k - 1] + p.logT)), g, 1));
+        p.log_len = logn;
+        p.z = tw->zi;
+        p.in = gin; p.in_col_stride = in_col_stride;
+        p.out = coef; p.out_col_stride = N;
+        unsigned t0 = 0;
+        for (unsigned d : pl.strided) {
+            p.t0 = t0;
+            launch_strided<false>(e, d, p, dim3((unsigned)(N >> (d + 5)), g, 1));
+            p.in = coef; p.in_col_stride = N;
+            t0 += d;
         }
-        // ---------------- forward on each coset: digits in reverse order
+        p.t0 = t0;
+        launch_contig(e, pl.contig, p, 1);
+        // ---------------- forward on every coset: coefficients -> bit-reversed evaluations, block bitrev_b(coset)
         p = PassParams{};
         p.width = g;
-        p.tw_logn = logn;
-        p.inverse = 0;
-        p.tw = tw_f;
-        p.out_brev = 1;
-        p.has_scale = 1;
-        p.sc = TwoLevel{sc->lo, sc->hi, sc->h1};
-        p.sc_lo_stride = 1u << sc->h1;
-        p.sc_hi_stride = 1u << (logn - sc->h1);
-        p.log_blowup = log_blowup;
-        p.in = coef; p.in_col_stride = N; p.out = gout; p.out_col_stride = out_col_stride;
         p.log_len = logn;
-        if (k == 1) {
-            p.mode = MODE_CONTIG; p.logT = LOG_TILE - dg[0];
-            launch_pass(e, dg[0], p, dim3((unsigned)(((uint64_t)g + (1u << p.logT) - 1) >> p.logT), 1, B));
+        p.z = sc->zf;
+        p.log_blowup = log_blowup;
+        p.coset = 1;
+        p.in = coef; p.in_col_stride = N;
+        p.out = gout; p.out_col_stride = out_col_stride;
+        p.scale = sc->ninv;
+        if (pl.strided.empty()) {
+            p.t0 = 0;
+            p.reverse_load = 1;
+            launch_contig(e, pl.contig, p, B);
         } else {
-            const unsigned f0 = dg[k - 1];
-            p.mode = MODE_STRIDED; p.logL = logn - f0; p.logT = pick_logT(f0, p.logL); p.tw_shift = 0;
-            launch_pass(e, f0, p, dim3((unsigned)(N >> (f0 + p.logT)), g, B));
-            // remaining passes run in place over the whole extended column (2^b blocks of N)
-            p.has_scale = 0; p.in = gout; p.in_col_stride = out_col_stride; p.log_len = logn + log_blowup;
-            const uint64_t M = N << log_blowup;
-            if (k == 3) {
-                p.logL = dg[0]; p.logT = pick_logT(dg[1], p.logL); p.tw_shift = f0;
-                launch_pass(e, dg[1], p, dim3((unsigned)(M >> (dg[1] + p.logT)), g, 1));
+            p.t0 = 0;
+            launch_strided<true>(e, pl.strided[0], p, dim3((unsigned)(N >> (pl.strided[0] + 5)), g, B));
+            p.in = gout; p.in_col_stride = out_col_stride; p.in_block = 1; p.scale = 0;
+            t0 = pl.strided[0];
+            for (size_t i = 1; i < pl.strided.size(); i++) {
+                p.t0 = t0;
+                launch_strided<false>(e, pl.strided[i], p, dim3((unsigned)(N >> (pl.strided[i] + 5)), g, B));
+                t0 += pl.strided[i];
             }
-            p.mode = MODE_CONTIG; p.logT = LOG_TILE - dg[0];
-            uint64_t subs = (uint64_t)g << (logn + log_blowup - dg[0]);
-            launch_pass(e, dg[0], p, dim3((unsigned)((subs + (1u << p.logT) - 1) >> p.logT), 1, 1));
+            p.t0 = t0;
+            launch_contig(e, pl.contig, p, B);
         }
     }
-    if (ws1) e->dfree(ws1, G * N * 4);
     e->dfree(coef, G * N * 4);
 }
 
