@@ -140,3 +140,73 @@ void orc_fill_synthetic(uint32_t* out, uint64_t height, uint64_t width, uint64_t
 }
 
 }  // extern "C"
+
+// ---- STARK prove / verify (oracle/stark.hpp, oracle/stark_verify.hpp) -------------------------------------
+#include "stark_verify.hpp"
+static std::string g_orc_error;
+extern "C" {
+const char* orc_last_error() { return g_orc_error.c_str(); }
+void orc_free(void* p) { free(p); }
+
+// mats: for every AIR in order, its cached main partitions then (if the key gives it a common main) the common
+// main; column-major canonical words, `heights[i]` rows for AIR i. Returns 0 and a malloc'ed proof on success.
+int orc_stark_prove(const uint32_t* key_words, size_t key_n, size_t n_airs, const uint32_t* air_ids,
+                    const uint32_t* const* mats, const uint64_t* heights, const uint32_t* const* pvs,
+                    uint32_t log_blowup, uint32_t num_queries, uint32_t pow_bits, int threads, uint8_t** proof_out,
+                    size_t* len_out) {
+    try {
+        KeyBlob key = parse_key(key_words, key_n);
+        std::vector<AirInput> airs(n_airs);
+        size_t mi = 0;
+        for (size_t i = 0; i < n_airs; i++) {
+            AirInput& a = airs[i];
+            a.air_id = air_ids[i];
+            if (a.air_id >= key.airs.size()) throw std::runtime_error("air_id out of range");
+            const AirKey& k = key.airs[a.air_id];
+            auto load = [&](uint32_t w) {
+                ColMatrix m(heights[i], w);
+                const F* src = reinterpret_cast<const F*>(mats[mi++]);
+                std::copy(src, src + m.d.size(), m.d.begin());
+                return m;
+            };
+            for (uint32_t w : k.cached_widths) a.cached.push_back(load(w));
+            if (k.width_common) a.common = load(k.width_common);
+            for (uint32_t j = 0; j < k.num_pv; j++) a.public_values.push_back(F(pvs[i][j]));
+        }
+        Proof p = stark_prove(key, airs, FriParams{log_blowup, num_queries, pow_bits}, threads);
+        std::vector<uint8_t> bytes = encode_proof(p);
+        *proof_out = (uint8_t*)malloc(bytes.size());
+        memcpy(*proof_out, bytes.data(), bytes.size());
+        *len_out = bytes.size();
+        return 0;
+    } catch (const std::exception& ex) {
+        g_orc_error = ex.what();
+        return -1;
+    }
+}
+
+// 0 = accepted; -1 = rejected / malformed (orc_last_error names the reference error it corresponds to)
+int orc_stark_verify(const uint32_t* key_words, size_t key_n, const uint8_t* proof, size_t len, uint32_t log_blowup,
+                     uint32_t num_queries, uint32_t pow_bits) {
+    try {
+        KeyBlob key = parse_key(key_words, key_n);
+        Proof p = decode_proof(proof, len);
+        // decode -> encode must round-trip (crates/sdk/tests/integration_test.rs:405-425)
+        std::vector<uint8_t> again = encode_proof(p);
+        if (again.size() != len || memcmp(again.data(), proof, len) != 0) throw VerifyError("codec round trip differs");
+        stark_verify(key, p, FriParams{log_blowup, num_queries, pow_bits});
+        return 0;
+    } catch (const std::exception& ex) {
+        g_orc_error = ex.what();
+        return -1;
+    }
+}
+
+// challenger known-answer hook: observe `n_obs` values, then sample `n_samples` (tests drive this against the
+// device/host challenger of the product library)
+void orc_challenger_run(const uint32_t* obs, size_t n_obs, uint32_t* samples, size_t n_samples) {
+    Challenger ch;
+    for (size_t i = 0; i < n_obs; i++) ch.observe(F(obs[i]));
+    for (size_t i = 0; i < n_samples; i++) samples[i] = ch.sample().v;
+}
+}

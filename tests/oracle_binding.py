@@ -38,6 +38,14 @@ class Oracle:
         lib.orc_ef_mul.argtypes = [vp, vp, vp]
         lib.orc_ef_inv.argtypes = [vp, vp]
         lib.orc_poseidon2_constants.argtypes = [vp]
+        lib.orc_last_error.restype = C.c_char_p
+        lib.orc_free.argtypes = [vp]
+        lib.orc_stark_prove.restype = C.c_int
+        lib.orc_stark_prove.argtypes = [vp, C.c_size_t, C.c_size_t, vp, vp, vp, vp, C.c_uint32, C.c_uint32, C.c_uint32,
+                                        C.c_int, C.POINTER(vp), C.POINTER(C.c_size_t)]
+        lib.orc_stark_verify.restype = C.c_int
+        lib.orc_stark_verify.argtypes = [vp, C.c_size_t, vp, C.c_size_t, C.c_uint32, C.c_uint32, C.c_uint32]
+        lib.orc_challenger_run.argtypes = [vp, C.c_size_t, vp, C.c_size_t]
 
     # ---- constants / field
     def poseidon2_constants(self):
@@ -137,6 +145,38 @@ class Oracle:
         if want_lde:
             return root, [np.ascontiguousarray(a.T) for a in ldes]
         return root
+
+    # ---- STARK
+    def stark_prove(self, key_words, airs, log_blowup, num_queries, pow_bits, threads=8):
+        """airs: list of (air_id, [matrices (height, width) uint32: cached parts then common], public_values)."""
+        key = np.ascontiguousarray(key_words, dtype=np.uint32)
+        ids = np.array([a[0] for a in airs], dtype=np.uint32)
+        heights = np.array([a[1][0].shape[0] for a in airs], dtype=np.uint64)
+        cols = [np.ascontiguousarray(m.T, dtype=np.uint32) for a in airs for m in a[1]]
+        mat_ptrs = (C.c_void_p * max(1, len(cols)))(*[c.ctypes.data for c in cols])
+        pvs = [np.ascontiguousarray(a[2], dtype=np.uint32) for a in airs]
+        pv_ptrs = (C.c_void_p * len(airs))(*[p.ctypes.data for p in pvs])
+        out, n = C.c_void_p(), C.c_size_t()
+        rc = self.lib.orc_stark_prove(key.ctypes.data, key.size, len(airs), ids.ctypes.data, mat_ptrs, heights.ctypes.data,
+                                      pv_ptrs, log_blowup, num_queries, pow_bits, threads, C.byref(out), C.byref(n))
+        if rc != 0:
+            raise RuntimeError("oracle prove: " + self.lib.orc_last_error().decode())
+        data = C.string_at(out.value, n.value)
+        self.lib.orc_free(out)
+        return data
+
+    def stark_verify(self, key_words, proof, log_blowup, num_queries, pow_bits):
+        """Returns None when accepted, else the name of the verification error."""
+        key = np.ascontiguousarray(key_words, dtype=np.uint32)
+        buf = (C.c_uint8 * len(proof)).from_buffer_copy(proof)
+        rc = self.lib.orc_stark_verify(key.ctypes.data, key.size, buf, len(proof), log_blowup, num_queries, pow_bits)
+        return None if rc == 0 else self.lib.orc_last_error().decode()
+
+    def challenger_run(self, observed, n_samples):
+        obs = np.ascontiguousarray(observed, dtype=np.uint32)
+        out = np.zeros(n_samples, dtype=np.uint32)
+        self.lib.orc_challenger_run(obs.ctypes.data, obs.size, out.ctypes.data, n_samples)
+        return out
 
     def fill_synthetic(self, height, width, seed):
         out = np.zeros((width, height), dtype=np.uint32)

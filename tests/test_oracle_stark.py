@@ -1,0 +1,102 @@
+"""CPU oracle: STARK prove -> codec -> verify, on the reference's own fixture shapes (Fibonacci AIR n = 32,
+extensions/native/recursion/src/tests.rs:109) and on the chain AIR; negative tests mirror
+crates/circuits/poseidon2-air/src/tests.rs:56-74 (pranked trace -> OodEvaluationMismatch)."""
+import numpy as np
+import pytest
+
+import airs
+
+P = 2013265921
+
+
+def build_key(orc, air_list, log_blowup):
+    for a in air_list:
+        if a.prep is not None:
+            a.prep_commit = orc.commit([a.prep], log_blowup)
+    return airs.key_blob(air_list)
+
+
+def test_challenger_duplex_order(orc):
+    # sample pops from the END of the rate part; an observe after a sample invalidates the remaining outputs
+    s = orc.challenger_run(np.arange(1, 9, dtype=np.uint32), 8)
+    st = np.zeros((1, 16), dtype=np.uint32)
+    st[0, :8] = np.arange(1, 9)
+    perm = orc.permute(st)[0]
+    assert list(s) == list(perm[:8][::-1])
+    # 3 pending inputs: the permutation runs at the first sample
+    s2 = orc.challenger_run(np.array([5, 6, 7], dtype=np.uint32), 2)
+    st[0] = 0
+    st[0, :3] = (5, 6, 7)
+    perm2 = orc.permute(st)[0]
+    assert list(s2) == [perm2[7], perm2[6]]
+
+
+@pytest.mark.parametrize("n,b,queries,pow_bits", [(32, 1, 4, 3), (8, 2, 3, 0), (1 << 10, 1, 5, 8)])
+def test_fibonacci_prove_verify(orc, n, b, queries, pow_bits):
+    air = airs.fibonacci_air()
+    key = build_key(orc, [air], b)
+    trace, pvs = airs.fibonacci_trace(n)
+    proof = orc.stark_prove(key, [(0, [trace], pvs)], b, queries, pow_bits)
+    assert orc.stark_verify(key, proof, b, queries, pow_bits) is None
+    # deterministic (minimum PoW witness)
+    assert proof == orc.stark_prove(key, [(0, [trace], pvs)], b, queries, pow_bits)
+    # wrong public value
+    bad = pvs.copy(); bad[2] = (int(bad[2]) + 1) % P
+    p2 = orc.stark_prove(key, [(0, [trace], bad)], b, queries, pow_bits)
+    assert "OodEvaluationMismatch" in orc.stark_verify(key, p2, b, queries, pow_bits)
+    # pranked trace cell
+    t2 = trace.copy(); t2[n // 2, 1] = (int(t2[n // 2, 1]) + 1) % P
+    p3 = orc.stark_prove(key, [(0, [t2], pvs)], b, queries, pow_bits)
+    assert "OodEvaluationMismatch" in orc.stark_verify(key, p3, b, queries, pow_bits)
+    # verifier parameters must match
+    assert orc.stark_verify(key, proof, b, queries + 1, pow_bits) is not None
+
+
+def test_proof_bytes_tamper(orc):
+    air = airs.fibonacci_air()
+    key = build_key(orc, [air], 1)
+    trace, pvs = airs.fibonacci_trace(64)
+    proof = bytearray(orc.stark_prove(key, [(0, [trace], pvs)], 1, 3, 2))
+    assert orc.stark_verify(key, bytes(proof), 1, 3, 2) is None
+    rng = np.random.default_rng(3)
+    rejected = 0
+    for pos in rng.integers(4, len(proof), size=40):
+        q = bytearray(proof)
+        q[pos] ^= 1
+        if orc.stark_verify(key, bytes(q), 1, 3, 2) is not None:
+            rejected += 1
+    assert rejected == 40
+    assert orc.stark_verify(key, bytes(proof[:-1]), 1, 3, 2) is not None
+
+
+def test_multi_air_mixed_heights_prep_cached(orc):
+    b = 1
+    a0 = airs.fibonacci_air()
+    a1 = airs.chain_air(7, with_prep=True, cached_width=3, height=64, seed=1)
+    a2 = airs.chain_air(5)
+    a3 = airs.chain_air(9, with_prep=True, height=16, seed=2)
+    key = build_key(orc, [a0, a1, a2, a3], b)
+    t0, pv0 = airs.fibonacci_trace(256)
+    p1, pv1 = airs.chain_trace(a1, 64, seed=5)
+    p2, pv2 = airs.chain_trace(a2, 512, seed=6)
+    p3, pv3 = airs.chain_trace(a3, 16, seed=7)
+    inputs = [(0, [t0], pv0), (1, p1, pv1), (2, p2, pv2), (3, p3, pv3)]
+    proof = orc.stark_prove(key, inputs, b, 6, 4)
+    assert orc.stark_verify(key, proof, b, 6, 4) is None
+    # optional AIRs: a subset of the key's AIRs (extensions/native/recursion/src/tests.rs optional-AIR cases)
+    proof2 = orc.stark_prove(key, [inputs[1], inputs[3]], b, 6, 4)
+    assert orc.stark_verify(key, proof2, b, 6, 4) is None
+    # cached partition inconsistent with the common main
+    bad = [m.copy() for m in p1]
+    bad[0][3, 1] = (int(bad[0][3, 1]) + 5) % P
+    proof3 = orc.stark_prove(key, [inputs[0], (1, bad, pv1), inputs[2], inputs[3]], b, 6, 4)
+    assert "OodEvaluationMismatch" in orc.stark_verify(key, proof3, b, 6, 4)
+
+
+def test_blowup2_quotient_degree2(orc):
+    b = 2
+    a = airs.chain_air(6)
+    key = build_key(orc, [a], b)
+    parts, pv = airs.chain_trace(a, 128, seed=9)
+    proof = orc.stark_prove(key, [(0, parts, pv)], b, 4, 5)
+    assert orc.stark_verify(key, proof, b, 4, 5) is None
