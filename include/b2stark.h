@@ -141,6 +141,45 @@ int32_t b2s_pcs_open(b2s_engine* e, const b2s_pcs_data* d, uint64_t index, uint3
 int32_t b2s_pcs_layer(b2s_engine* e, const b2s_pcs_data* d, uint32_t level, uint32_t* out);
 void b2s_pcs_free(b2s_pcs_data* d);
 
+/* ---- proving key and proof (StarkEngine::prove) ---------------------------------------------------------
+ * device.transport_pk_to_device(&pk)                     crates/vm/src/arch/vm.rs:382,
+ *                                                        crates/sdk/src/prover/vm/mod.rs:23
+ * The reference's MultiStarkProvingKey is a serde type of the un-vendored openvm-stark-backend; the Rust shim
+ *  flattens it into this library's key blob: little-endian u32 words
+ *   'B2PK', 1, pre_hash[8], log_up_pow_bits, num_airs, then per AIR
+ *     width_preprocessed, n_cached, cached_widths[], width_common_main, width_after_challenge, log_quotient_degree,
+ *     num_public_values, num_exposed_values,
+ *     [if width_preprocessed: commit[8], log_height, row-major canonical trace]
+ *     num_nodes, nodes[][4] = {kind,a,b,c}, num_constraints, constraint_idx[]
+ * (node kinds: 0 Constant 1 Preprocessed 2 Main 3 Permutation 4 Public 5 Challenge 6 Exposed 7 IsFirstRow
+ *  8 IsLastRow 9 IsTransition 10 Add 11 Sub 12 Neg 13 Mul; content of SymbolicExpressionDag as consumed at
+ *  extensions/native/recursion/src/stark/mod.rs:1023-1085, types.rs:19-95).
+ * Loading uploads and commits the preprocessed traces (the root must equal the key's commit) and compiles each
+ * constraint DAG into the register-allocated program the quotient kernel interprets. */
+typedef struct b2s_pk b2s_pk;
+int32_t b2s_pk_load(b2s_engine* e, const uint32_t* key_words, size_t n_words, b2s_pk** out);
+void b2s_pk_free(b2s_pk* pk);
+
+/* AirProvingContext {cached_mains: Vec<CommittedTraceData>, common_main, public_values}
+ * (built at crates/vm/src/arch/vm.rs:588-599; GPU instance crates/vm/src/system/cuda/program.rs:121-125).
+ * A cached main is passed as the PcsData returned by b2s_commit on that single trace. */
+typedef struct {
+    uint32_t air_id;
+    uint32_t n_cached;
+    const b2s_pcs_data* const* cached;
+    const b2s_matrix* common_main;      /* NULL when the AIR has no common main */
+    const uint32_t* public_values;      /* canonical */
+    uint32_t n_public_values;
+} b2s_air_ctx;
+
+/* engine.prove(&pk, ctx) -> Proof<SC>                    crates/vm/src/arch/vm.rs:694,1005
+ * Transcript order: extensions/native/recursion/src/stark/mod.rs:140-364; opening: fri/two_adic_pcs.rs:41-376,
+ * fri/mod.rs:33-170. AIRs must be given in strictly increasing air_id. The proof is returned in the reference's
+ * wire format (crates/sdk/src/codec.rs:92-330) in a buffer released with b2s_free. Proof-of-work witnesses are the
+ * minimum valid ones (the reference returns any valid witness). This round: AIRs without interactions. */
+int32_t b2s_prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_airs, uint8_t** proof_bytes,
+                  size_t* proof_len);
+
 /* ---- primitives run on the device, for known-answer / parity tests ------------------------------------ */
 /* n states of 16 canonical words, permuted in place on the GPU */
 int32_t b2s_poseidon2_permute(b2s_engine* e, uint32_t* host_states, size_t n_states);

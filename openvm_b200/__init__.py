@@ -9,9 +9,11 @@ from .engine import (  # noqa: F401
     B2Device,
     DeviceMatrix,
     PcsData,
+    ProvingKey,
+    AirProvingContext,
     FriParameters,
     B2StarkError,
     library_path,
 )
 
-__all__ = ["B2Engine", "B2Device", "DeviceMatrix", "PcsData", "FriParameters", "B2StarkError", "library_path"]
+__all__ = ["B2Engine", "B2Device", "DeviceMatrix", "PcsData", "ProvingKey", "AirProvingContext", "FriParameters", "B2StarkError", "library_path"]

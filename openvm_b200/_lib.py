@@ -22,6 +22,12 @@ class Metrics(C.Structure):
                 ("poseidon2_permutations", C.c_uint64)]
 
 
+class AirCtx(C.Structure):
+    _fields_ = [("air_id", C.c_uint32), ("n_cached", C.c_uint32), ("cached", C.POINTER(C.c_void_p)),
+                ("common_main", C.c_void_p), ("public_values", C.POINTER(C.c_uint32)),
+                ("n_public_values", C.c_uint32)]
+
+
 # name -> (restype, argtypes); must list every symbol declared in include/b2stark.h
 SIGNATURES = {
     "b2s_engine_new": (C.c_int32, [C.POINTER(FriParams), C.c_int32, C.POINTER(vp)]),
@@ -52,6 +58,9 @@ SIGNATURES = {
     "b2s_pcs_open": (C.c_int32, [vp, vp, C.c_uint64, vp, vp]),
     "b2s_pcs_layer": (C.c_int32, [vp, vp, C.c_uint32, vp]),
     "b2s_pcs_free": (None, [vp]),
+    "b2s_pk_load": (C.c_int32, [vp, vp, C.c_size_t, C.POINTER(vp)]),
+    "b2s_pk_free": (None, [vp]),
+    "b2s_prove": (C.c_int32, [vp, vp, vp, C.c_size_t, C.POINTER(vp), C.POINTER(C.c_size_t)]),
     "b2s_poseidon2_permute": (C.c_int32, [vp, vp, C.c_size_t]),
     "b2s_bench_modmul": (C.c_int32, [vp, C.c_uint64, C.c_uint32, C.c_int32, C.POINTER(C.c_double)]),
     "b2s_bench_poseidon2": (C.c_int32, [vp, C.c_uint64, C.c_uint32, C.POINTER(C.c_double)]),

@@ -100,6 +100,8 @@ int32_t guarded(const b2s_engine* e_const, F&& fn) {
     }
 }
 
+}  // namespace
+namespace b2 {
 b2s_matrix* new_matrix(b2s_engine* e, uint64_t height, uint64_t width) {
     b2s_matrix* m = new b2s_matrix();
     m->eng = e;
@@ -119,7 +121,32 @@ void free_pcs(b2s_pcs_data* d) {
     delete d;
 }
 
-}  // namespace
+b2s_pcs_data* commit_matrices(b2s_engine* e, const b2s_matrix* const* mats, const Fp* shifts, size_t n) {
+    StageScope total(e, ST_COMMIT);
+    b2s_pcs_data* d = new b2s_pcs_data();
+    d->eng = e;
+    try {
+        const uint32_t lb = e->params.log_blowup;
+        for (size_t i = 0; i < n; i++) {
+            const b2s_matrix* in = mats[i];
+            B2_REQUIRE(in != nullptr, B2S_ERR_BAD_ARG, "null matrix");
+            B2_REQUIRE(is_pow2(in->height), B2S_ERR_SHAPE, "commit: trace height must be a power of two");
+            B2_REQUIRE(in->width > 0, B2S_ERR_SHAPE, "commit: zero-width trace");
+            b2s_matrix* lde = new_matrix(e, in->height << lb, in->width);
+            d->mats.push_back(lde);
+            d->owns.push_back(true);
+            StageScope sc(e, ST_LDE);
+            lde_columns(e, in->d, in->height, log2_exact(in->height), in->width, lb, shifts ? shifts[i] : Fp::one(), lde->d,
+                        lde->height);
+        }
+        mmcs_build(e, d);
+    } catch (...) {
+        free_pcs(d);
+        throw;
+    }
+    return d;
+}
+}  // namespace b2
 
 extern "C" {
 
@@ -369,29 +396,43 @@ int32_t b2s_commit(b2s_engine* e, const b2s_matrix* const* mats, size_t n_mats, 
     if (!e || !mats || !n_mats || !root8 || !out) return B2S_ERR_BAD_ARG;
     *out = nullptr;
     return guarded(e, [&] {
-        StageScope total(e, ST_COMMIT);
-        b2s_pcs_data* d = new b2s_pcs_data();
-        d->eng = e;
+        b2s_pcs_data* d = commit_matrices(e, mats, nullptr, n_mats);
         try {
-            const uint32_t lb = e->params.log_blowup;
-            for (size_t i = 0; i < n_mats; i++) {
-                const b2s_matrix* in = mats[i];
-                B2_REQUIRE(in != nullptr, B2S_ERR_BAD_ARG, "null matrix");
-                B2_REQUIRE(is_pow2(in->height), B2S_ERR_SHAPE, "commit: trace height must be a power of two");
-                B2_REQUIRE(in->width > 0, B2S_ERR_SHAPE, "commit: zero-width trace");
-                b2s_matrix* lde = new_matrix(e, in->height << lb, in->width);
-                d->mats.push_back(lde);
-                d->owns.push_back(true);
-                StageScope sc(e, ST_LDE);
-                lde_columns(e, in->d, in->height, log2_exact(in->height), in->width, lb, Fp::one(), lde->d, lde->height);
-            }
-            mmcs_build(e, d);
             root_to_host(e, d, root8);
         } catch (...) {
             free_pcs(d);
             throw;
         }
         *out = d;
+    });
+}
+
+// ---- proving key / prove ---------------------------------------------------------------------------------------
+int32_t b2s_pk_load(b2s_engine* e, const uint32_t* key_words, size_t n_words, b2s_pk** out) {
+    if (!e || !key_words || !out) return B2S_ERR_BAD_ARG;
+    *out = nullptr;
+    return guarded(e, [&] { *out = pk_load(e, key_words, n_words); });
+}
+
+void b2s_pk_free(b2s_pk* pk) {
+    if (!pk) return;
+    cudaSetDevice(pk->eng->device);
+    pk_free(pk);
+}
+
+int32_t b2s_prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_airs, uint8_t** proof_bytes,
+                  size_t* proof_len) {
+    if (!e || !pk || !airs || !n_airs || !proof_bytes || !proof_len) return B2S_ERR_BAD_ARG;
+    *proof_bytes = nullptr;
+    *proof_len = 0;
+    return guarded(e, [&] {
+        std::vector<uint8_t> bytes;
+        prove(e, pk, airs, n_airs, bytes);
+        uint8_t* buf = (uint8_t*)malloc(bytes.size() ? bytes.size() : 1);
+        if (!buf) fail(B2S_ERR_OOM, "proof buffer allocation failed");
+        memcpy(buf, bytes.data(), bytes.size());
+        *proof_bytes = buf;
+        *proof_len = bytes.size();
     });
 }
 

@@ -94,6 +94,34 @@ struct b2s_pcs_data {
 };
 
 namespace b2 {
+// one AIR of a loaded proving key (prover.cu)
+struct AirKeyDev {
+    uint32_t width_prep = 0, width_common = 0, width_after = 0, log_qd = 0, num_pv = 0, num_exposed = 0;
+    std::vector<uint32_t> cached_widths;
+    uint32_t prep_log_height = 0;
+    uint32_t prep_commit[8] = {0};       // Montgomery
+    b2s_matrix* prep_trace = nullptr;
+    b2s_pcs_data* prep_pcs = nullptr;
+    // compiled constraint program: {op, dst, a, b} words, device copy + host count
+    std::vector<uint4> program;
+    uint4* d_program = nullptr;
+    uint32_t num_slots = 0, num_constraints = 0;
+    uint32_t total_cols() const {
+        uint32_t t = width_prep + width_common;
+        for (uint32_t w : cached_widths) t += w;
+        return t;
+    }
+};
+}  // namespace b2
+
+struct b2s_pk {
+    b2s_engine* eng = nullptr;
+    uint32_t pre_hash[8] = {0};          // Montgomery
+    uint32_t log_up_pow_bits = 0;
+    std::vector<b2::AirKeyDev> airs;
+};
+
+namespace b2 {
 
 inline unsigned log2_exact(uint64_t x) {
     unsigned l = 0;
@@ -128,6 +156,23 @@ void fill_synthetic(b2s_engine* e, uint32_t* d, uint64_t height, uint64_t width,
 void gather_open(b2s_engine* e, const b2s_pcs_data* d, uint64_t index, uint32_t* h_rows, uint32_t* h_proof);
 void download_layer(b2s_engine* e, const b2s_pcs_data* d, uint32_t level, uint32_t* h_out);
 double bench_modmul(b2s_engine* e, uint64_t threads, uint32_t iters, int ilp);
+struct OpenDesc {
+    const uint32_t* base;  // column 0 of a matrix, or plane 0 of a digest layer
+    uint64_t stride;       // height (matrix) or node count (layer)
+    uint64_t row;
+    uint32_t count;        // width or 8
+    uint32_t out_off;
+};
+void gather_rows(b2s_engine* e, const std::vector<OpenDesc>& descs, size_t total_words, uint32_t* h_out);
+// prover.cu
+b2s_pk* pk_load(b2s_engine* e, const uint32_t* words, size_t n);
+void pk_free(b2s_pk* pk);
+void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_airs, std::vector<uint8_t>& out);
+// api.cu helpers shared with the prover
+b2s_matrix* new_matrix(b2s_engine* e, uint64_t height, uint64_t width);
+void free_pcs(b2s_pcs_data* d);
+// commit `mats` (evaluations over shifts[i]*H, natural order): LDE each, then one MMCS tree; the PcsData owns the LDEs
+b2s_pcs_data* commit_matrices(b2s_engine* e, const b2s_matrix* const* mats, const Fp* shifts, size_t n);
 double bench_poseidon2(b2s_engine* e, uint64_t threads, uint32_t iters);
 
 }  // namespace b2

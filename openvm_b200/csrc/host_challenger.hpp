@@ -1,0 +1,86 @@
+// Host side of the Fiat-Shamir transcript: Poseidon2 permutation and DuplexChallenger<F, Perm, 16, 8> on the CPU,
+// Montgomery form (shares field.cuh and the generated constants with the device code).
+//
+// Replaces (reference, external): p3-challenger `DuplexChallenger`, host-side and sequential in the reference as
+// well; in-tree twin extensions/native/recursion/src/challenger/duplex.rs:27-131 (observe / sample pop order /
+// sample_bits / check_witness). The transcript is a few thousand permutations per proof; the searches that are
+// not tiny (proof-of-work grinding) run on the device (prover.cu: pow_grind_kernel).
+#pragma once
+#include "field.cuh"
+#include "poseidon2_constants.cuh"
+
+namespace b2 {
+
+struct HostPoseidon2 {
+    uint32_t ext[8][16] = B2_P2_EXT_ALL;
+    uint32_t partial[13] = B2_P2_PARTIAL;
+    uint32_t diag[16] = B2_P2_DIAG;
+
+    static Fp sbox(Fp x) { Fp x2 = x * x, x3 = x2 * x, x4 = x2 * x2; return x3 * x4; }
+    static void external(Fp* s) {
+        for (int b = 0; b < 16; b += 4) {
+            Fp x0 = s[b], x1 = s[b + 1], x2 = s[b + 2], x3 = s[b + 3];
+            Fp sum = x0 + x1 + x2 + x3;
+            s[b] = sum + x0 + x1 + x1;          // 2x0 + 3x1 + x2 + x3
+            s[b + 1] = sum + x1 + x2 + x2;      // x0 + 2x1 + 3x2 + x3
+            s[b + 2] = sum + x2 + x3 + x3;      // x0 + x1 + 2x2 + 3x3
+            s[b + 3] = sum + x3 + x0 + x0;      // 3x0 + x1 + x2 + 2x3
+        }
+        Fp sums[4];
+        for (int i = 0; i < 16; i++) sums[i & 3] += s[i];
+        for (int i = 0; i < 16; i++) s[i] += sums[i & 3];
+    }
+    void permute(Fp* s) const {
+        external(s);
+        for (int r = 0; r < 4; r++) {
+            for (int i = 0; i < 16; i++) s[i] = sbox(s[i] + Fp::raw(ext[r][i]));
+            external(s);
+        }
+        for (int r = 0; r < 13; r++) {
+            s[0] = sbox(s[0] + Fp::raw(partial[r]));
+            Fp sum;
+            for (int i = 0; i < 16; i++) sum += s[i];
+            for (int i = 0; i < 16; i++) s[i] = sum + s[i] * Fp::raw(diag[i]);
+        }
+        for (int r = 4; r < 8; r++) {
+            for (int i = 0; i < 16; i++) s[i] = sbox(s[i] + Fp::raw(ext[r][i]));
+            external(s);
+        }
+    }
+};
+
+struct HostChallenger {
+    HostPoseidon2 perm;
+    Fp st[16];
+    int in_ptr = 0, out_ptr = 0;
+    uint64_t permutations = 0;
+
+    void duplexing() { in_ptr = 0; perm.permute(st); out_ptr = 8; permutations++; }
+    void observe(Fp v) {
+        out_ptr = 0;
+        st[in_ptr++] = v;
+        if (in_ptr == 8) duplexing();
+    }
+    void observe_canonical(uint32_t c) { observe(Fp::from_canonical(c)); }
+    void observe_digest(const uint32_t* monty8) { for (int i = 0; i < 8; i++) observe(Fp::raw(monty8[i])); }
+    void observe_ext(const Fp4& e) { for (int i = 0; i < 4; i++) observe(e.c[i]); }
+    Fp sample() {
+        if (in_ptr != 0 || out_ptr == 0) duplexing();
+        return st[--out_ptr];
+    }
+    Fp4 sample_ext() {
+        Fp4 e;
+        for (int i = 0; i < 4; i++) e.c[i] = sample();
+        return e;
+    }
+    uint32_t sample_bits(unsigned bits) {
+        uint32_t v = sample().to_canonical();
+        return bits >= 32 ? v : (v & ((1u << bits) - 1));
+    }
+    bool check_witness(unsigned bits, Fp w) {
+        observe(w);
+        return sample_bits(bits) == 0;
+    }
+};
+
+}  // namespace b2

@@ -1,0 +1,933 @@
+// StarkEngine::prove on the device: quotient evaluation, out-of-domain opening, FRI commit phase, proof-of-work
+// and query openings, driven by a host-side Fiat-Shamir transcript, emitted in the reference's proof wire format.
+//
+// Replaces (reference, external): openvm-stark-backend `MultiTraceStarkProver::prove` / `QuotientCommitter` /
+// `OpeningProver` and Plonky3 `TwoAdicFriPcs::open`, reached from crates/vm/src/arch/vm.rs:694,1005. The in-tree
+// specification followed step by step is the verifier twin:
+//   extensions/native/recursion/src/stark/mod.rs:130-834,903-1126   transcript, rounds, constraint folding
+//   extensions/native/recursion/src/fri/two_adic_pcs.rs:41-376      opened-value order, reduced openings, queries
+//   extensions/native/recursion/src/fri/mod.rs:33-170               fold formula and beta^2 roll-in
+//   extensions/native/recursion/src/fri/domain.rs:59-155            selectors, quotient chunk domains
+//   crates/sdk/src/codec.rs:92-330                                  wire format
+//
+// Device work (all integer-pipe bound, one thread per row unless noted):
+//   quotient_kernel       interprets the AIR's register-allocated constraint program on every row of the quotient
+//                         domain (= the first N*qd rows of the bit-reversed LDE), folds with alpha, divides by Z_H
+//   bary_weights_kernel   x_i / (z - x_i) for the N points of LDE block 0, once per (height, point)
+//   bary_dot_kernel       per column sum_i p(x_i) * weight_i  -> p(z)          (block per column x split)
+//   reduced_open_kernel   ro_h[row] += alpha^o * (sum_t alpha^t p_t(z) - sum_t alpha^t p_t(x)) / (z - x)
+//   fri_pack / fri_fold   commit-phase leaves (2 EF = 8 words per row) and the arity-2 fold with beta^2 roll-in
+//   pow_grind_kernel      parallel search for the minimum proof-of-work witness
+//   gather_rows_kernel    all query openings (rows and Merkle siblings) of all rounds in one launch
+#include "common.cuh"
+#include "host_challenger.hpp"
+#include "poseidon2.cuh"
+
+#include <algorithm>
+#include <array>
+#include <map>
+
+namespace b2 {
+
+// ---- key blob -> device key --------------------------------------------------------------------------------
+enum NodeKind { N_CONST = 0, N_PREP, N_MAIN, N_PERM, N_PUBLIC, N_CHALLENGE, N_EXPOSED, N_FIRST, N_LAST, N_TRANS,
+                N_ADD, N_SUB, N_NEG, N_MUL };
+enum Op { OP_LOAD = 0, OP_PUBLIC, OP_CONST, OP_FIRST, OP_LAST, OP_TRANS, OP_ADD, OP_SUB, OP_NEG, OP_MUL, OP_ACC };
+
+struct HostNode { uint32_t kind, a, b, c; };
+
+// Compile the DAG (topological node list + constraint indices) into a straight-line program over a small set of
+// slots: dead nodes are dropped, a slot is recycled after the last use of its value, and each constraint becomes
+// an OP_ACC with the index of its alpha power (constraint k of C carries alpha^(C-1-k): Horner order).
+static void compile_dag(AirKeyDev& air, const std::vector<HostNode>& nodes, const std::vector<uint32_t>& cidx) {
+    const size_t n = nodes.size();
+    std::vector<uint32_t> last_use(n, 0);
+    std::vector<char> live(n, 0);
+    for (uint32_t c : cidx) {
+        B2_REQUIRE(c < n, B2S_ERR_BAD_ARG, "key: constraint index out of range");
+        live[c] = 1;
+    }
+    for (size_t i = n; i-- > 0;) {
+        if (!live[i]) continue;
+        const HostNode& nd = nodes[i];
+        if (nd.kind >= N_ADD) {
+            B2_REQUIRE(nd.a < i && (nd.kind == N_NEG || nd.b < i), B2S_ERR_BAD_ARG, "key: DAG is not topologically ordered");
+            live[nd.a] = 1;
+            if (nd.kind != N_NEG) live[nd.b] = 1;
+        }
+    }
+    for (size_t i = 0; i < n; i++) {
+        if (!live[i]) continue;
+        const HostNode& nd = nodes[i];
+        last_use[i] = std::max<uint32_t>(last_use[i], (uint32_t)i);
+        if (nd.kind >= N_ADD) {
+            last_use[nd.a] = (uint32_t)i;
+            if (nd.kind != N_NEG) last_use[nd.b] = (uint32_t)i;
+        }
+    }
+    // column index of a variable inside the AIR's pointer table: [preprocessed][part 0][part 1]...
+    std::vector<uint32_t> part_base;
+    uint32_t base = air.width_prep;
+    for (uint32_t w : air.cached_widths) { part_base.push_back(base); base += w; }
+    if (air.width_common) part_base.push_back(base);
+    auto part_width = [&](uint32_t p) { return p < air.cached_widths.size() ? air.cached_widths[p] : air.width_common; };
+
+    std::vector<uint32_t> slot_of(n, 0xFFFFFFFFu), free_slots;
+    std::vector<std::vector<uint32_t>> expiring(n);
+    for (size_t i = 0; i < n; i++) if (live[i]) expiring[last_use[i]].push_back((uint32_t)i);
+    uint32_t num_slots = 0;
+    const uint32_t C = (uint32_t)cidx.size();
+    std::vector<std::vector<uint32_t>> acc_of(n);
+    for (uint32_t k = 0; k < C; k++) acc_of[cidx[k]].push_back(C - 1 - k);
+    air.program.clear();
+    for (size_t i = 0; i < n; i++) {
+        if (!live[i]) continue;
+        const HostNode& nd = nodes[i];
+        uint32_t sa = 0, sb = 0;
+        if (nd.kind >= N_ADD) {
+            sa = slot_of[nd.a];
+            sb = nd.kind == N_NEG ? 0 : slot_of[nd.b];
+        }
+        uint32_t dst;
+        if (!free_slots.empty()) { dst = free_slots.back(); free_slots.pop_back(); } else dst = num_slots++;
+        slot_of[i] = dst;
+        switch (nd.kind) {
+            case N_CONST:
+                B2_REQUIRE(nd.a < P, B2S_ERR_BAD_ARG, "key: non-canonical constant");
+                air.program.push_back(make_uint4(OP_CONST, dst, Fp::from_canonical(nd.a).v, 0));
+                break;
+            case N_PREP:
+                B2_REQUIRE(nd.a < air.width_prep && nd.b < 2, B2S_ERR_BAD_ARG, "key: preprocessed variable out of range");
+                air.program.push_back(make_uint4(OP_LOAD, dst, nd.a, nd.b));
+                break;
+            case N_MAIN:
+                B2_REQUIRE(nd.c < part_base.size() && nd.a < part_width(nd.c) && nd.b < 2, B2S_ERR_BAD_ARG,
+                           "key: main variable out of range");
+                air.program.push_back(make_uint4(OP_LOAD, dst, part_base[nd.c] + nd.a, nd.b));
+                break;
+            case N_PUBLIC:
+                B2_REQUIRE(nd.a < air.num_pv, B2S_ERR_BAD_ARG, "key: public value out of range");
+                air.program.push_back(make_uint4(OP_PUBLIC, dst, nd.a, 0));
+                break;
+            case N_FIRST: air.program.push_back(make_uint4(OP_FIRST, dst, 0, 0)); break;
+            case N_LAST: air.program.push_back(make_uint4(OP_LAST, dst, 0, 0)); break;
+            case N_TRANS: air.program.push_back(make_uint4(OP_TRANS, dst, 0, 0)); break;
+            case N_ADD: air.program.push_back(make_uint4(OP_ADD, dst, sa, sb)); break;
+            case N_SUB: air.program.push_back(make_uint4(OP_SUB, dst, sa, sb)); break;
+            case N_NEG: air.program.push_back(make_uint4(OP_NEG, dst, sa, 0)); break;
+            case N_MUL: air.program.push_back(make_uint4(OP_MUL, dst, sa, sb)); break;
+            default:
+                fail(B2S_ERR_BAD_ARG, "key: node kind needs a challenge phase (interactions are not supported in this build)");
+        }
+        for (uint32_t pw : acc_of[i]) air.program.push_back(make_uint4(OP_ACC, 0, dst, pw));
+        for (uint32_t j : expiring[i]) free_slots.push_back(slot_of[j]);
+    }
+    air.num_slots = std::max<uint32_t>(num_slots, 1);
+    air.num_constraints = C;
+}
+
+static void root_monty(b2s_engine* e, const b2s_pcs_data* d, uint32_t out[8]) {
+    B2_CUDA(cudaMemcpyAsync(out, d->layers.back(), 32, cudaMemcpyDeviceToHost, e->stream));
+    B2_CUDA(cudaStreamSynchronize(e->stream));
+}
+
+void pk_free(b2s_pk* pk) {
+    if (!pk) return;
+    b2s_engine* e = pk->eng;
+    for (auto& a : pk->airs) {
+        if (a.prep_pcs) free_pcs(a.prep_pcs);
+        if (a.prep_trace) b2s_matrix_free(a.prep_trace);
+        if (a.d_program) e->dfree(a.d_program, a.program.size() * sizeof(uint4));
+    }
+    delete pk;
+}
+
+b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n) {
+    size_t i = 0;
+    auto rd = [&]() -> uint32_t {
+        if (i >= n) fail(B2S_ERR_BAD_ARG, "key blob truncated");
+        return w[i++];
+    };
+    B2_REQUIRE(rd() == 0x4B503242u, B2S_ERR_BAD_ARG, "key blob: bad magic");
+    B2_REQUIRE(rd() == 1, B2S_ERR_BAD_ARG, "key blob: unsupported version");
+    b2s_pk* pk = new b2s_pk();
+    pk->eng = e;
+    try {
+        for (int j = 0; j < 8; j++) {
+            uint32_t v = rd();
+            B2_REQUIRE(v < P, B2S_ERR_BAD_ARG, "key blob: non-canonical pre_hash");
+            pk->pre_hash[j] = Fp::from_canonical(v).v;
+        }
+        pk->log_up_pow_bits = rd();
+        const uint32_t na = rd();
+        B2_REQUIRE(na <= (1u << 20), B2S_ERR_BAD_ARG, "key blob: AIR count");
+        pk->airs.resize(na);
+        for (auto& a : pk->airs) {
+            a.width_prep = rd();
+            uint32_t nc = rd();
+            B2_REQUIRE(nc <= 1024, B2S_ERR_BAD_ARG, "key blob: cached main count");
+            a.cached_widths.resize(nc);
+            for (auto& c : a.cached_widths) c = rd();
+            a.width_common = rd(); a.width_after = rd(); a.log_qd = rd(); a.num_pv = rd(); a.num_exposed = rd();
+            B2_REQUIRE(a.width_after == 0 && a.num_exposed == 0, B2S_ERR_BAD_ARG,
+                       "key: AIRs with interactions (after-challenge trace) are not supported in this build");
+            if (a.log_qd > e->params.log_blowup) fail(B2S_ERR_CONSTRAINT_DEGREE, "key: quotient degree exceeds the engine's blowup");
+            if (a.width_prep) {
+                for (int j = 0; j < 8; j++) a.prep_commit[j] = Fp::from_canonical(rd()).v;
+                a.prep_log_height = rd();
+                B2_REQUIRE(a.prep_log_height + e->params.log_blowup <= TWO_ADICITY, B2S_ERR_SHAPE, "key: preprocessed height");
+                const size_t cnt = (size_t)a.width_prep << a.prep_log_height;
+                B2_REQUIRE(i + cnt <= n, B2S_ERR_BAD_ARG, "key blob truncated (preprocessed trace)");
+                B2_REQUIRE(b2s_matrix_upload(e, w + i, (uint64_t)1 << a.prep_log_height, a.width_prep, B2S_LAYOUT_ROW_MAJOR,
+                                             B2S_REPR_CANONICAL, &a.prep_trace) == 0,
+                           B2S_ERR_INTERNAL, std::string("key: preprocessed upload failed: ") + e->last_error);
+                i += cnt;
+                const b2s_matrix* m = a.prep_trace;
+                a.prep_pcs = commit_matrices(e, &m, nullptr, 1);
+                uint32_t root[8];
+                root_monty(e, a.prep_pcs, root);
+                B2_REQUIRE(memcmp(root, a.prep_commit, 32) == 0, B2S_ERR_BAD_ARG,
+                           "key: preprocessed commitment does not match the committed trace");
+            }
+            const uint32_t nn = rd();
+            B2_REQUIRE((size_t)nn * 4 <= n - i, B2S_ERR_BAD_ARG, "key blob truncated (nodes)");
+            std::vector<HostNode> nodes(nn);
+            for (auto& nd : nodes) { nd.kind = rd(); nd.a = rd(); nd.b = rd(); nd.c = rd(); }
+            const uint32_t ncst = rd();
+            B2_REQUIRE(ncst <= n - i, B2S_ERR_BAD_ARG, "key blob truncated (constraints)");
+            std::vector<uint32_t> cidx(ncst);
+            for (auto& c : cidx) c = rd();
+            compile_dag(a, nodes, cidx);
+            if (!a.program.empty()) {
+                a.d_program = (uint4*)e->dmalloc(a.program.size() * sizeof(uint4));
+                B2_CUDA(cudaMemcpyAsync(a.d_program, a.program.data(), a.program.size() * sizeof(uint4), cudaMemcpyHostToDevice,
+                                        e->stream));
+            }
+        }
+        B2_REQUIRE(i == n, B2S_ERR_BAD_ARG, "key blob: trailing words");
+        B2_CUDA(cudaStreamSynchronize(e->stream));
+    } catch (...) {
+        pk_free(pk);
+        throw;
+    }
+    return pk;
+}
+
+// ---- quotient ---------------------------------------------------------------------------------------------------
+struct QuotientParams {
+    const uint4* program;
+    uint32_t prog_len;
+    const uint32_t* const* cols;   // LDE column base pointers, [preprocessed][part 0][part 1]...
+    const uint32_t* publics;       // Montgomery
+    const uint32_t* alpha_pows;    // [num_constraints][4], alpha^j
+    uint32_t* out;                 // qd chunk matrices, each 4 columns x N rows, column-major, natural row order
+    uint32_t n, b, lq;
+    uint32_t gq;                   // generator of order 2^(n+lq)
+    uint32_t ginv;                 // w_n^-1
+    uint32_t zh[16], inv_zh[16];   // Z_H(x) = x^N - 1 takes qd values on the quotient domain: index kq mod qd
+};
+
+// Thread r owns LDE row r (r < N*qd: the rows of the quotient domain are a prefix of the bit-reversed LDE), so the
+// `local` reads are coalesced; the `next` row differs from r by one XOR mask for whole warps except at carries.
+template <int NSLOT>
+__global__ void __launch_bounds__(128) quotient_kernel(QuotientParams p) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lm = p.n + p.b;
+    if (r >= (1u << (p.n + p.lq))) return;
+    const uint32_t K = lm ? (__brev(r) >> (32 - lm)) : 0u;
+    const uint32_t kq = K >> (p.b - p.lq);
+    const uint32_t Kn = (K + (1u << p.b)) & ((1u << lm) - 1);
+    const uint32_t rn = lm ? (__brev(Kn) >> (32 - lm)) : 0u;
+    const uint32_t rows[2] = {r, rn};
+    const Fp x = Fp::raw(M_GENERATOR) * fp_pow(Fp::raw(p.gq), kq);
+    const uint32_t qi = kq & ((1u << p.lq) - 1);
+    const Fp zh = Fp::raw(p.zh[qi]);
+    const Fp ginv = Fp::raw(p.ginv);
+    bool have_first = false, have_last = false;
+    Fp is_first, is_last;
+    uint32_t slot[NSLOT];
+    Fp acc[4];
+    for (uint32_t pc = 0; pc < p.prog_len; pc++) {
+        const uint4 ins = __ldg(p.program + pc);
+        switch (ins.x) {
+            case OP_LOAD: slot[ins.y] = __ldg(p.cols[ins.z] + rows[ins.w]); break;
+            case OP_PUBLIC: slot[ins.y] = __ldg(p.publics + ins.z); break;
+            case OP_CONST: slot[ins.y] = ins.z; break;
+            case OP_FIRST:
+                if (!have_first) { is_first = zh * fp_inv(x - Fp::one()); have_first = true; }
+                slot[ins.y] = is_first.v;
+                break;
+            case OP_LAST:
+                if (!have_last) { is_last = zh * fp_inv(x - ginv); have_last = true; }
+                slot[ins.y] = is_last.v;
+                break;
+            case OP_TRANS: slot[ins.y] = (x - ginv).v; break;
+            case OP_ADD: slot[ins.y] = (Fp::raw(slot[ins.z]) + Fp::raw(slot[ins.w])).v; break;
+            case OP_SUB: slot[ins.y] = (Fp::raw(slot[ins.z]) - Fp::raw(slot[ins.w])).v; break;
+            case OP_NEG: slot[ins.y] = (-Fp::raw(slot[ins.z])).v; break;
+            case OP_MUL: slot[ins.y] = (Fp::raw(slot[ins.z]) * Fp::raw(slot[ins.w])).v; break;
+            default: {  // OP_ACC
+                const uint4 ap = __ldg(reinterpret_cast<const uint4*>(p.alpha_pows) + ins.w);
+                const Fp v = Fp::raw(slot[ins.z]);
+                acc[0] += v * Fp::raw(ap.x); acc[1] += v * Fp::raw(ap.y);
+                acc[2] += v * Fp::raw(ap.z); acc[3] += v * Fp::raw(ap.w);
+            }
+        }
+    }
+    const Fp iz = Fp::raw(p.inv_zh[qi]);
+    const uint64_t N = (uint64_t)1 << p.n;
+    const uint32_t row = kq >> p.lq;
+#pragma unroll
+    for (int c = 0; c < 4; c++) p.out[((uint64_t)qi * 4 + c) * N + row] = (acc[c] * iz).v;
+}
+
+template <int NSLOT>
+static void launch_quotient_t(b2s_engine* e, const QuotientParams& p) {
+    const uint32_t rows = 1u << (p.n + p.lq);
+    quotient_kernel<NSLOT><<<(rows + 127) / 128, 128, 0, e->stream>>>(p);
+    B2_CHECK_LAUNCH();
+    e->launches[3]++;
+}
+static void launch_quotient(b2s_engine* e, uint32_t slots, const QuotientParams& p) {
+    if (slots <= 32) launch_quotient_t<32>(e, p);
+    else if (slots <= 128) launch_quotient_t<128>(e, p);
+    else if (slots <= 512) launch_quotient_t<512>(e, p);
+    else if (slots <= 2048) launch_quotient_t<2048>(e, p);
+    else if (slots <= 8192) launch_quotient_t<8192>(e, p);
+    else fail(B2S_ERR_CONSTRAINT_DEGREE, "quotient: constraint program needs more than 8192 live values");
+}
+
+// ---- out-of-domain evaluation (barycentric over LDE block 0) ---------------------------------------------------------
+// Block 0 of an LDE of a height-N trace holds p(x_i), x_i = g * w_N^{bitrev_n(i)}, i < N. For z off the coset:
+//   p(z) = ((z/g)^N - 1) / N * sum_i p(x_i) * x_i / (z - x_i)
+__global__ void bary_weights_kernel(uint32_t* __restrict__ wts, uint32_t n, Fp4 z, uint32_t wn) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t N = 1u << n;
+    if (i >= N) return;
+    const uint32_t e = n ? (__brev(i) >> (32 - n)) : 0u;
+    const Fp x = Fp::raw(M_GENERATOR) * fp_pow(Fp::raw(wn), e);
+    Fp4 d = z - x;
+    Fp4 w = fp4_inv(d) * x;
+#pragma unroll
+    for (int c = 0; c < 4; c++) wts[(uint64_t)c * N + i] = w.c[c].v;
+}
+
+constexpr int DOT_THREADS = 256;
+// grid (column, split): partial[(col * splits + split) * 4 + c] = sum over the split's rows of col[i] * wts[c][i]
+__global__ void __launch_bounds__(DOT_THREADS) bary_dot_kernel(const uint32_t* __restrict__ mat, uint64_t col_stride,
+                                                               const uint32_t* __restrict__ wts, uint32_t n,
+                                                               uint32_t* __restrict__ partial) {
+    __shared__ uint32_t sm[4][DOT_THREADS];
+    const uint32_t N = 1u << n;
+    const uint32_t col = blockIdx.x, split = blockIdx.y, splits = gridDim.y;
+    const uint32_t per = (N + splits - 1) / splits;
+    const uint32_t lo = split * per, hi = min(N, lo + per);
+    const uint32_t* __restrict__ colp = mat + (uint64_t)col * col_stride;
+    Fp acc[4];
+    for (uint32_t i = lo + threadIdx.x; i < hi; i += DOT_THREADS) {
+        const Fp v = Fp::raw(colp[i]);
+#pragma unroll
+        for (int c = 0; c < 4; c++) acc[c] += v * Fp::raw(wts[(uint64_t)c * N + i]);
+    }
+#pragma unroll
+    for (int c = 0; c < 4; c++) sm[c][threadIdx.x] = acc[c].v;
+    __syncthreads();
+    for (int s = DOT_THREADS / 2; s > 0; s >>= 1) {
+        if (threadIdx.x < s) {
+#pragma unroll
+            for (int c = 0; c < 4; c++) sm[c][threadIdx.x] = (Fp::raw(sm[c][threadIdx.x]) + Fp::raw(sm[c][threadIdx.x + s])).v;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x < 4) partial[((uint64_t)col * splits + split) * 4 + threadIdx.x] = sm[threadIdx.x][0];
+}
+
+// ---- reduced openings ------------------------------------------------------------------------------------------------
+struct ReducedParams {
+    const uint32_t* mat;        // LDE matrix, column-major, height 2^h
+    uint32_t width, h;
+    const uint32_t* alpha_pows; // [>= width][4]
+    uint32_t* ro;               // 4 planes of 2^h
+    uint32_t npoints;
+    Fp4 z[2], cz[2], coef[2];   // point, sum_t alpha^t p_t(z), alpha^offset
+    uint32_t wh;                // generator of order 2^h
+};
+__global__ void __launch_bounds__(128) reduced_open_kernel(ReducedParams p) {
+    const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t H = 1u << p.h;
+    if (row >= H) return;
+    Fp4 inner = Fp4::zero();
+    for (uint32_t t = 0; t < p.width; t++) {
+        const Fp v = Fp::raw(__ldg(p.mat + (uint64_t)t * H + row));
+        const uint4 ap = __ldg(reinterpret_cast<const uint4*>(p.alpha_pows) + t);
+        inner.c[0] += v * Fp::raw(ap.x); inner.c[1] += v * Fp::raw(ap.y);
+        inner.c[2] += v * Fp::raw(ap.z); inner.c[3] += v * Fp::raw(ap.w);
+    }
+    const uint32_t e = p.h ? (__brev(row) >> (32 - p.h)) : 0u;
+    const Fp x = Fp::raw(M_GENERATOR) * fp_pow(Fp::raw(p.wh), e);
+    Fp4 acc = Fp4::zero();
+    for (uint32_t j = 0; j < p.npoints; j++) acc += p.coef[j] * ((p.cz[j] - inner) * fp4_inv(p.z[j] - x));
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        uint32_t* dst = p.ro + (uint64_t)c * H + row;
+        *dst = (Fp::raw(*dst) + acc.c[c]).v;
+    }
+}
+
+// ---- FRI commit phase ------------------------------------------------------------------------------------------------
+// planes[4][2R] (bit-reversed evaluations) -> leaf matrix 8 columns x R rows: column 4k+c of row p = coefficient c of
+// element 2p+k  (fri/mod.rs:93-116: a commit-phase leaf is the pair (e0, e1) flattened)
+__global__ void fri_pack_kernel(const uint32_t* __restrict__ planes, uint32_t* __restrict__ leaf, uint32_t R) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= R) return;
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const uint2 pr = *reinterpret_cast<const uint2*>(planes + (uint64_t)c * 2 * R + 2 * p);
+        leaf[(uint64_t)c * R + p] = pr.x;
+        leaf[(uint64_t)(4 + c) * R + p] = pr.y;
+    }
+}
+// next[p] = e0 + (beta - x0)(e1 - e0)/(x1 - x0) + beta^2 * roll[p],  x0 = w_lh^{bitrev_lh(2p)}, x1 = -x0
+__global__ void fri_fold_kernel(const uint32_t* __restrict__ cur, uint32_t* __restrict__ next,
+                                const uint32_t* __restrict__ roll, uint32_t lh, uint32_t w, Fp4 beta, Fp4 beta2) {
+    const uint32_t R = 1u << (lh - 1);
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= R) return;
+    Fp4 e0, e1;
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const uint2 pr = *reinterpret_cast<const uint2*>(cur + (uint64_t)c * 2 * R + 2 * p);
+        e0.c[c] = Fp::raw(pr.x);
+        e1.c[c] = Fp::raw(pr.y);
+    }
+    const uint32_t ex = lh > 1 ? (__brev(p) >> (32 - (lh - 1))) : 0u;  // bitrev_lh(2p) = bitrev_{lh-1}(p)
+    const Fp x0 = fp_pow(Fp::raw(w), ex);
+    const Fp inv = fp_inv(-(x0 + x0));
+    Fp4 f = e0 + (beta - x0) * ((e1 - e0) * inv);
+    if (roll) {
+        Fp4 r;
+#pragma unroll
+        for (int c = 0; c < 4; c++) r.c[c] = Fp::raw(roll[(uint64_t)c * R + p]);
+        f += beta2 * r;
+    }
+#pragma unroll
+    for (int c = 0; c < 4; c++) next[(uint64_t)c * R + p] = f.c[c].v;
+}
+
+// ---- proof of work ------------------------------------------------------------------------------------------------------
+struct PowParams { uint32_t st[16]; uint32_t in_ptr, bits, base; };
+__global__ void __launch_bounds__(128) pow_grind_kernel(PowParams p, uint32_t count, uint32_t* result) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const uint32_t w = p.base + t;
+    if (w >= P) return;
+    Fp s[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) s[i] = Fp::raw(p.st[i]);
+    const Fp wm = Fp::from_canonical(w);
+#pragma unroll
+    for (int i = 0; i < 8; i++) if ((uint32_t)i == p.in_ptr) s[i] = wm;
+    poseidon2_permute(s);
+    const uint32_t v = s[7].to_canonical();
+    if ((v & ((1u << p.bits) - 1)) == 0) atomicMin(result, w);
+}
+
+// ---- host-side helpers ----------------------------------------------------------------------------------------------------
+struct Scratch {  // device buffers released when the proof is done (or abandoned)
+    b2s_engine* e;
+    std::vector<std::pair<void*, size_t>> bufs;
+    std::vector<b2s_pcs_data*> pcs;
+    explicit Scratch(b2s_engine* e_) : e(e_) {}
+    uint32_t* words(size_t n) {
+        void* p = e->dmalloc(n * 4);
+        bufs.push_back({p, n * 4});
+        return (uint32_t*)p;
+    }
+    void* bytes(size_t n) {
+        void* p = e->dmalloc(n);
+        bufs.push_back({p, n});
+        return p;
+    }
+    ~Scratch() {
+        for (auto* d : pcs) free_pcs(d);
+        for (auto& b : bufs) e->dfree(b.first, b.second);
+    }
+};
+
+struct ByteWriter {
+    std::vector<uint8_t>& buf;
+    void u32(uint32_t x) { for (int i = 0; i < 4; i++) buf.push_back((uint8_t)(x >> (8 * i))); }
+    void f(Fp x) { u32(x.to_canonical()); }
+    void ef(const Fp4& e) { for (int i = 0; i < 4; i++) f(e.c[i]); }
+    void efs(const std::vector<Fp4>& v) { u32((uint32_t)v.size()); for (auto& e : v) ef(e); }
+    void digest_monty(const uint32_t* d) { for (int i = 0; i < 8; i++) f(Fp::raw(d[i])); }
+    void words(const uint32_t* w, size_t n) { for (size_t i = 0; i < n; i++) u32(w[i]); }  // already canonical
+};
+
+struct RoundMat {
+    const b2s_matrix* lde;
+    unsigned log_n;                          // log2 of the trace height
+    std::vector<Fp4> points;
+    std::vector<std::vector<Fp4>> values;    // [point][column]
+};
+struct Round {
+    const b2s_pcs_data* pcs;
+    std::vector<RoundMat> mats;              // caller order
+};
+
+static Fp4 fp4_from(Fp a) { return Fp4(a); }
+static Fp4 fp4_pow2k(Fp4 x, unsigned k) { for (unsigned i = 0; i < k; i++) x = x * x; return x; }
+
+static void upload_ef_powers(b2s_engine* e, uint32_t* d, const Fp4& base, size_t count) {
+    std::vector<uint32_t> h(count * 4);
+    Fp4 p = Fp4::one();
+    for (size_t i = 0; i < count; i++) {
+        for (int c = 0; c < 4; c++) h[4 * i + c] = p.c[c].v;
+        p = p * base;
+    }
+    B2_CUDA(cudaMemcpyAsync(d, h.data(), h.size() * 4, cudaMemcpyHostToDevice, e->stream));
+    B2_CUDA(cudaStreamSynchronize(e->stream));  // h is a stack-lifetime buffer
+}
+
+// ---- prove -------------------------------------------------------------------------------------------------------------------
+void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_airs, std::vector<uint8_t>& out) {
+    B2_REQUIRE(pk->eng == e, B2S_ERR_BAD_ARG, "prove: key was loaded on a different engine");
+    StageScope total_scope(e, ST_PROVE);
+    Scratch scratch(e);
+    const unsigned b = e->params.log_blowup;
+    HostChallenger ch;
+    std::vector<unsigned> logn(n_airs);
+    std::vector<const AirKeyDev*> keys(n_airs);
+    unsigned log_max_height = 0;
+    for (size_t i = 0; i < n_airs; i++) {
+        const b2s_air_ctx& a = airs[i];
+        B2_REQUIRE(a.air_id < pk->airs.size(), B2S_ERR_BAD_ARG, "prove: air_id out of range");
+        B2_REQUIRE(i == 0 || a.air_id > airs[i - 1].air_id, B2S_ERR_BAD_ARG, "prove: air ids must be strictly increasing");
+        const AirKeyDev& k = pk->airs[a.air_id];
+        keys[i] = &k;
+        B2_REQUIRE(a.n_public_values == k.num_pv && (k.num_pv == 0 || a.public_values), B2S_ERR_SHAPE, "prove: public value count");
+        B2_REQUIRE(a.n_cached == k.cached_widths.size(), B2S_ERR_SHAPE, "prove: cached main count");
+        B2_REQUIRE((k.width_common != 0) == (a.common_main != nullptr), B2S_ERR_SHAPE, "prove: common main presence");
+        uint64_t h = 0;
+        if (a.common_main) {
+            B2_REQUIRE(a.common_main->width == k.width_common, B2S_ERR_SHAPE, "prove: common main width");
+            h = a.common_main->height;
+        }
+        for (uint32_t p = 0; p < a.n_cached; p++) {
+            const b2s_pcs_data* c = a.cached[p];
+            B2_REQUIRE(c && c->mats.size() == 1 && c->mats[0]->width == k.cached_widths[p], B2S_ERR_SHAPE, "prove: cached main shape");
+            uint64_t hc = c->mats[0]->height >> b;
+            B2_REQUIRE(h == 0 || h == hc, B2S_ERR_SHAPE, "prove: partition heights differ");
+            h = hc;
+        }
+        B2_REQUIRE(h && is_pow2(h), B2S_ERR_SHAPE, "prove: trace height must be a power of two");
+        logn[i] = log2_exact(h);
+        B2_REQUIRE(logn[i] + b <= TWO_ADICITY, B2S_ERR_SHAPE, "prove: trace too tall for this blowup");
+        B2_REQUIRE(!k.width_prep || k.prep_log_height == logn[i], B2S_ERR_SHAPE, "prove: preprocessed trace height mismatch");
+        log_max_height = std::max(log_max_height, logn[i]);
+    }
+    // transcript prefix (stark/mod.rs:140-149, 231-238, 247-254)
+    ch.observe_digest(pk->pre_hash);
+    ch.observe_canonical((uint32_t)n_airs);
+    for (size_t i = 0; i < n_airs; i++) ch.observe_canonical(airs[i].air_id);
+    for (size_t i = 0; i < n_airs; i++)
+        for (uint32_t j = 0; j < airs[i].n_public_values; j++) {
+            B2_REQUIRE(airs[i].public_values[j] < P, B2S_ERR_BAD_ARG, "prove: non-canonical public value");
+            ch.observe_canonical(airs[i].public_values[j]);
+        }
+    for (size_t i = 0; i < n_airs; i++) if (keys[i]->width_prep) ch.observe_digest(keys[i]->prep_commit);
+    // main commitments: cached mains in (AIR, partition) order, then one tree over all common mains
+    std::vector<std::array<uint32_t, 8>> main_commits;
+    for (size_t i = 0; i < n_airs; i++)
+        for (uint32_t p = 0; p < airs[i].n_cached; p++) {
+            std::array<uint32_t, 8> r;
+            root_monty(e, airs[i].cached[p], r.data());
+            main_commits.push_back(r);
+        }
+    std::vector<const b2s_matrix*> commons;
+    std::vector<size_t> common_of;
+    for (size_t i = 0; i < n_airs; i++) if (airs[i].common_main) { commons.push_back(airs[i].common_main); common_of.push_back(i); }
+    B2_REQUIRE(!commons.empty(), B2S_ERR_SHAPE, "prove: no common main trace");
+    b2s_pcs_data* common_pcs = commit_matrices(e, commons.data(), nullptr, commons.size());
+    scratch.pcs.push_back(common_pcs);
+    {
+        std::array<uint32_t, 8> r;
+        root_monty(e, common_pcs, r.data());
+        main_commits.push_back(r);
+    }
+    for (auto& c : main_commits) ch.observe_digest(c.data());
+    for (size_t i = 0; i < n_airs; i++) ch.observe_canonical(logn[i]);
+    const Fp4 alpha = ch.sample_ext();
+
+    // ---- quotient (stark/mod.rs:366-416; fri/domain.rs:59-155)
+    std::vector<b2s_matrix> chunk_views;   // one N x 4 matrix per (AIR, chunk)
+    std::vector<Fp> chunk_shifts;
+    std::vector<unsigned> chunk_logn;
+    {
+        StageScope qs(e, ST_QUOTIENT);
+        uint32_t max_c = 1;
+        for (auto* k : keys) max_c = std::max(max_c, k->num_constraints);
+        uint32_t* d_apow = scratch.words((size_t)max_c * 4);
+        upload_ef_powers(e, d_apow, alpha, max_c);
+        size_t total_chunks = 0;
+        for (auto* k : keys) total_chunks += (size_t)1 << k->log_qd;
+        chunk_views.reserve(total_chunks);
+        for (size_t i = 0; i < n_airs; i++) {
+            const AirKeyDev& k = *keys[i];
+            const unsigned n = logn[i], lq = k.log_qd;
+            const uint64_t N = (uint64_t)1 << n;
+            // column pointer table: [preprocessed][cached parts][common]
+            std::vector<const uint32_t*> cols;
+            auto push_cols = [&](const b2s_matrix* m) { for (uint64_t c = 0; c < m->width; c++) cols.push_back(m->d + c * m->height); };
+            if (k.width_prep) push_cols(k.prep_pcs->mats[0]);
+            for (uint32_t p = 0; p < airs[i].n_cached; p++) push_cols(airs[i].cached[p]->mats[0]);
+            if (k.width_common) {
+                size_t pos = std::find(common_of.begin(), common_of.end(), i) - common_of.begin();
+                push_cols(common_pcs->mats[pos]);
+            }
+            const uint32_t** d_cols = (const uint32_t**)scratch.bytes(std::max<size_t>(cols.size(), 1) * sizeof(void*));
+            uint32_t* d_pv = scratch.words(std::max<uint32_t>(k.num_pv, 1));
+            std::vector<uint32_t> pv(std::max<uint32_t>(k.num_pv, 1), 0);
+            for (uint32_t j = 0; j < k.num_pv; j++) pv[j] = Fp::from_canonical(airs[i].public_values[j]).v;
+            if (!cols.empty()) B2_CUDA(cudaMemcpyAsync(d_cols, cols.data(), cols.size() * sizeof(void*), cudaMemcpyHostToDevice, e->stream));
+            B2_CUDA(cudaMemcpyAsync(d_pv, pv.data(), pv.size() * 4, cudaMemcpyHostToDevice, e->stream));
+            B2_CUDA(cudaStreamSynchronize(e->stream));
+            QuotientParams qp{};
+            qp.program = k.d_program; qp.prog_len = (uint32_t)k.program.size();
+            qp.cols = d_cols; qp.publics = d_pv; qp.alpha_pows = d_apow;
+            qp.out = scratch.words(((size_t)4 << lq) * N);
+            qp.n = n; qp.b = b; qp.lq = lq;
+            const Fp gq = two_adic_generator(n + lq);
+            qp.gq = gq.v;
+            qp.ginv = fp_inv(two_adic_generator(n)).v;
+            // x^N on the quotient domain: (g * gq^k)^N = g^N * w_qd^(k mod qd)
+            const Fp gN = fp_pow(Fp::raw(M_GENERATOR), N);
+            const Fp wq = two_adic_generator(lq);
+            Fp wpow = Fp::one();
+            for (uint32_t j = 0; j < (1u << lq); j++) {
+                Fp zh = gN * wpow - Fp::one();
+                qp.zh[j] = zh.v;
+                qp.inv_zh[j] = fp_inv(zh).v;
+                wpow *= wq;
+            }
+            launch_quotient(e, k.num_slots, qp);
+            Fp sh = Fp::raw(M_GENERATOR);
+            for (uint32_t j = 0; j < (1u << lq); j++) {
+                b2s_matrix v;
+                v.eng = e; v.d = qp.out + (size_t)j * 4 * N; v.height = N; v.width = 4; v.owned = false;
+                chunk_views.push_back(v);
+                chunk_shifts.push_back(sh);
+                chunk_logn.push_back(n);
+                sh *= gq;
+            }
+        }
+    }
+    std::vector<const b2s_matrix*> chunk_ptrs;
+    for (auto& v : chunk_views) chunk_ptrs.push_back(&v);
+    b2s_pcs_data* quotient_pcs = commit_matrices(e, chunk_ptrs.data(), chunk_shifts.data(), chunk_ptrs.size());
+    scratch.pcs.push_back(quotient_pcs);
+    std::array<uint32_t, 8> quotient_commit;
+    root_monty(e, quotient_pcs, quotient_commit.data());
+    ch.observe_digest(quotient_commit.data());
+    const Fp4 zeta = ch.sample_ext();
+
+    // ---- opening rounds: [preprocessed per AIR][cached mains][common main][quotient]  (stark/mod.rs:418-698)
+    StageScope open_scope(e, ST_OPENING);
+    std::vector<Round> rounds;
+    auto trace_mat = [&](const b2s_matrix* lde, size_t i) {
+        return RoundMat{lde, logn[i], {zeta, zeta * two_adic_generator(logn[i])}, {}};
+    };
+    for (size_t i = 0; i < n_airs; i++)
+        if (keys[i]->width_prep) rounds.push_back(Round{keys[i]->prep_pcs, {trace_mat(keys[i]->prep_pcs->mats[0], i)}});
+    const size_t first_cached = rounds.size();
+    for (size_t i = 0; i < n_airs; i++)
+        for (uint32_t p = 0; p < airs[i].n_cached; p++)
+            rounds.push_back(Round{airs[i].cached[p], {trace_mat(airs[i].cached[p]->mats[0], i)}});
+    const size_t common_round = rounds.size();
+    {
+        Round r{common_pcs, {}};
+        for (size_t m = 0; m < common_of.size(); m++) r.mats.push_back(trace_mat(common_pcs->mats[m], common_of[m]));
+        rounds.push_back(r);
+    }
+    const size_t quotient_round = rounds.size();
+    {
+        Round r{quotient_pcs, {}};
+        for (size_t m = 0; m < chunk_views.size(); m++) r.mats.push_back(RoundMat{quotient_pcs->mats[m], chunk_logn[m], {zeta}, {}});
+        rounds.push_back(r);
+    }
+    // (i) out-of-domain values. Weights are shared by all matrices of one trace height: index 0 = zeta, 1 = zeta * w_n.
+    {
+        std::map<unsigned, std::array<uint32_t*, 2>> weights;
+        auto get_weights = [&](unsigned n, int which, const Fp4& z) {
+            auto& slot = weights[n];
+            if (!slot[which]) {
+                slot[which] = scratch.words((size_t)4 << n);
+                const uint32_t N = 1u << n;
+                bary_weights_kernel<<<(N + 127) / 128, 128, 0, e->stream>>>(slot[which], n, z, two_adic_generator(n).v);
+                B2_CHECK_LAUNCH();
+                e->launches[3]++;
+            }
+            return slot[which];
+        };
+        struct Job { size_t r, m, p; uint32_t splits; size_t off; };
+        std::vector<Job> jobs;
+        size_t partial_words = 0;
+        for (size_t r = 0; r < rounds.size(); r++)
+            for (size_t m = 0; m < rounds[r].mats.size(); m++)
+                for (size_t p = 0; p < rounds[r].mats[m].points.size(); p++) {
+                    const RoundMat& rm = rounds[r].mats[m];
+                    uint32_t splits = (uint32_t)std::min<uint64_t>(64, std::max<uint64_t>(1, ((uint64_t)1 << rm.log_n) / 4096));
+                    jobs.push_back(Job{r, m, p, splits, partial_words});
+                    partial_words += (size_t)rm.lde->width * splits * 4;
+                }
+        uint32_t* d_partial = scratch.words(partial_words);
+        for (auto& j : jobs) {
+            const RoundMat& rm = rounds[j.r].mats[j.m];
+            uint32_t* w = get_weights(rm.log_n, (int)j.p, rm.points[j.p]);
+            bary_dot_kernel<<<dim3((unsigned)rm.lde->width, j.splits), DOT_THREADS, 0, e->stream>>>(rm.lde->d, rm.lde->height, w,
+                                                                                                    rm.log_n, d_partial + j.off);
+            B2_CHECK_LAUNCH();
+            e->launches[3]++;
+        }
+        std::vector<uint32_t> partial(partial_words);
+        B2_CUDA(cudaMemcpyAsync(partial.data(), d_partial, partial_words * 4, cudaMemcpyDeviceToHost, e->stream));
+        B2_CUDA(cudaStreamSynchronize(e->stream));
+        const Fp ginv = fp_inv(Fp::raw(M_GENERATOR));
+        for (auto& j : jobs) {
+            RoundMat& rm = rounds[j.r].mats[j.m];
+            const Fp ninv = fp_inv(Fp::from_canonical((uint32_t)(((uint64_t)1 << rm.log_n) % P)));
+            const Fp4 scale = (fp4_pow2k(rm.points[j.p] * ginv, rm.log_n) - Fp::one()) * ninv;
+            std::vector<Fp4> vals(rm.lde->width);
+            for (uint64_t c = 0; c < rm.lde->width; c++) {
+                Fp4 s = Fp4::zero();
+                for (uint32_t sp = 0; sp < j.splits; sp++)
+                    for (int k = 0; k < 4; k++) s.c[k] += Fp::raw(partial[j.off + (c * j.splits + sp) * 4 + k]);
+                vals[c] = s * scale;
+            }
+            if (rm.values.size() <= j.p) rm.values.resize(j.p + 1);
+            rm.values[j.p] = std::move(vals);
+        }
+    }
+    // observed round -> matrix -> point -> column (two_adic_pcs.rs:63-95)
+    for (auto& r : rounds)
+        for (auto& m : r.mats)
+            for (auto& pt : m.values)
+                for (auto& v : pt) ch.observe_ext(v);
+    const Fp4 fri_alpha = ch.sample_ext();
+
+    // (ii) reduced openings per LDE log height; the alpha power runs on per height (two_adic_pcs.rs:175-196, 313-325)
+    const unsigned L = log_max_height + b;
+    std::map<unsigned, uint32_t*> ro;
+    {
+        uint64_t max_w = 1;
+        for (auto& r : rounds) for (auto& m : r.mats) max_w = std::max<uint64_t>(max_w, m.lde->width);
+        uint32_t* d_apow = scratch.words((max_w + 1) * 4);
+        upload_ef_powers(e, d_apow, fri_alpha, max_w + 1);
+        std::map<unsigned, Fp4> alpha_pow;
+        for (auto& r : rounds)
+            for (auto& m : r.mats) {
+                const unsigned h = m.log_n + b;
+                if (!ro.count(h)) {
+                    ro[h] = scratch.words((size_t)4 << h);
+                    B2_CUDA(cudaMemsetAsync(ro[h], 0, (size_t)16 << h, e->stream));
+                    alpha_pow[h] = Fp4::one();
+                }
+                ReducedParams rp{};
+                rp.mat = m.lde->d; rp.width = (uint32_t)m.lde->width; rp.h = h;
+                rp.alpha_pows = d_apow; rp.ro = ro[h]; rp.npoints = (uint32_t)m.points.size();
+                rp.wh = two_adic_generator(h).v;
+                Fp4 aw = Fp4::one();
+                for (uint64_t t = 0; t < m.lde->width; t++) aw = aw * fri_alpha;
+                for (size_t j = 0; j < m.points.size(); j++) {
+                    Fp4 cz = Fp4::zero(), ap = Fp4::one();
+                    for (auto& v : m.values[j]) { cz += v * ap; ap = ap * fri_alpha; }
+                    rp.z[j] = m.points[j]; rp.cz[j] = cz; rp.coef[j] = alpha_pow[h];
+                    alpha_pow[h] = alpha_pow[h] * aw;
+                }
+                reduced_open_kernel<<<((1u << h) + 127) / 128, 128, 0, e->stream>>>(rp);
+                B2_CHECK_LAUNCH();
+                e->launches[3]++;
+            }
+    }
+
+    // (iii) FRI commit phase (two_adic_pcs.rs:111-130; fri/mod.rs:139-165)
+    std::vector<b2s_pcs_data*> fri_trees;
+    std::vector<b2s_matrix*> fri_leaves;
+    std::vector<std::array<uint32_t, 8>> fri_commits;
+    uint32_t* folded = ro[L];
+    struct LeafGuard {
+        std::vector<b2s_matrix*>& v;
+        ~LeafGuard() { for (auto* m : v) b2s_matrix_free(m); }
+    } leaf_guard{fri_leaves};
+    for (unsigned lh = L; lh > b; lh--) {
+        const uint32_t R = 1u << (lh - 1);
+        b2s_matrix* leaf = new_matrix(e, R, 8);
+        fri_leaves.push_back(leaf);
+        fri_pack_kernel<<<(R + 127) / 128, 128, 0, e->stream>>>(folded, leaf->d, R);
+        B2_CHECK_LAUNCH();
+        e->launches[3]++;
+        b2s_pcs_data* t = new b2s_pcs_data();
+        t->eng = e;
+        b2s_matrix* view = new b2s_matrix(*leaf);
+        view->owned = false;
+        t->mats.push_back(view);
+        t->owns.push_back(true);
+        scratch.pcs.push_back(t);
+        mmcs_build(e, t);
+        fri_trees.push_back(t);
+        std::array<uint32_t, 8> root;
+        root_monty(e, t, root.data());
+        fri_commits.push_back(root);
+        ch.observe_digest(root.data());
+        const Fp4 beta = ch.sample_ext();
+        uint32_t* next = scratch.words((size_t)4 * R);
+        auto it = ro.find(lh - 1);
+        fri_fold_kernel<<<(R + 127) / 128, 128, 0, e->stream>>>(folded, next, it != ro.end() ? it->second : nullptr, lh,
+                                                               two_adic_generator(lh).v, beta, beta * beta);
+        B2_CHECK_LAUNCH();
+        e->launches[3]++;
+        folded = next;
+    }
+    // final polynomial: log_final_poly_len = 0, the constant (two_adic_pcs.rs:52-58)
+    Fp4 final_poly;
+    {
+        const uint32_t len = 1u << b;
+        std::vector<uint32_t> h((size_t)4 * len);
+        B2_CUDA(cudaMemcpyAsync(h.data(), folded, h.size() * 4, cudaMemcpyDeviceToHost, e->stream));
+        B2_CUDA(cudaStreamSynchronize(e->stream));
+        for (int c = 0; c < 4; c++) final_poly.c[c] = Fp::raw(h[(size_t)c * len]);
+        for (uint32_t i = 1; i < len; i++)
+            for (int c = 0; c < 4; c++)
+                B2_REQUIRE(h[(size_t)c * len + i] == h[(size_t)c * len], B2S_ERR_INTERNAL, "fri: folded polynomial is not constant");
+    }
+    ch.observe_ext(final_poly);
+    // (iv) proof of work: minimum witness (duplex.rs:122-130)
+    Fp pow_witness;
+    {
+        const unsigned bits = e->params.proof_of_work_bits;
+        B2_REQUIRE(bits < 31, B2S_ERR_BAD_ARG, "prove: proof_of_work_bits too large");
+        uint32_t* d_res = scratch.words(1);
+        PowParams pp{};
+        for (int i = 0; i < 16; i++) pp.st[i] = ch.st[i].v;
+        pp.in_ptr = (uint32_t)ch.in_ptr;
+        pp.bits = bits;
+        uint32_t found = 0xFFFFFFFFu;
+        const uint32_t batch = 1u << 20;
+        for (uint64_t base = 0; base < P && found == 0xFFFFFFFFu; base += batch) {
+            pp.base = (uint32_t)base;
+            B2_CUDA(cudaMemsetAsync(d_res, 0xFF, 4, e->stream));
+            pow_grind_kernel<<<batch / 128, 128, 0, e->stream>>>(pp, batch, d_res);
+            B2_CHECK_LAUNCH();
+            e->launches[3]++;
+            e->permutations += batch;
+            B2_CUDA(cudaMemcpyAsync(&found, d_res, 4, cudaMemcpyDeviceToHost, e->stream));
+            B2_CUDA(cudaStreamSynchronize(e->stream));
+        }
+        B2_REQUIRE(found != 0xFFFFFFFFu, B2S_ERR_INTERNAL, "prove: no proof-of-work witness exists");
+        pow_witness = Fp::from_canonical(found);
+        B2_REQUIRE(ch.check_witness(bits, pow_witness), B2S_ERR_INTERNAL, "prove: device proof-of-work witness rejected by the host transcript");
+    }
+    // (v) queries: every opening of every query in one gather (two_adic_pcs.rs:170-372; fri/mod.rs:72-135)
+    const unsigned nq = e->params.num_queries;
+    std::vector<uint32_t> indices(nq);
+    for (auto& ix : indices) ix = ch.sample_bits(L);
+    std::vector<OpenDesc> descs;
+    size_t off = 0;
+    auto push = [&](const uint32_t* base, uint64_t stride, uint64_t row, uint32_t count) {
+        B2_REQUIRE(off + count < 0xFFFFFFFFull, B2S_ERR_INTERNAL, "prove: opening buffer too large");
+        descs.push_back(OpenDesc{base, stride, row, count, (uint32_t)off});
+        off += count;
+    };
+    for (uint32_t ix : indices) {
+        for (auto& r : rounds) {
+            const b2s_pcs_data* d = r.pcs;
+            const uint64_t idx = (uint64_t)ix >> (L - d->log_max_height);
+            for (auto* m : d->mats) push(m->d, m->height, idx >> (d->log_max_height - log2_exact(m->height)), (uint32_t)m->width);
+            for (unsigned l = 0; l < d->log_max_height; l++) push(d->layers[l], d->layer_nodes[l], (idx >> l) ^ 1, 8);
+        }
+        for (size_t i = 0; i < fri_trees.size(); i++) {
+            const b2s_pcs_data* d = fri_trees[i];
+            const uint64_t pos = (uint64_t)ix >> i, pair = pos >> 1;
+            // sibling value: the other element of the leaf pair = 4 columns of the leaf matrix
+            const b2s_matrix* leaf = d->mats[0];
+            push(leaf->d + (uint64_t)4 * ((pos & 1) ^ 1) * leaf->height, leaf->height, pair, 4);
+            for (unsigned l = 0; l < d->log_max_height; l++) push(d->layers[l], d->layer_nodes[l], (pair >> l) ^ 1, 8);
+        }
+    }
+    std::vector<uint32_t> opened(off);
+    gather_rows(e, descs, off, opened.data());
+
+    // ---- proof bytes (crates/sdk/src/codec.rs:92-330) -------------------------------------------------------------------
+    out.clear();
+    ByteWriter w{out};
+    w.u32(1);  // CODEC_VERSION
+    w.u32((uint32_t)main_commits.size());
+    for (auto& c : main_commits) w.digest_monty(c.data());
+    w.u32(0);  // after_challenge commitments: no challenge phase
+    w.digest_monty(quotient_commit.data());
+    // FriProof
+    w.u32((uint32_t)fri_commits.size());
+    for (auto& c : fri_commits) w.digest_monty(c.data());
+    w.u32(nq);
+    {
+        size_t pos = 0;
+        for (unsigned q = 0; q < nq; q++) {
+            w.u32((uint32_t)rounds.size());
+            for (auto& r : rounds) {
+                const b2s_pcs_data* d = r.pcs;
+                w.u32((uint32_t)d->mats.size());
+                for (auto* m : d->mats) {
+                    w.u32((uint32_t)m->width);
+                    w.words(opened.data() + pos, m->width);
+                    pos += m->width;
+                }
+                w.u32(d->log_max_height);
+                w.words(opened.data() + pos, (size_t)8 * d->log_max_height);
+                pos += (size_t)8 * d->log_max_height;
+            }
+            w.u32((uint32_t)fri_trees.size());
+            for (auto* d : fri_trees) {
+                w.words(opened.data() + pos, 4);
+                pos += 4;
+                w.u32(d->log_max_height);
+                w.words(opened.data() + pos, (size_t)8 * d->log_max_height);
+                pos += (size_t)8 * d->log_max_height;
+            }
+        }
+    }
+    w.u32(1);
+    w.ef(final_poly);
+    w.f(pow_witness);
+    // OpenedValues
+    auto adjacent = [&](const RoundMat& m) { w.efs(m.values[0]); w.efs(m.values[1]); };
+    w.u32((uint32_t)first_cached);
+    for (size_t r = 0; r < first_cached; r++) adjacent(rounds[r].mats[0]);
+    w.u32((uint32_t)(common_round - first_cached + 1));
+    for (size_t r = first_cached; r < common_round; r++) { w.u32(1); adjacent(rounds[r].mats[0]); }
+    w.u32((uint32_t)rounds[common_round].mats.size());
+    for (auto& m : rounds[common_round].mats) adjacent(m);
+    w.u32(0);  // after_challenge phases
+    w.u32((uint32_t)n_airs);
+    {
+        size_t m = 0;
+        for (size_t i = 0; i < n_airs; i++) {
+            const uint32_t qd = 1u << keys[i]->log_qd;
+            w.u32(qd);
+            for (uint32_t j = 0; j < qd; j++) w.efs(rounds[quotient_round].mats[m++].values[0]);
+        }
+    }
+    // per_air
+    w.u32((uint32_t)n_airs);
+    for (size_t i = 0; i < n_airs; i++) {
+        w.u32(airs[i].air_id);
+        w.u32(1u << logn[i]);
+        w.u32(0);  // exposed_values_after_challenge
+        w.u32(airs[i].n_public_values);
+        w.words(airs[i].public_values, airs[i].n_public_values);
+    }
+    out.push_back(0);       // RapPhaseSeqKind::FriLogUp
+    w.u32(0xFFFFFFFFu);     // no logup witness
+    B2_CUDA(cudaStreamSynchronize(e->stream));
+}
+
+}  // namespace b2

@@ -127,19 +127,27 @@ void fill_synthetic(b2s_engine* e, uint32_t* d, uint64_t height, uint64_t width,
 }
 
 // ---- Merkle opening gather ---------------------------------------------------------------------------
-struct OpenDesc {
-    const uint32_t* base;  // column 0 of a matrix, or plane 0 of a digest layer
-    uint64_t stride;       // height (matrix) or node count (layer)
-    uint64_t row;
-    uint32_t count;        // width or 8
-    uint32_t out_off;
-};
 __global__ void gather_kernel(const OpenDesc* descs, uint32_t ndesc, uint32_t* out) {
     uint32_t di = blockIdx.x;
     if (di >= ndesc) return;
     OpenDesc d = descs[di];
     for (uint32_t c = threadIdx.x; c < d.count; c += blockDim.x)
         out[d.out_off + c] = Fp::raw(d.base[(uint64_t)c * d.stride + d.row]).to_canonical();
+}
+// every descriptor copies `count` strided words (a matrix row or a digest) to out[out_off..], canonical form;
+// one launch and one device-to-host copy for the whole list
+void gather_rows(b2s_engine* e, const std::vector<OpenDesc>& descs, size_t total_words, uint32_t* h_out) {
+    if (descs.empty()) return;
+    OpenDesc* dd = (OpenDesc*)e->dmalloc(descs.size() * sizeof(OpenDesc));
+    uint32_t* dout = (uint32_t*)e->dmalloc(total_words * 4);
+    B2_CUDA(cudaMemcpyAsync(dd, descs.data(), descs.size() * sizeof(OpenDesc), cudaMemcpyHostToDevice, e->stream));
+    gather_kernel<<<(unsigned)descs.size(), 128, 0, e->stream>>>(dd, (uint32_t)descs.size(), dout);
+    B2_CHECK_LAUNCH();
+    e->launches[3]++;
+    B2_CUDA(cudaMemcpyAsync(h_out, dout, total_words * 4, cudaMemcpyDeviceToHost, e->stream));
+    B2_CUDA(cudaStreamSynchronize(e->stream));
+    e->dfree(dd, descs.size() * sizeof(OpenDesc));
+    e->dfree(dout, total_words * 4);
 }
 void gather_open(b2s_engine* e, const b2s_pcs_data* d, uint64_t index, uint32_t* h_rows, uint32_t* h_proof) {
     B2_REQUIRE(index < ((uint64_t)1 << d->log_max_height), B2S_ERR_BAD_ARG, "open: index out of range");
@@ -155,19 +163,10 @@ void gather_open(b2s_engine* e, const b2s_pcs_data* d, uint64_t index, uint32_t*
         descs.push_back(OpenDesc{d->layers[l], d->layer_nodes[l], (index >> l) ^ 1, 8u, off});
         off += 8;
     }
-    OpenDesc* dd = (OpenDesc*)e->dmalloc(descs.size() * sizeof(OpenDesc));
-    uint32_t* dout = (uint32_t*)e->dmalloc((size_t)off * 4);
-    B2_CUDA(cudaMemcpyAsync(dd, descs.data(), descs.size() * sizeof(OpenDesc), cudaMemcpyHostToDevice, e->stream));
-    gather_kernel<<<(unsigned)descs.size(), 128, 0, e->stream>>>(dd, (uint32_t)descs.size(), dout);
-    B2_CHECK_LAUNCH();
-    e->launches[3]++;
     std::vector<uint32_t> tmp(off);
-    B2_CUDA(cudaMemcpyAsync(tmp.data(), dout, (size_t)off * 4, cudaMemcpyDeviceToHost, e->stream));
-    B2_CUDA(cudaStreamSynchronize(e->stream));
+    gather_rows(e, descs, off, tmp.data());
     if (h_rows) memcpy(h_rows, tmp.data(), (size_t)rows_words * 4);
     if (h_proof) memcpy(h_proof, tmp.data() + rows_words, (size_t)(off - rows_words) * 4);
-    e->dfree(dd, descs.size() * sizeof(OpenDesc));
-    e->dfree(dout, (size_t)off * 4);
 }
 
 void download_layer(b2s_engine* e, const b2s_pcs_data* d, uint32_t level, uint32_t* h_out) {

@@ -141,6 +141,35 @@ class PcsData:
             pass
 
 
+class ProvingKey:
+    """Device-resident proving key (transport_pk_to_device; crates/vm/src/arch/vm.rs:382)."""
+
+    def __init__(self, engine, handle):
+        self._engine = engine
+        self._h = handle
+
+    def free(self):
+        if self._h:
+            self._engine._lib.b2s_pk_free(self._h)
+        self._h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+@dataclass
+class AirProvingContext:
+    """AirProvingContext{cached_mains, common_main, public_values} for one AIR (crates/vm/src/arch/vm.rs:588-599).
+    cached_mains are PcsData objects returned by device.commit([trace])."""
+    air_id: int
+    common_main: object = None
+    public_values: object = ()
+    cached_mains: tuple = ()
+
+
 class B2Device:
     """ProverDevice: TraceCommitter + DeviceDataTransporter (QuotientCommitter / OpeningProver: see prover)."""
 
@@ -230,6 +259,14 @@ class B2Device:
         pcs._keepalive = list(matrices)
         return root, pcs
 
+    def transport_pk_to_device(self, key_words):
+        """key_words: uint32 key blob (include/b2stark.h: b2s_pk_load)."""
+        e = self._e
+        a = np.ascontiguousarray(key_words, dtype=np.uint32)
+        h = C.c_void_p()
+        e._check(e._lib.b2s_pk_load(e._h, a.ctypes.data, a.size, C.byref(h)))
+        return ProvingKey(e, h)
+
     def poseidon2_permute(self, states):
         e = self._e
         a = np.ascontiguousarray(states, dtype=np.uint32).reshape(-1, 16).copy()
@@ -259,6 +296,28 @@ class B2Engine:
 
     def fri_params(self):
         return self._params
+
+    def prove(self, pk, ctx):
+        """StarkEngine::prove(&pk, ctx) -> proof bytes in the reference wire format (crates/sdk/src/codec.rs).
+        ctx: list of AirProvingContext in strictly increasing air_id."""
+        n = len(ctx)
+        arr = (_lib.AirCtx * n)()
+        keep = []
+        for i, a in enumerate(ctx):
+            pv = np.ascontiguousarray(a.public_values, dtype=np.uint32)
+            cached = (C.c_void_p * max(1, len(a.cached_mains)))(*[c._h for c in a.cached_mains])
+            keep += [pv, cached]
+            arr[i].air_id = a.air_id
+            arr[i].n_cached = len(a.cached_mains)
+            arr[i].cached = C.cast(cached, C.POINTER(C.c_void_p))
+            arr[i].common_main = a.common_main._h if a.common_main is not None else None
+            arr[i].public_values = pv.ctypes.data_as(C.POINTER(C.c_uint32))
+            arr[i].n_public_values = pv.size
+        out, ln = C.c_void_p(), C.c_size_t()
+        self._check(self._lib.b2s_prove(self._h, pk._h, arr, n, C.byref(out), C.byref(ln)))
+        data = C.string_at(out.value, ln.value)
+        self._lib.b2s_free(out)
+        return data
 
     def device(self):
         return self._device
