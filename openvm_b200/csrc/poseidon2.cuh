@@ -20,11 +20,26 @@ static __constant__ uint32_t P2C_EXT[8][16] = B2_P2_EXT_ALL;
 static __constant__ uint32_t P2C_PARTIAL[13] = B2_P2_PARTIAL;
 static __constant__ uint32_t P2C_DIAG[16] = B2_P2_DIAG;
 
+// Montgomery product whose  m = lo * (-p^-1)  step runs on the ALU pipe as shifts/adds instead of a 4-cycle IMAD
+// on fmaheavy: -p^-1 = 2^31 - 2^27 - 1 (mod 2^32). Used for a fraction of the S-box products to balance the two
+// pipes (ncu: fmaheavy 87 % busy, alu 53 %, profiles/r1c).
+B2_D Fp mul_alu(Fp a, Fp b) {
+    const uint64_t t = (uint64_t)a.v * b.v;
+    const uint32_t lo = (uint32_t)t;
+    uint32_t m;  // inline PTX so the compiler does not fold the shifts back into a multiply by 0x77ffffff
+    asm("{\n\t.reg .u32 a, b;\n\tshl.b32 a, %1, 31;\n\tshl.b32 b, %1, 27;\n\tsub.u32 a, a, b;\n\tsub.u32 %0, a, %1;\n\t}"
+        : "=r"(m) : "r"(lo));
+    const uint64_t u = t + (uint64_t)m * P;
+    const uint32_t r = (uint32_t)(u >> 32);
+    const uint32_t s = r - P;
+    return Fp::raw(s < r ? s : r);
+}
+template <int MASK>
 B2_D Fp sbox7(Fp x) {
-    Fp x2 = x * x;
-    Fp x3 = x2 * x;
-    Fp x4 = x2 * x2;
-    return x3 * x4;
+    Fp x2 = (MASK & 1) ? mul_alu(x, x) : x * x;
+    Fp x3 = (MASK & 2) ? mul_alu(x2, x) : x2 * x;
+    Fp x4 = (MASK & 4) ? mul_alu(x2, x2) : x2 * x2;
+    return (MASK & 8) ? mul_alu(x3, x4) : x3 * x4;
 }
 
 // [[2,3,1,1],[1,2,3,1],[1,1,2,3],[3,1,1,2]] on four lanes: 7 additions + 2 doublings
@@ -88,6 +103,13 @@ B2_D void p2_internal(Fp (&s)[16]) {
 // (E external layer, S_r add-constants + x^7 on all lanes, P partial round). Loops are kept rolled on purpose:
 // fully unrolled, one permutation is ~100 KB of SASS, which thrashes the instruction cache (ncu: stall
 // no_instruction dominant, profiles/r1a_ncu_full_summary.md); rolled it is ~9 KB.
+#ifndef B2_P2_FULL_MASK
+#define B2_P2_FULL_MASK 0
+#endif
+#ifndef B2_P2_PARTIAL_MASK
+#define B2_P2_PARTIAL_MASK 0
+#endif
+template <int FULL_MASK = B2_P2_FULL_MASK, int PARTIAL_MASK = B2_P2_PARTIAL_MASK>
 B2_D void poseidon2_permute(Fp (&s)[16]) {
 #pragma unroll 1
     for (int r = 0; r < 9; r++) {
@@ -95,13 +117,13 @@ B2_D void poseidon2_permute(Fp (&s)[16]) {
         if (r == 4) {
 #pragma unroll 1
             for (int q = 0; q < 13; q++) {
-                s[0] = sbox7(s[0] + Fp::raw(P2C_PARTIAL[q]));
+                s[0] = sbox7<PARTIAL_MASK>(s[0] + Fp::raw(P2C_PARTIAL[q]));
                 p2_internal(s);
             }
         }
         if (r < 8) {
 #pragma unroll
-            for (int i = 0; i < 16; i++) s[i] = sbox7(s[i] + Fp::raw(P2C_EXT[r][i]));
+            for (int i = 0; i < 16; i++) s[i] = sbox7<FULL_MASK>(s[i] + Fp::raw(P2C_EXT[r][i]));
         }
     }
 }

@@ -1,161 +1,3 @@
-"""Test AIRs and the key-blob writer (format: oracle/air.hpp header / include/b2stark.h b2s_pk_load).
-
-A tiny symbolic builder produces the SymbolicExpressionDag node list the way the reference's keygen does
-(topological order, constraints listed by node index). The AIRs mirror the reference's own fixtures:
-  * FibonacciAir(0, 1, n): 2 columns, 3 public values -- openvm_stark_sdk::dummy_airs::fib_air as used in
-    extensions/native/recursion/src/tests.rs:40,109,118 and benchmarks/prove/src/bin/verify_fibair.rs:38-39
-  * ChainAir: SURVEY.md 8(d) "chain AIR" (degree-3 constraints -> quotient degree 2), with optional preprocessed
-    and cached-main partitions so every kind of opening round is exercised.
-"""
-import numpy as np
-
-P = 2013265921
-(N_CONST, N_PREP, N_MAIN, N_PERM, N_PUBLIC, N_CHALLENGE, N_EXPOSED, N_FIRST, N_LAST, N_TRANS, N_ADD, N_SUB, N_NEG,
- N_MUL) = range(14)
-
-
-class Dag:
-    def __init__(self):
-        self.nodes = []
-        self.index = {}
-        self.constraints = []
-
-    def _node(self, kind, a=0, b=0, c=0):
-        key = (kind, a, b, c)
-        if key not in self.index:
-            self.index[key] = len(self.nodes)
-            self.nodes.append(key)
-        return Expr(self, self.index[key])
-
-    def const(self, v): return self._node(N_CONST, v % P)
-    def prep(self, col, offset=0): return self._node(N_PREP, col, offset)
-    def main(self, col, offset=0, part=0): return self._node(N_MAIN, col, offset, part)
-    def public(self, i): return self._node(N_PUBLIC, i)
-    def is_first(self): return self._node(N_FIRST)
-    def is_last(self): return self._node(N_LAST)
-    def is_transition(self): return self._node(N_TRANS)
-
-    def assert_zero(self, e):
-        self.constraints.append(e.i)
-
-
-class Expr:
-    def __init__(self, dag, i):
-        self.dag, self.i = dag, i
-
-    def _lift(self, o):
-        return o if isinstance(o, Expr) else self.dag.const(o)
-
-    def __add__(self, o): return self.dag._node(N_ADD, self.i, self._lift(o).i)
-    def __sub__(self, o): return self.dag._node(N_SUB, self.i, self._lift(o).i)
-    def __mul__(self, o): return self.dag._node(N_MUL, self.i, self._lift(o).i)
-    def __neg__(self): return self.dag._node(N_NEG, self.i)
-
-
-class Air:
-    """Key-side description of one AIR."""
-
-    def __init__(self, dag, width_common, num_pv, log_qd, cached_widths=(), prep=None):
-        self.dag, self.width_common, self.num_pv, self.log_qd = dag, width_common, num_pv, log_qd
-        self.cached_widths = list(cached_widths)
-        self.prep = prep            # (height, width) uint32 array or None
-        self.prep_commit = None     # 8 words, filled by the key builder
-
-
-def key_blob(airs, pre_hash=None, log_up_pow_bits=0):
-    """airs: list of Air (prep_commit set where prep is not None). Returns the uint32 word array."""
-    w = [0x4B503242, 1]
-    w += list(pre_hash if pre_hash is not None else range(101, 109))
-    w += [log_up_pow_bits, len(airs)]
-    for a in airs:
-        w += [0 if a.prep is None else a.prep.shape[1], len(a.cached_widths)] + a.cached_widths
-        w += [a.width_common, 0, a.log_qd, a.num_pv, 0]
-        if a.prep is not None:
-            assert a.prep_commit is not None
-            w += [int(x) for x in a.prep_commit]
-            w += [a.prep.shape[0].bit_length() - 1]
-            w += [int(x) for x in a.prep.reshape(-1)]
-        w += [len(a.dag.nodes)]
-        for n in a.dag.nodes:
-            w += list(n)
-        w += [len(a.dag.constraints)] + a.dag.constraints
-    return np.array(w, dtype=np.uint32)
-
-
-# ---------------------------------------------------------------------------------------------------------------
-def fibonacci_air():
-    d = Dag()
-    left, right = d.main(0), d.main(1)
-    nleft, nright = d.main(0, 1), d.main(1, 1)
-    a, b, x = d.public(0), d.public(1), d.public(2)
-    d.assert_zero(d.is_first() * (left - a))
-    d.assert_zero(d.is_first() * (right - b))
-    d.assert_zero(d.is_transition() * (nleft - right))
-    d.assert_zero(d.is_transition() * (nright - (left + right)))
-    d.assert_zero(d.is_last() * (right - x))
-    return Air(d, width_common=2, num_pv=3, log_qd=0)
-
-
-def fibonacci_trace(n, a=0, b=1):
-    t = np.zeros((n, 2), dtype=np.uint32)
-    for i in range(n):
-        t[i] = (a, b)
-        a, b = b, (a + b) % P
-    return t, np.array([t[0, 0], t[0, 1], t[n - 1, 1]], dtype=np.uint32)
-
-
-def chain_air(width, with_prep=False, cached_width=0, height=None, seed=0):
-    """Columns x_0..x_{W-1} of the common main: x_{j+2} = x_j * x_{j+1} + x_j (degree 2), a degree-3 booleanity
-    style constraint x_0 * (x_1 * x_2 - x_3 + x_0) = 0 ... kept satisfiable by construction: instead we use
-    y := x_j * x_{j+1} * x_{j+2} - x_{j+3}' terms only on columns defined that way. Layout:
-      common main: x_0, x_1 free per row; x_{j+2} = x_j * x_{j+1} + x_j for j + 2 < W - 1;
-                   last column c = x_0 * x_1 * x_2 (degree 3)
-      transition: next.x_0 = local.x_0 + 1 ; first row: x_0 = pv_0 ; last row: x_1 = pv_1
-      preprocessed (optional, width 2): p_0 = row index, p_1 = seed-derived; constraint x_1 = p_0 * p_1 + pv_0
-      cached main (optional): k columns, each = x_0 + column index (degree 1)
-    """
-    assert width >= 5
-    d = Dag()
-    x = [d.main(j, 0, 1 if cached_width else 0) for j in range(width)]
-    nx0 = d.main(0, 1, 1 if cached_width else 0)
-    for j in range(width - 3):
-        d.assert_zero(x[j + 2] - (x[j] * x[j + 1] + x[j]))
-    d.assert_zero(x[width - 1] - x[0] * x[1] * x[2])
-    d.assert_zero(d.is_transition() * (nx0 - x[0] - 1))
-    d.assert_zero(d.is_first() * (x[0] - d.public(0)))
-    d.assert_zero(d.is_last() * (x[1] - d.public(1)))
-    prep = None
-    if with_prep:
-        assert height is not None
-        rng = np.random.default_rng(1000 + seed)
-        prep = np.stack([np.arange(height, dtype=np.uint64) % P,
-                         rng.integers(0, P, size=height, dtype=np.uint64)], axis=1).astype(np.uint32)
-        d.assert_zero(x[1] - (d.prep(0) * d.prep(1) + d.public(0)))
-        # a rotated preprocessed access
-        d.assert_zero(d.is_transition() * (d.prep(0, 1) - d.prep(0) - 1))
-    for k in range(cached_width):
-        d.assert_zero(d.main(k, 0, 0) - x[0] - k)
-    return Air(d, width_common=width, num_pv=2, log_qd=1, cached_widths=[cached_width] if cached_width else [], prep=prep)
-
-
-def chain_trace(air, height, seed=0):
-    """Returns ([cached parts..., common], public values) satisfying chain_air."""
-    W = air.width_common
-    rng = np.random.default_rng(seed)
-    pv0 = int(rng.integers(0, P))
-    t = np.zeros((height, W), dtype=object)
-    x0 = (pv0 + np.arange(height)) % P
-    if air.prep is not None:
-        x1 = (air.prep[:, 0].astype(object) * air.prep[:, 1].astype(object) + pv0) % P
-    else:
-        x1 = rng.integers(0, P, size=height, dtype=np.uint64).astype(object)
-    t[:, 0], t[:, 1] = x0, x1
-    for j in range(W - 3):
-        t[:, j + 2] = (t[:, j] * t[:, j + 1] + t[:, j]) % P
-    t[:, W - 1] = (t[:, 0] * t[:, 1] * t[:, 2]) % P
-    common = t.astype(np.uint64).astype(np.uint32)
-    parts = []
-    for cw in air.cached_widths:
-        parts.append(np.stack([(common[:, 0].astype(np.uint64) + k) % P for k in range(cw)], axis=1).astype(np.uint32))
-    parts.append(common)
-    return parts, np.array([pv0, int(common[height - 1, 1])], dtype=np.uint32)
+"""Test-side alias of openvm_b200.airs (key-blob writer and sample AIRs)."""
+from openvm_b200.airs import *  # noqa: F401,F403
+from openvm_b200.airs import Air, Dag, key_blob, fibonacci_air, fibonacci_trace, chain_air, chain_trace  # noqa: F401
