@@ -34,6 +34,9 @@ class Dag:
     def prep(self, col, offset=0): return self._node(N_PREP, col, offset)
     def main(self, col, offset=0, part=0): return self._node(N_MAIN, col, offset, part)
     def public(self, i): return self._node(N_PUBLIC, i)
+    def perm(self, col, offset=0): return self._node(N_PERM, col, offset)
+    def challenge(self, i): return self._node(N_CHALLENGE, i)
+    def exposed(self, i): return self._node(N_EXPOSED, i)
     def is_first(self): return self._node(N_FIRST)
     def is_last(self): return self._node(N_LAST)
     def is_transition(self): return self._node(N_TRANS)
@@ -63,16 +66,68 @@ class Air:
         self.cached_widths = list(cached_widths)
         self.prep = prep            # (height, width) uint32 array or None
         self.prep_commit = None     # 8 words, filled by the key builder
+        self.interactions = []      # (bus, type 0 send / 1 receive, count Expr, [field Exprs])
+        self.chunks = []            # lists of interaction indices, one reciprocal-sum column each
+
+    def add_interaction(self, bus, fields, count, is_send=True):
+        self.interactions.append((bus, 0 if is_send else 1, count, list(fields)))
+
+    def finalize_logup(self, max_chunk=1):
+        """Append the FRI-LogUp constraints to the DAG (what the reference's keygen does through
+        `eval_fri_log_up_phase`; formula recalled, PARITY UNPINNED -- DESIGN.md):
+          denom_i = alpha + sum_j beta^j * field_ij + beta^len_i * (bus_i + 1)
+          per chunk c:  perm_c * prod_i denom_i = sum_i (+-count_i) * prod_{k != i} denom_k
+          phi (last column) is the running sum of sum_c perm_c; its final value is the exposed cumulative sum."""
+        if not self.interactions:
+            return self
+        d = self.dag
+        alpha, beta = d.challenge(0), d.challenge(1)
+        max_len = max(len(f) for _, _, _, f in self.interactions)
+        betas = [d.const(1)]
+        for _ in range(max_len):
+            betas.append(betas[-1] * beta)
+        denoms, counts = [], []
+        for bus, typ, count, fields in self.interactions:
+            den = alpha
+            for j, f in enumerate(fields):
+                den = den + (betas[j] * f if j else f)
+            den = den + betas[len(fields)] * (bus + 1)
+            denoms.append(den)
+            counts.append(-count if typ else count)
+        idx = list(range(len(self.interactions)))
+        self.chunks = [idx[i:i + max_chunk] for i in range(0, len(idx), max_chunk)]
+        nch = len(self.chunks)
+        for c, chunk in enumerate(self.chunks):
+            prod = denoms[chunk[0]]
+            for i in chunk[1:]:
+                prod = prod * denoms[i]
+            rhs = None
+            for i in chunk:
+                term = counts[i]
+                for k in chunk:
+                    if k != i:
+                        term = term * denoms[k]
+                rhs = term if rhs is None else rhs + term
+            d.assert_zero(d.perm(c) * prod - rhs)
+        phi, nphi = d.perm(nch), d.perm(nch, 1)
+        s0, s1 = d.perm(0), d.perm(0, 1)
+        for c in range(1, nch):
+            s0, s1 = s0 + d.perm(c), s1 + d.perm(c, 1)
+        d.assert_zero(d.is_first() * (phi - s0))
+        d.assert_zero(d.is_transition() * (nphi - phi - s1))
+        d.assert_zero(d.is_last() * (phi - d.exposed(0)))
+        return self
 
 
 def key_blob(airs, pre_hash=None, log_up_pow_bits=0):
     """airs: list of Air (prep_commit set where prep is not None). Returns the uint32 word array."""
-    w = [0x4B503242, 1]
+    w = [0x4B503242, 2]
     w += list(pre_hash if pre_hash is not None else range(101, 109))
     w += [log_up_pow_bits, len(airs)]
     for a in airs:
         w += [0 if a.prep is None else a.prep.shape[1], len(a.cached_widths)] + a.cached_widths
-        w += [a.width_common, 0, a.log_qd, a.num_pv, 0]
+        nch = len(a.chunks)
+        w += [a.width_common, nch + 1 if nch else 0, a.log_qd, a.num_pv, 1 if nch else 0]
         if a.prep is not None:
             assert a.prep_commit is not None
             w += [int(x) for x in a.prep_commit]
@@ -82,6 +137,12 @@ def key_blob(airs, pre_hash=None, log_up_pow_bits=0):
         for n in a.dag.nodes:
             w += list(n)
         w += [len(a.dag.constraints)] + a.dag.constraints
+        w += [len(a.interactions)]
+        for bus, typ, count, fields in a.interactions:
+            w += [bus, typ, count.i, len(fields)] + [f.i for f in fields]
+        w += [nch]
+        for ch in a.chunks:
+            w += [len(ch)] + ch
     return np.array(w, dtype=np.uint32)
 
 
@@ -162,6 +223,38 @@ def chain_trace(air, height, seed=0):
         parts.append(np.stack([(t[:, 0] + np.uint64(k)) % p for k in range(cw)], axis=1).astype(np.uint32))
     parts.append(common)
     return parts, np.array([pv0, int(common[height - 1, 1])], dtype=np.uint32)
+
+
+def dummy_interaction_air(n_fields, is_send, bus=0, log_qd=1):
+    """DummyInteractionAir of the reference's tests (openvm_stark_sdk::dummy_airs::interaction, used at
+    extensions/native/recursion/src/tests.rs:57-68,170-181): columns [count, field_0..]; one interaction, no other
+    constraints."""
+    d = Dag()
+    count = d.main(0)
+    fields = [d.main(1 + j) for j in range(n_fields)]
+    a = Air(d, width_common=1 + n_fields, num_pv=0, log_qd=log_qd)
+    a.add_interaction(bus, fields, count, is_send)
+    return a.finalize_logup(1)
+
+
+def lookup_chain_air(width, bus=3):
+    """chain_air whose rows are also sent on a bus: (x_0, x_1) with multiplicity 1 and (x_2) on bus+1 with multiplicity
+    x_3's low bit is not needed -- multiplicity 1; two interactions in one chunk (degree 3)."""
+    a = chain_air(width)
+    d = a.dag
+    a.add_interaction(bus, [d.main(0), d.main(1)], d.const(1), True)
+    a.add_interaction(bus + 1, [d.main(2)], d.const(1), True)
+    return a.finalize_logup(2)
+
+
+def lookup_chain_receiver(bus=3):
+    """receives what lookup_chain_air sends: columns [m, a, b, c]: receive (a, b) on `bus` and (c) on bus+1, count m."""
+    d = Dag()
+    m, a_, b_, c_ = (d.main(j) for j in range(4))
+    a = Air(d, width_common=4, num_pv=0, log_qd=1)
+    a.add_interaction(bus, [a_, b_], m, False)
+    a.add_interaction(bus + 1, [c_], m, False)
+    return a.finalize_logup(2)
 
 
 def build_key(air_list, commit_fn, **kw):

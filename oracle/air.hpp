@@ -12,6 +12,8 @@
 //     log_quotient_degree, num_public_values, num_exposed_values,
 //     [if width_preprocessed: commit[8], log_height, row-major canonical data[height*width]]
 //     num_nodes, nodes[num_nodes][4] = {kind, a, b, c}, num_constraints, constraint_idx[num_constraints]
+//     num_interactions, per interaction {bus, type (0 send, 1 receive), count_node, n_fields, field_nodes[n_fields]},
+//     num_chunks, per chunk {n, interaction indices[n]}     (FRI-LogUp: one reciprocal-sum column per chunk)
 // Node kinds: 0 Constant(a) | 1 Preprocessed(col a, offset b) | 2 Main(col a, offset b, part c) |
 //   3 Permutation(EF col a, offset b) | 4 Public(a) | 5 Challenge(a) | 6 Exposed(a) |
 //   7 IsFirstRow | 8 IsLastRow | 9 IsTransition | 10 Add(a,b) | 11 Sub(a,b) | 12 Neg(a) | 13 Mul(a,b)
@@ -27,7 +29,11 @@ enum NodeKind { N_CONST = 0, N_PREP, N_MAIN, N_PERM, N_PUBLIC, N_CHALLENGE, N_EX
                 N_ADD, N_SUB, N_NEG, N_MUL };
 struct Node { uint32_t kind, a, b, c; };
 
+struct Interaction { uint32_t bus, type, count_node; std::vector<uint32_t> fields; };
+
 struct AirKey {
+    std::vector<Interaction> interactions;
+    std::vector<std::vector<uint32_t>> chunks;
     uint32_t width_prep = 0;
     std::vector<uint32_t> cached_widths;
     uint32_t width_common = 0, width_after = 0, log_qd = 0, num_pv = 0, num_exposed = 0;
@@ -50,7 +56,7 @@ inline KeyBlob parse_key(const uint32_t* w, size_t n) {
     size_t i = 0;
     auto rd = [&]() -> uint32_t { if (i >= n) throw std::runtime_error("key blob truncated"); return w[i++]; };
     if (rd() != 0x4B503242u) throw std::runtime_error("key blob: bad magic");
-    if (rd() != 1) throw std::runtime_error("key blob: bad version");
+    if (rd() != 2) throw std::runtime_error("key blob: bad version");
     KeyBlob k;
     for (int j = 0; j < 8; j++) k.pre_hash[j] = F(rd());
     k.log_up_pow_bits = rd();
@@ -72,6 +78,17 @@ inline KeyBlob parse_key(const uint32_t* w, size_t n) {
         for (auto& nd : a.nodes) { nd.kind = rd(); nd.a = rd(); nd.b = rd(); nd.c = rd(); }
         a.constraint_idx.resize(rd());
         for (auto& c : a.constraint_idx) c = rd();
+        a.interactions.resize(rd());
+        for (auto& it : a.interactions) {
+            it.bus = rd(); it.type = rd(); it.count_node = rd();
+            it.fields.resize(rd());
+            for (auto& f : it.fields) f = rd();
+        }
+        a.chunks.resize(rd());
+        for (auto& ch : a.chunks) { ch.resize(rd()); for (auto& x : ch) x = rd(); }
+        if (a.interactions.empty() != (a.width_after == 0) || (a.width_after && a.width_after != a.chunks.size() + 1) ||
+            a.num_exposed != (a.width_after ? 1u : 0u))
+            throw std::runtime_error("key blob: interaction / after-challenge shape mismatch");
     }
     if (i != n) throw std::runtime_error("key blob: trailing words");
     return k;
@@ -92,12 +109,15 @@ struct EvalInputs {
 inline EF lift(F x) { return EF(x); }
 inline EF lift(const EF& x) { return x; }
 
-// Evaluates every node (as EF, the common super-type) and returns the alpha-folded constraint value.
+// Evaluates every node (as EF, the common super-type). Nodes that need inputs the caller did not provide
+// (perm / challenges / exposed == nullptr) evaluate to zero; callers only read nodes that do not depend on them.
 template <typename T>
-inline EF eval_dag_fold(const AirKey& air, const EvalInputs<T>& in, const EF& alpha) {
+inline std::vector<EF> eval_dag_nodes(const AirKey& air, const EvalInputs<T>& in) {
     std::vector<EF> v(air.nodes.size());
     for (size_t i = 0; i < air.nodes.size(); i++) {
         const Node& nd = air.nodes[i];
+        if ((nd.kind == N_PERM && !in.perm[0]) || (nd.kind == N_CHALLENGE && !in.challenges) || (nd.kind == N_EXPOSED && !in.exposed))
+            continue;
         switch (nd.kind) {
             case N_CONST: v[i] = EF(F(nd.a)); break;
             case N_PREP: v[i] = lift(in.prep[nd.b][nd.a]); break;
@@ -116,6 +136,13 @@ inline EF eval_dag_fold(const AirKey& air, const EvalInputs<T>& in, const EF& al
             default: throw std::runtime_error("dag: bad node kind");
         }
     }
+    return v;
+}
+
+// alpha-folded constraint value: acc = acc * alpha + node[constraint_idx[k]]
+template <typename T>
+inline EF eval_dag_fold(const AirKey& air, const EvalInputs<T>& in, const EF& alpha) {
+    std::vector<EF> v = eval_dag_nodes(air, in);
     EF acc;
     for (uint32_t c : air.constraint_idx) acc = acc * alpha + v[c];
     return acc;

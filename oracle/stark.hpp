@@ -2,8 +2,11 @@
 //
 // StarkEngine::prove (absent dependency openvm-stark-backend @ 002f52e; PARITY UNPINNED), restated so that the
 // transcript matches the in-tree verifier twin extensions/native/recursion/src/stark/mod.rs:130-834 step by step
-// (SURVEY.md 3.2 / 8g). Scope of this restatement: AIRs without interactions (no after-challenge phase), any
-// number of cached mains, optional preprocessed trace, quotient degree 2^k <= 2^log_blowup.
+// (SURVEY.md 3.2 / 8g): any number of cached mains, optional preprocessed trace, quotient degree 2^k <= 2^log_blowup,
+// and the single FRI-LogUp challenge phase (stark/mod.rs:307-358): PoW, two EF challenges, one reciprocal-sum column
+// per interaction chunk plus the running-sum column, exposed cumulative sum. The LogUp denominators follow
+//   alpha + sum_j beta^j field_j + beta^len (bus + 1)        (recalled from the absent dependency; the constraints
+// that pin it for a given key are part of that key's DAG, so prover and verifier stay consistent by construction).
 #pragma once
 #include "air.hpp"
 #include "pcs.hpp"
@@ -89,6 +92,79 @@ inline Proof stark_prove(const KeyBlob& key, const std::vector<AirInput>& airs, 
     }
     for (auto& c : proof.main_trace_commits) ch.observe_digest(c);
     for (unsigned l : logn) ch.observe(F(l));
+    // --- FRI-LogUp phase
+    bool any_inter = false;
+    for (uint32_t id : ids) any_inter |= !key.airs[id].interactions.empty();
+    EF challenges[2];
+    std::vector<EF> cumsum(airs.size());
+    std::shared_ptr<Committed> after;
+    std::vector<size_t> after_of;  // air position of each after-challenge matrix
+    if (any_inter) {
+        proof.has_logup_witness = true;
+        proof.logup_pow_witness = ch.grind(key.log_up_pow_bits);
+        challenges[0] = ch.sample_ext();
+        challenges[1] = ch.sample_ext();
+        std::vector<ColMatrix> perms;
+        for (size_t i = 0; i < airs.size(); i++) {
+            const AirKey& k = key.airs[ids[i]];
+            if (k.interactions.empty()) continue;
+            const size_t N = (size_t)1 << logn[i], nch = k.chunks.size();
+            size_t max_len = 0;
+            for (auto& it : k.interactions) max_len = std::max(max_len, it.fields.size());
+            std::vector<EF> betas(max_len + 1, EF(F(1)));
+            for (size_t j = 1; j <= max_len; j++) betas[j] = betas[j - 1] * challenges[1];
+            ColMatrix prepm;
+            if (k.width_prep) prepm = to_col_major(k.prep, N, k.width_prep);
+            ColMatrix pm(N, 4 * (nch + 1));
+            EF phi;
+            for (size_t r = 0; r < N; r++) {
+                const size_t rr[2] = {r, (r + 1) % N};
+                std::vector<std::vector<F>> rows[2];
+                std::vector<F> prow[2];
+                EvalInputs<F> in;
+                for (int o = 0; o < 2; o++) {
+                    for (size_t p = 0; p < k.num_parts(); p++) {
+                        const ColMatrix& m = p < airs[i].cached.size() ? airs[i].cached[p] : airs[i].common;
+                        rows[o].emplace_back(m.width);
+                        for (size_t c = 0; c < m.width; c++) rows[o][p][c] = m.at(rr[o], c);
+                    }
+                    for (auto& v : rows[o]) in.main[o].push_back(v.data());
+                    if (k.width_prep) {
+                        prow[o].resize(k.width_prep);
+                        for (size_t c = 0; c < k.width_prep; c++) prow[o][c] = prepm.at(rr[o], c);
+                        in.prep[o] = prow[o].data();
+                    }
+                }
+                in.publics = airs[i].public_values.data();
+                in.is_first = F(r == 0 ? 1 : 0); in.is_last = F(r == N - 1 ? 1 : 0); in.is_transition = F(r == N - 1 ? 0 : 1);
+                std::vector<EF> v = eval_dag_nodes(k, in);
+                EF row_sum;
+                for (size_t c = 0; c < nch; c++) {
+                    EF s;
+                    for (uint32_t ii : k.chunks[c]) {
+                        const Interaction& it = k.interactions[ii];
+                        EF den = challenges[0];
+                        for (size_t j = 0; j < it.fields.size(); j++) den += betas[j] * v[it.fields[j]];
+                        den += betas[it.fields.size()] * F(it.bus + 1);
+                        EF cnt = v[it.count_node];
+                        if (it.type) cnt = -cnt;
+                        s += cnt * einv(den);
+                    }
+                    for (int e = 0; e < 4; e++) pm.at(r, 4 * c + e) = s.c[e];
+                    row_sum += s;
+                }
+                phi += row_sum;
+                for (int e = 0; e < 4; e++) pm.at(r, 4 * nch + e) = phi.c[e];
+            }
+            cumsum[i] = phi;
+            perms.push_back(std::move(pm));
+            after_of.push_back(i);
+        }
+        for (size_t i : after_of) ch.observe_ext(cumsum[i]);
+        after = pcs_commit(perms, std::vector<F>(perms.size(), F(1)), b, threads);
+        proof.after_challenge_commits.push_back(after->root());
+        ch.observe_digest(after->root());
+    }
     const EF alpha = ch.sample_ext();
     // --- quotient
     std::vector<ColMatrix> chunks;
@@ -106,9 +182,15 @@ inline Proof stark_prove(const KeyBlob& key, const std::vector<AirInput>& airs, 
         const F gq = two_adic_generator(n + lq);
         std::vector<ColMatrix> cm;
         for (size_t j = 0; j < ((size_t)1 << lq); j++) cm.emplace_back(N, 4);
+        const ColMatrix* perm_lde = nullptr;
+        if (!k.interactions.empty()) {
+            size_t pos = std::find(after_of.begin(), after_of.end(), i) - after_of.begin();
+            perm_lde = &after->ldes[pos];
+        }
         parallel_for(Q, threads, [&](size_t lo, size_t hi) {
             std::vector<std::vector<F>> rows[2];
             std::vector<F> prow[2];
+            std::vector<EF> perm_row[2];
             for (size_t kq = lo; kq < hi; kq++) {
                 const size_t K = kq << (b - lq);
                 const size_t r[2] = {(size_t)bitrev64(K, n + b), (size_t)bitrev64((K + ((size_t)1 << b)) % M, n + b)};
@@ -125,6 +207,16 @@ inline Proof stark_prove(const KeyBlob& key, const std::vector<AirInput>& airs, 
                         for (size_t c = 0; c < k.width_prep; c++) prow[o][c] = prep[i]->ldes[0].at(r[o], c);
                         in.prep[o] = prow[o].data();
                     }
+                }
+                if (perm_lde) {
+                    for (int o = 0; o < 2; o++) {
+                        perm_row[o].resize(k.width_after);
+                        for (size_t c = 0; c < k.width_after; c++)
+                            for (int e = 0; e < 4; e++) perm_row[o][c].c[e] = perm_lde->at(r[o], 4 * c + e);
+                        in.perm[o] = perm_row[o].data();
+                    }
+                    in.challenges = challenges;
+                    in.exposed = &cumsum[i];
                 }
                 in.publics = airs[i].public_values.data();
                 const F x = F(GENERATOR) * fpow(gq, kq);
@@ -152,6 +244,11 @@ inline Proof stark_prove(const KeyBlob& key, const std::vector<AirInput>& airs, 
         for (size_t pos : common_of) r.points.push_back(trace_points(pos));
         rounds.push_back(r);
     }
+    if (after) {
+        OpenRound r{after, {}, {}};
+        for (size_t pos : after_of) r.points.push_back(trace_points(pos));
+        rounds.push_back(r);
+    }
     {
         OpenRound r{quotient, {}, {}};
         for (size_t j = 0; j < chunks.size(); j++) r.points.push_back({zeta});
@@ -169,6 +266,12 @@ inline Proof stark_prove(const KeyBlob& key, const std::vector<AirInput>& airs, 
         proof.opened_main.push_back(part);
         ri++;
     }
+    if (after) {
+        std::vector<AdjacentOpened> part;
+        for (auto& v : rounds[ri].values) part.push_back({v[0], v[1]});
+        proof.opened_after.push_back(part);
+        ri++;
+    }
     {
         size_t m = 0;
         for (size_t i = 0; i < airs.size(); i++) {
@@ -180,6 +283,7 @@ inline Proof stark_prove(const KeyBlob& key, const std::vector<AirInput>& airs, 
     for (size_t i = 0; i < airs.size(); i++) {
         AirProofData d;
         d.air_id = ids[i]; d.degree = 1u << logn[i]; d.public_values = airs[i].public_values;
+        if (!key.airs[ids[i]].interactions.empty()) d.exposed_values_after_challenge = {{cumsum[i]}};
         proof.per_air.push_back(d);
     }
     return proof;

@@ -3,7 +3,7 @@
 // MultiTraceStarkVerifier::verify_raps, transliterated from the in-tree recursive verifier
 //   extensions/native/recursion/src/stark/mod.rs:130-834 (transcript, rounds), :903-1126 (constraints, quotient)
 //   extensions/native/recursion/src/fri/domain.rs:59-155 (selectors, zerofiers, chunk domains)
-// for the 0-phase case (AIRs without interactions).
+// including the single FRI-LogUp challenge phase (stark/mod.rs:307-358, 1129-1160).
 #pragma once
 #include "pcs_verify.hpp"
 #include "stark.hpp"
@@ -29,17 +29,41 @@ inline void stark_verify(const KeyBlob& key, const Proof& proof, const FriParams
         if (!a.degree || (a.degree & (a.degree - 1))) throw VerifyError("InvalidProofShape: degree");
         unsigned l = log2u(a.degree);
         if (l + b > TWO_ADICITY) throw VerifyError("InvalidProofShape: degree too large");
-        if (!a.exposed_values_after_challenge.empty()) throw VerifyError("InvalidProofShape: exposed values without a challenge phase");
+        if (k.num_exposed) {
+            if (a.exposed_values_after_challenge.size() != 1 || a.exposed_values_after_challenge[0].size() != 1)
+                throw VerifyError("InvalidProofShape: exposed values");
+        } else if (!a.exposed_values_after_challenge.empty()) {
+            throw VerifyError("InvalidProofShape: exposed values without interactions");
+        }
         ids.push_back(a.air_id); pvs.push_back(a.public_values); logn.push_back(l);
     }
     observe_prefix(ch, key, ids, pvs);
     size_t num_cached = 0, num_prep = 0;
     for (uint32_t id : ids) { num_cached += key.airs[id].cached_widths.size(); num_prep += key.airs[id].width_prep ? 1 : 0; }
     if (proof.main_trace_commits.size() != num_cached + 1) throw VerifyError("InvalidProofShape: main commits");
-    if (!proof.after_challenge_commits.empty() || !proof.opened_after.empty() || proof.has_logup_witness)
-        throw VerifyError("InvalidProofShape: unexpected challenge phase");
+    size_t num_after = 0;
+    for (uint32_t id : ids) num_after += key.airs[id].width_after ? 1 : 0;
+    const bool phase = num_after != 0;
+    if (phase != !proof.after_challenge_commits.empty() || phase != !proof.opened_after.empty() || phase != proof.has_logup_witness ||
+        proof.after_challenge_commits.size() > 1 || proof.opened_after.size() > 1)
+        throw VerifyError("InvalidProofShape: challenge phase");
     for (auto& c : proof.main_trace_commits) ch.observe_digest(c);
     for (unsigned l : logn) ch.observe(F(l));
+    EF challenges[2];
+    if (phase) {
+        if (!ch.check_witness(key.log_up_pow_bits, proof.logup_pow_witness)) throw VerifyError("InvalidLogUpPowWitness");
+        challenges[0] = ch.sample_ext();
+        challenges[1] = ch.sample_ext();
+        EF total;
+        for (size_t i = 0; i < na; i++)
+            if (key.airs[ids[i]].num_exposed) {
+                const EF& cs = proof.per_air[i].exposed_values_after_challenge[0][0];
+                ch.observe_ext(cs);
+                total += cs;
+            }
+        if (!total.is_zero()) throw VerifyError("NonZeroCumulativeSum");
+        ch.observe_digest(proof.after_challenge_commits[0]);
+    }
     const EF alpha = ch.sample_ext();
     ch.observe_digest(proof.quotient_commit);
     const EF zeta = ch.sample_ext();
@@ -78,6 +102,15 @@ inline void stark_verify(const KeyBlob& key, const Proof& proof, const FriParams
     if (cm != common_vals.size()) throw VerifyError("InvalidProofShape: common main count");
     common_round.commit = proof.main_trace_commits[num_cached];
     rounds.push_back(common_round);
+    if (phase) {
+        VerifyRound ar;
+        ar.commit = proof.after_challenge_commits[0];
+        if (proof.opened_after[0].size() != num_after) throw VerifyError("InvalidProofShape: after-challenge openings");
+        size_t am = 0;
+        for (size_t i = 0; i < na; i++)
+            if (key.airs[ids[i]].width_after) { ar.mats.push_back(trace_mat(i, proof.opened_after[0][am], 4 * key.airs[ids[i]].width_after)); am++; }
+        rounds.push_back(ar);
+    }
     VerifyRound qround;
     qround.commit = proof.quotient_commit;
     for (size_t i = 0; i < na; i++) {
@@ -92,6 +125,7 @@ inline void stark_verify(const KeyBlob& key, const Proof& proof, const FriParams
     verify_pcs(rounds, proof.fri, log_max_height, b, fp.num_queries, fp.pow_bits, ch);
     // --- constraints at zeta
     pi = 0; mc = 0; cm = 0;
+    size_t am = 0;
     for (size_t i = 0; i < na; i++) {
         const AirKey& k = key.airs[ids[i]];
         const unsigned n = logn[i];
@@ -103,6 +137,20 @@ inline void stark_verify(const KeyBlob& key, const Proof& proof, const FriParams
             mc++;
         }
         if (k.width_common) { in.main[0].push_back(common_vals[cm].local.data()); in.main[1].push_back(common_vals[cm].next.data()); cm++; }
+        std::vector<EF> perm[2];
+        if (k.width_after) {
+            // unflatten: EF column c = sum_e opened(base column 4c+e) * x^e   (stark/mod.rs:1035-1047)
+            const AdjacentOpened& ov = proof.opened_after[0][am++];
+            const std::vector<EF>* src[2] = {&ov.local, &ov.next};
+            for (int o = 0; o < 2; o++) {
+                perm[o].resize(k.width_after);
+                for (size_t c = 0; c < k.width_after; c++)
+                    for (int e = 0; e < 4; e++) { EF mono; mono.c[e] = F(1); perm[o][c] += mono * (*src[o])[4 * c + e]; }
+                in.perm[o] = perm[o].data();
+            }
+            in.challenges = challenges;
+            in.exposed = proof.per_air[i].exposed_values_after_challenge[0].data();
+        }
         in.publics = proof.per_air[i].public_values.data();
         // selectors_at_point on the trace domain (shift 1)
         const F ginv = finv(two_adic_generator(n));

@@ -100,3 +100,64 @@ def test_blowup2_quotient_degree2(orc):
     parts, pv = airs.chain_trace(a, 128, seed=9)
     proof = orc.stark_prove(key, [(0, parts, pv)], b, 4, 5)
     assert orc.stark_verify(key, proof, b, 4, 5) is None
+
+
+def interaction_traces(n_send, n_recv, n_fields, seed=0, unbalanced=False):
+    """sender rows (count, fields) and a receiver holding the same multiset in a different order / grouping."""
+    rng = np.random.default_rng(seed)
+    send = np.zeros((n_send, 1 + n_fields), dtype=np.uint32)
+    send[:, 0] = rng.integers(0, 4, size=n_send)
+    send[:, 1:] = rng.integers(0, 50, size=(n_send, n_fields))
+    # receiver: merge equal messages, pad with zero-count rows
+    agg = {}
+    for row in send:
+        key = tuple(int(x) for x in row[1:])
+        agg[key] = agg.get(key, 0) + int(row[0])
+    items = [(c, k) for k, c in agg.items() if c]
+    assert len(items) <= n_recv
+    recv = np.zeros((n_recv, 1 + n_fields), dtype=np.uint32)
+    for i, (c, k) in enumerate(reversed(items)):
+        recv[i, 0] = c
+        recv[i, 1:] = k
+    if unbalanced:
+        recv[0, 0] += 1
+    return send, recv
+
+
+def test_logup_sender_receiver(orc):
+    b = 1
+    snd = airs.dummy_interaction_air(2, True)
+    rcv = airs.dummy_interaction_air(2, False)
+    fib = airs.fibonacci_air()
+    key = airs.key_blob([fib, snd, rcv], log_up_pow_bits=5)
+    send, recv = interaction_traces(64, 128, 2, seed=4)
+    t0, pv0 = airs.fibonacci_trace(32)
+    none = np.zeros(0, dtype=np.uint32)
+    inputs = [(0, [t0], pv0), (1, [send], none), (2, [recv], none)]
+    proof = orc.stark_prove(key, inputs, b, 5, 4)
+    assert orc.stark_verify(key, proof, b, 5, 4) is None
+    # without the interacting AIRs there is no challenge phase at all
+    p0 = orc.stark_prove(key, inputs[:1], b, 5, 4)
+    assert orc.stark_verify(key, p0, b, 5, 4) is None
+    # unbalanced buses: the proof is well-formed but the cumulative sums do not cancel
+    send2, recv2 = interaction_traces(64, 128, 2, seed=4, unbalanced=True)
+    p2 = orc.stark_prove(key, [inputs[0], (1, [send2], none), (2, [recv2], none)], b, 5, 4)
+    assert "NonZeroCumulativeSum" in orc.stark_verify(key, p2, b, 5, 4)
+
+
+def test_logup_two_interactions_per_chunk_with_constraints(orc):
+    b = 1
+    a0 = airs.lookup_chain_air(6)
+    a1 = airs.lookup_chain_receiver()
+    key = airs.key_blob([a0, a1], log_up_pow_bits=3)
+    parts, pv = airs.chain_trace(a0, 64, seed=3)
+    x = parts[-1]
+    recv = np.zeros((64, 4), dtype=np.uint32)
+    recv[:, 0] = 1
+    recv[:, 1:4] = x[::-1, 0:3]
+    none = np.zeros(0, dtype=np.uint32)
+    proof = orc.stark_prove(key, [(0, parts, pv), (1, [recv], none)], b, 4, 2)
+    assert orc.stark_verify(key, proof, b, 4, 2) is None
+    bad = recv.copy(); bad[5, 2] = (int(bad[5, 2]) + 1) % P
+    p2 = orc.stark_prove(key, [(0, parts, pv), (1, [bad], none)], b, 4, 2)
+    assert "NonZeroCumulativeSum" in orc.stark_verify(key, p2, b, 4, 2)
