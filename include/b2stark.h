@@ -146,27 +146,34 @@ void b2s_pcs_free(b2s_pcs_data* d);
  *                                                        crates/sdk/src/prover/vm/mod.rs:23
  * The reference's MultiStarkProvingKey is a serde type of the un-vendored openvm-stark-backend; the Rust shim
  *  flattens it into this library's key blob: little-endian u32 words
- *   'B2PK', 1, pre_hash[8], log_up_pow_bits, num_airs, then per AIR
+ *   'B2PK', 2, pre_hash[8], log_up_pow_bits, num_airs, then per AIR
  *     width_preprocessed, n_cached, cached_widths[], width_common_main, width_after_challenge, log_quotient_degree,
  *     num_public_values, num_exposed_values,
  *     [if width_preprocessed: commit[8], log_height, row-major canonical trace]
  *     num_nodes, nodes[][4] = {kind,a,b,c}, num_constraints, constraint_idx[]
+ *     num_interactions, per interaction {bus, type (0 send / 1 receive), count_node, n_fields, field_nodes[]},
+ *     num_chunks, per chunk {n, interaction indices[n]}   (FRI-LogUp: one reciprocal-sum column per chunk, then
+ *     the running-sum column; width_after_challenge = num_chunks + 1 extension-field columns)
  * (node kinds: 0 Constant 1 Preprocessed 2 Main 3 Permutation 4 Public 5 Challenge 6 Exposed 7 IsFirstRow
  *  8 IsLastRow 9 IsTransition 10 Add 11 Sub 12 Neg 13 Mul; content of SymbolicExpressionDag as consumed at
  *  extensions/native/recursion/src/stark/mod.rs:1023-1085, types.rs:19-95).
  * Loading uploads and commits the preprocessed traces (the root must equal the key's commit) and compiles each
- * constraint DAG into the register-allocated program the quotient kernel interprets. */
+ * constraint DAG into the register-allocated program the quotient kernel interprets, and each AIR's interaction
+ * list into the program the LogUp trace kernel interprets. */
 typedef struct b2s_pk b2s_pk;
 int32_t b2s_pk_load(b2s_engine* e, const uint32_t* key_words, size_t n_words, b2s_pk** out);
 void b2s_pk_free(b2s_pk* pk);
 
 /* AirProvingContext {cached_mains: Vec<CommittedTraceData>, common_main, public_values}
  * (built at crates/vm/src/arch/vm.rs:588-599; GPU instance crates/vm/src/system/cuda/program.rs:121-125).
- * A cached main is passed as the PcsData returned by b2s_commit on that single trace. */
+ * A cached main is passed as the PcsData returned by b2s_commit on that single trace, plus (CommittedTraceData
+ * carries both) the trace itself: cached_traces is only read for AIRs with interactions, whose after-challenge
+ * trace is generated from the main trace rows, and may be NULL otherwise. */
 typedef struct {
     uint32_t air_id;
     uint32_t n_cached;
     const b2s_pcs_data* const* cached;
+    const b2s_matrix* const* cached_traces;  /* n_cached device traces (height x cached width), or NULL */
     const b2s_matrix* common_main;      /* NULL when the AIR has no common main */
     const uint32_t* public_values;      /* canonical */
     uint32_t n_public_values;
@@ -176,7 +183,9 @@ typedef struct {
  * Transcript order: extensions/native/recursion/src/stark/mod.rs:140-364; opening: fri/two_adic_pcs.rs:41-376,
  * fri/mod.rs:33-170. AIRs must be given in strictly increasing air_id. The proof is returned in the reference's
  * wire format (crates/sdk/src/codec.rs:92-330) in a buffer released with b2s_free. Proof-of-work witnesses are the
- * minimum valid ones (the reference returns any valid witness). This round: AIRs without interactions. */
+ * minimum valid ones (the reference returns any valid witness). AIRs with interactions run the single FRI-LogUp
+ * challenge phase (stark/mod.rs:307-358): log_up_pow_bits grinding, two extension challenges, the after-challenge
+ * trace of every interacting AIR committed in one tree, exposed cumulative sums in the proof. */
 int32_t b2s_prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_airs, uint8_t** proof_bytes,
                   size_t* proof_len);
 

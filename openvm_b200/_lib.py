@@ -24,7 +24,7 @@ class Metrics(C.Structure):
 
 class AirCtx(C.Structure):
     _fields_ = [("air_id", C.c_uint32), ("n_cached", C.c_uint32), ("cached", C.POINTER(C.c_void_p)),
-                ("common_main", C.c_void_p), ("public_values", C.POINTER(C.c_uint32)),
+                ("cached_traces", C.POINTER(C.c_void_p)), ("common_main", C.c_void_p), ("public_values", C.POINTER(C.c_uint32)),
                 ("n_public_values", C.c_uint32)]
 
 

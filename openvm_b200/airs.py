@@ -271,3 +271,42 @@ def segment_shapes(scale_log=0):
     a few tall narrow range/lookup AIRs, ALU/branch/load-store chips of 20-40 columns, one wide hash chip."""
     base = [(19, 5), (17, 36), (17, 40), (16, 28), (16, 20), (15, 32), (14, 66), (13, 200), (12, 16), (10, 8)]
     return [(max(4, h + scale_log), w) for h, w in base]
+
+
+def lookup_chain_air_parts(width, height, seed=0, bus=5, cached_width=2):
+    """chain_air with a preprocessed trace and a cached partition whose interactions read every kind of column:
+    send (x_0, x_1) once per row on `bus`; send (cached_0, prep_0, next x_0) with multiplicity prep_0 (the row index)
+    on bus + 1. One interaction per chunk -> two reciprocal-sum columns."""
+    a = chain_air(width, with_prep=True, cached_width=cached_width, height=height, seed=seed)
+    d = a.dag
+    a.add_interaction(bus, [d.main(0, 0, 1), d.main(1, 0, 1)], d.const(1), True)
+    a.add_interaction(bus + 1, [d.main(0, 0, 0), d.prep(0), d.main(0, 1, 1)], d.prep(0), True)
+    return a.finalize_logup(1)
+
+
+def multi_receiver_air(field_lens, bus0, max_chunk=1):
+    """columns [m_0, fields_0.., m_1, fields_1.., ...]: interaction i receives its fields with multiplicity m_i on
+    bus0 + i."""
+    d = Dag()
+    col = 0
+    a = Air(d, width_common=sum(field_lens) + len(field_lens), num_pv=0, log_qd=1)
+    for i, ln in enumerate(field_lens):
+        m = d.main(col)
+        a.add_interaction(bus0 + i, [d.main(col + 1 + j) for j in range(ln)], m, False)
+        col += 1 + ln
+    return a.finalize_logup(max_chunk)
+
+
+def lookup_chain_parts_receiver_trace(air, parts):
+    """receiver rows for lookup_chain_air_parts: the same messages, in reverse row order."""
+    cached, common = parts[0], parts[-1]
+    n = common.shape[0]
+    prep0 = air.prep[:, 0]
+    t = np.zeros((n, 7), dtype=np.uint32)
+    t[:, 0] = 1
+    t[:, 1:3] = common[:, 0:2]
+    t[:, 3] = prep0
+    t[:, 4] = cached[:, 0]
+    t[:, 5] = prep0
+    t[:, 6] = np.roll(common[:, 0], -1)
+    return t[::-1].copy()

@@ -105,7 +105,13 @@ struct AirKeyDev {
     // compiled constraint program: {op, dst, a, b} words, device copy + host count
     std::vector<uint4> program;
     uint4* d_program = nullptr;
-    uint32_t num_slots = 0, num_constraints = 0;
+    uint32_t num_slots = 0, num_slots_e = 0, num_constraints = 0;
+    // FRI-LogUp: interaction program (evaluates message fields / counts on trace rows), per-interaction bus and
+    // message length, number of chunks (= after-challenge EF columns - 1)
+    std::vector<uint4> iprogram;
+    uint4* d_iprogram = nullptr;
+    uint32_t islots = 0, num_chunks = 0, max_fields = 0;
+    std::vector<uint32_t> inter_bus, inter_len;
     uint32_t total_cols() const {
         uint32_t t = width_prep + width_common;
         for (uint32_t w : cached_widths) t += w;

@@ -32,20 +32,41 @@ namespace b2 {
 // ---- key blob -> device key --------------------------------------------------------------------------------
 enum NodeKind { N_CONST = 0, N_PREP, N_MAIN, N_PERM, N_PUBLIC, N_CHALLENGE, N_EXPOSED, N_FIRST, N_LAST, N_TRANS,
                 N_ADD, N_SUB, N_NEG, N_MUL };
-enum Op { OP_LOAD = 0, OP_PUBLIC, OP_CONST, OP_FIRST, OP_LAST, OP_TRANS, OP_ADD, OP_SUB, OP_NEG, OP_MUL, OP_ACC };
+enum Op { OP_LOAD = 0, OP_PUBLIC, OP_CONST, OP_FIRST, OP_LAST, OP_TRANS, OP_ADD, OP_SUB, OP_NEG, OP_MUL, OP_ACC,
+          // extension-field values (after-challenge columns, challenges, exposed values and what depends on them)
+          OP_LOADP, OP_CHAL, OP_EXPOSED, OP_ADD_EE, OP_ADD_EF, OP_SUB_EE, OP_SUB_EF, OP_SUB_FE, OP_NEG_E, OP_MUL_EE,
+          OP_MUL_EF, OP_ACC_E,
+          // interaction program (LogUp trace generation)
+          OP_IFIELD, OP_IEND };
 
 struct HostNode { uint32_t kind, a, b, c; };
+struct HostInteraction { uint32_t bus, type, count_node; std::vector<uint32_t> fields; };
 
-// Compile the DAG (topological node list + constraint indices) into a straight-line program over a small set of
-// slots: dead nodes are dropped, a slot is recycled after the last use of its value, and each constraint becomes
-// an OP_ACC with the index of its alpha power (constraint k of C carries alpha^(C-1-k): Horner order).
-static void compile_dag(AirKeyDev& air, const std::vector<HostNode>& nodes, const std::vector<uint32_t>& cidx) {
+// Compile the DAG (topological node list) into a straight-line program over two small slot files (base field and
+// extension field): dead nodes are dropped, a slot is recycled after the last use of its value.
+//   quotient mode:    roots = constraints; constraint k of C becomes OP_ACC / OP_ACC_E with the index of its alpha
+//                     power (alpha^(C-1-k): Horner order of the reference's constraint folder)
+//   interaction mode: roots = message fields and counts of the interactions; after the node code, per chunk and per
+//                     interaction: OP_IFIELD (slot, j) ... OP_IEND (flags: bit0 receive, bit1 last of its chunk)
+struct Compiled {
+    std::vector<uint4> program;
+    uint32_t slots_f = 1, slots_e = 1;
+};
+static Compiled compile_dag(const AirKeyDev& air, const std::vector<HostNode>& nodes, const std::vector<uint32_t>& cidx,
+                            const std::vector<HostInteraction>* inter, const std::vector<std::vector<uint32_t>>* chunks) {
     const size_t n = nodes.size();
+    const uint32_t NEVER = 0xFFFFFFFFu;
     std::vector<uint32_t> last_use(n, 0);
-    std::vector<char> live(n, 0);
-    for (uint32_t c : cidx) {
-        B2_REQUIRE(c < n, B2S_ERR_BAD_ARG, "key: constraint index out of range");
+    std::vector<char> live(n, 0), is_e(n, 0);
+    auto root = [&](uint32_t c, bool pin) {
+        B2_REQUIRE(c < n, B2S_ERR_BAD_ARG, "key: node index out of range");
         live[c] = 1;
+        if (pin) last_use[c] = NEVER;
+    };
+    if (inter) {
+        for (auto& it : *inter) { root(it.count_node, true); for (uint32_t f : it.fields) root(f, true); }
+    } else {
+        for (uint32_t c : cidx) root(c, false);
     }
     for (size_t i = n; i-- > 0;) {
         if (!live[i]) continue;
@@ -59,71 +80,114 @@ static void compile_dag(AirKeyDev& air, const std::vector<HostNode>& nodes, cons
     for (size_t i = 0; i < n; i++) {
         if (!live[i]) continue;
         const HostNode& nd = nodes[i];
-        last_use[i] = std::max<uint32_t>(last_use[i], (uint32_t)i);
+        if (last_use[i] != NEVER) last_use[i] = std::max<uint32_t>(last_use[i], (uint32_t)i);
+        if (nd.kind == N_PERM || nd.kind == N_CHALLENGE || nd.kind == N_EXPOSED) is_e[i] = 1;
         if (nd.kind >= N_ADD) {
-            last_use[nd.a] = (uint32_t)i;
-            if (nd.kind != N_NEG) last_use[nd.b] = (uint32_t)i;
+            if (last_use[nd.a] != NEVER) last_use[nd.a] = (uint32_t)i;
+            if (nd.kind != N_NEG && last_use[nd.b] != NEVER) last_use[nd.b] = (uint32_t)i;
+            is_e[i] = is_e[nd.a] || (nd.kind != N_NEG && is_e[nd.b]);
         }
+        B2_REQUIRE(!(inter && is_e[i]), B2S_ERR_BAD_ARG, "key: interaction message depends on a challenge-phase value");
     }
-    // column index of a variable inside the AIR's pointer table: [preprocessed][part 0][part 1]...
+    // column index of a variable inside the AIR's pointer table: [preprocessed][part 0][part 1]...[after-challenge]
     std::vector<uint32_t> part_base;
     uint32_t base = air.width_prep;
     for (uint32_t w : air.cached_widths) { part_base.push_back(base); base += w; }
-    if (air.width_common) part_base.push_back(base);
+    if (air.width_common) { part_base.push_back(base); base += air.width_common; }
+    const uint32_t perm_base = base;
     auto part_width = [&](uint32_t p) { return p < air.cached_widths.size() ? air.cached_widths[p] : air.width_common; };
 
-    std::vector<uint32_t> slot_of(n, 0xFFFFFFFFu), free_slots;
+    Compiled out;
+    std::vector<uint32_t> slot_of(n, NEVER), free_f, free_e;
     std::vector<std::vector<uint32_t>> expiring(n);
-    for (size_t i = 0; i < n; i++) if (live[i]) expiring[last_use[i]].push_back((uint32_t)i);
-    uint32_t num_slots = 0;
+    for (size_t i = 0; i < n; i++) if (live[i] && last_use[i] != NEVER) expiring[last_use[i]].push_back((uint32_t)i);
+    uint32_t nf = 0, ne = 0;
     const uint32_t C = (uint32_t)cidx.size();
     std::vector<std::vector<uint32_t>> acc_of(n);
-    for (uint32_t k = 0; k < C; k++) acc_of[cidx[k]].push_back(C - 1 - k);
-    air.program.clear();
+    if (!inter) for (uint32_t k = 0; k < C; k++) acc_of[cidx[k]].push_back(C - 1 - k);
+    auto emit = [&](uint32_t op, uint32_t d, uint32_t a, uint32_t b2) { out.program.push_back(make_uint4(op, d, a, b2)); };
     for (size_t i = 0; i < n; i++) {
         if (!live[i]) continue;
         const HostNode& nd = nodes[i];
         uint32_t sa = 0, sb = 0;
+        bool ea = false, eb = false;
         if (nd.kind >= N_ADD) {
-            sa = slot_of[nd.a];
-            sb = nd.kind == N_NEG ? 0 : slot_of[nd.b];
+            sa = slot_of[nd.a]; ea = is_e[nd.a];
+            if (nd.kind != N_NEG) { sb = slot_of[nd.b]; eb = is_e[nd.b]; }
         }
         uint32_t dst;
-        if (!free_slots.empty()) { dst = free_slots.back(); free_slots.pop_back(); } else dst = num_slots++;
+        if (is_e[i]) { if (!free_e.empty()) { dst = free_e.back(); free_e.pop_back(); } else dst = ne++; }
+        else { if (!free_f.empty()) { dst = free_f.back(); free_f.pop_back(); } else dst = nf++; }
         slot_of[i] = dst;
         switch (nd.kind) {
             case N_CONST:
                 B2_REQUIRE(nd.a < P, B2S_ERR_BAD_ARG, "key: non-canonical constant");
-                air.program.push_back(make_uint4(OP_CONST, dst, Fp::from_canonical(nd.a).v, 0));
+                emit(OP_CONST, dst, Fp::from_canonical(nd.a).v, 0);
                 break;
             case N_PREP:
                 B2_REQUIRE(nd.a < air.width_prep && nd.b < 2, B2S_ERR_BAD_ARG, "key: preprocessed variable out of range");
-                air.program.push_back(make_uint4(OP_LOAD, dst, nd.a, nd.b));
+                emit(OP_LOAD, dst, nd.a, nd.b);
                 break;
             case N_MAIN:
                 B2_REQUIRE(nd.c < part_base.size() && nd.a < part_width(nd.c) && nd.b < 2, B2S_ERR_BAD_ARG,
                            "key: main variable out of range");
-                air.program.push_back(make_uint4(OP_LOAD, dst, part_base[nd.c] + nd.a, nd.b));
+                emit(OP_LOAD, dst, part_base[nd.c] + nd.a, nd.b);
+                break;
+            case N_PERM:
+                B2_REQUIRE(nd.a < air.width_after && nd.b < 2, B2S_ERR_BAD_ARG, "key: after-challenge variable out of range");
+                emit(OP_LOADP, dst, perm_base + 4 * nd.a, nd.b);
                 break;
             case N_PUBLIC:
                 B2_REQUIRE(nd.a < air.num_pv, B2S_ERR_BAD_ARG, "key: public value out of range");
-                air.program.push_back(make_uint4(OP_PUBLIC, dst, nd.a, 0));
+                emit(OP_PUBLIC, dst, nd.a, 0);
                 break;
-            case N_FIRST: air.program.push_back(make_uint4(OP_FIRST, dst, 0, 0)); break;
-            case N_LAST: air.program.push_back(make_uint4(OP_LAST, dst, 0, 0)); break;
-            case N_TRANS: air.program.push_back(make_uint4(OP_TRANS, dst, 0, 0)); break;
-            case N_ADD: air.program.push_back(make_uint4(OP_ADD, dst, sa, sb)); break;
-            case N_SUB: air.program.push_back(make_uint4(OP_SUB, dst, sa, sb)); break;
-            case N_NEG: air.program.push_back(make_uint4(OP_NEG, dst, sa, 0)); break;
-            case N_MUL: air.program.push_back(make_uint4(OP_MUL, dst, sa, sb)); break;
-            default:
-                fail(B2S_ERR_BAD_ARG, "key: node kind needs a challenge phase (interactions are not supported in this build)");
+            case N_CHALLENGE:
+                B2_REQUIRE(nd.a < 2 && air.width_after, B2S_ERR_BAD_ARG, "key: challenge out of range");
+                emit(OP_CHAL, dst, nd.a, 0);
+                break;
+            case N_EXPOSED:
+                B2_REQUIRE(nd.a < air.num_exposed, B2S_ERR_BAD_ARG, "key: exposed value out of range");
+                emit(OP_EXPOSED, dst, nd.a, 0);
+                break;
+            case N_FIRST: emit(OP_FIRST, dst, 0, 0); break;
+            case N_LAST: emit(OP_LAST, dst, 0, 0); break;
+            case N_TRANS: emit(OP_TRANS, dst, 0, 0); break;
+            case N_ADD:
+                if (!ea && !eb) emit(OP_ADD, dst, sa, sb);
+                else if (ea && eb) emit(OP_ADD_EE, dst, sa, sb);
+                else if (ea) emit(OP_ADD_EF, dst, sa, sb);
+                else emit(OP_ADD_EF, dst, sb, sa);
+                break;
+            case N_SUB:
+                if (!ea && !eb) emit(OP_SUB, dst, sa, sb);
+                else if (ea && eb) emit(OP_SUB_EE, dst, sa, sb);
+                else if (ea) emit(OP_SUB_EF, dst, sa, sb);
+                else emit(OP_SUB_FE, dst, sa, sb);
+                break;
+            case N_NEG: emit(ea ? OP_NEG_E : OP_NEG, dst, sa, 0); break;
+            case N_MUL:
+                if (!ea && !eb) emit(OP_MUL, dst, sa, sb);
+                else if (ea && eb) emit(OP_MUL_EE, dst, sa, sb);
+                else if (ea) emit(OP_MUL_EF, dst, sa, sb);
+                else emit(OP_MUL_EF, dst, sb, sa);
+                break;
+            default: fail(B2S_ERR_BAD_ARG, "key: unknown node kind");
         }
-        for (uint32_t pw : acc_of[i]) air.program.push_back(make_uint4(OP_ACC, 0, dst, pw));
-        for (uint32_t j : expiring[i]) free_slots.push_back(slot_of[j]);
+        for (uint32_t pw : acc_of[i]) emit(is_e[i] ? OP_ACC_E : OP_ACC, 0, dst, pw);
+        for (uint32_t j : expiring[i]) (is_e[j] ? free_e : free_f).push_back(slot_of[j]);
     }
-    air.num_slots = std::max<uint32_t>(num_slots, 1);
-    air.num_constraints = C;
+    if (inter) {
+        for (auto& ch : *chunks)
+            for (size_t q = 0; q < ch.size(); q++) {
+                B2_REQUIRE(ch[q] < inter->size(), B2S_ERR_BAD_ARG, "key: interaction chunk index out of range");
+                const HostInteraction& it = (*inter)[ch[q]];
+                for (size_t j = 0; j < it.fields.size(); j++) emit(OP_IFIELD, 0, slot_of[it.fields[j]], (uint32_t)j);
+                emit(OP_IEND, (it.type ? 1u : 0u) | (q + 1 == ch.size() ? 2u : 0u), slot_of[it.count_node], ch[q]);
+            }
+    }
+    out.slots_f = std::max<uint32_t>(nf, 1);
+    out.slots_e = std::max<uint32_t>(ne, 1);
+    return out;
 }
 
 static void root_monty(b2s_engine* e, const b2s_pcs_data* d, uint32_t out[8]) {
@@ -138,6 +202,7 @@ void pk_free(b2s_pk* pk) {
         if (a.prep_pcs) free_pcs(a.prep_pcs);
         if (a.prep_trace) b2s_matrix_free(a.prep_trace);
         if (a.d_program) e->dfree(a.d_program, a.program.size() * sizeof(uint4));
+        if (a.d_iprogram) e->dfree(a.d_iprogram, a.iprogram.size() * sizeof(uint4));
     }
     delete pk;
 }
@@ -149,7 +214,7 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n) {
         return w[i++];
     };
     B2_REQUIRE(rd() == 0x4B503242u, B2S_ERR_BAD_ARG, "key blob: bad magic");
-    B2_REQUIRE(rd() == 1, B2S_ERR_BAD_ARG, "key blob: unsupported version");
+    B2_REQUIRE(rd() == 2, B2S_ERR_BAD_ARG, "key blob: unsupported version");
     b2s_pk* pk = new b2s_pk();
     pk->eng = e;
     try {
@@ -169,8 +234,8 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n) {
             a.cached_widths.resize(nc);
             for (auto& c : a.cached_widths) c = rd();
             a.width_common = rd(); a.width_after = rd(); a.log_qd = rd(); a.num_pv = rd(); a.num_exposed = rd();
-            B2_REQUIRE(a.width_after == 0 && a.num_exposed == 0, B2S_ERR_BAD_ARG,
-                       "key: AIRs with interactions (after-challenge trace) are not supported in this build");
+            B2_REQUIRE(a.num_exposed == (a.width_after ? 1u : 0u) && a.width_after < (1u << 20), B2S_ERR_BAD_ARG,
+                       "key: after-challenge shape");
             if (a.log_qd > e->params.log_blowup) fail(B2S_ERR_CONSTRAINT_DEGREE, "key: quotient degree exceeds the engine's blowup");
             if (a.width_prep) {
                 for (int j = 0; j < 8; j++) a.prep_commit[j] = Fp::from_canonical(rd()).v;
@@ -197,11 +262,46 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n) {
             B2_REQUIRE(ncst <= n - i, B2S_ERR_BAD_ARG, "key blob truncated (constraints)");
             std::vector<uint32_t> cidx(ncst);
             for (auto& c : cidx) c = rd();
-            compile_dag(a, nodes, cidx);
-            if (!a.program.empty()) {
-                a.d_program = (uint4*)e->dmalloc(a.program.size() * sizeof(uint4));
-                B2_CUDA(cudaMemcpyAsync(a.d_program, a.program.data(), a.program.size() * sizeof(uint4), cudaMemcpyHostToDevice,
-                                        e->stream));
+            const uint32_t ni = rd();
+            B2_REQUIRE(ni <= n - i, B2S_ERR_BAD_ARG, "key blob truncated (interactions)");
+            std::vector<HostInteraction> inter(ni);
+            for (auto& it : inter) {
+                it.bus = rd(); it.type = rd(); it.count_node = rd();
+                const uint32_t nf = rd();
+                B2_REQUIRE(nf <= n - i, B2S_ERR_BAD_ARG, "key blob truncated (interaction fields)");
+                it.fields.resize(nf);
+                for (auto& f : it.fields) f = rd();
+                a.inter_bus.push_back(it.bus);
+                a.inter_len.push_back(nf);
+                a.max_fields = std::max(a.max_fields, nf);
+            }
+            const uint32_t nch = rd();
+            B2_REQUIRE(nch <= n - i, B2S_ERR_BAD_ARG, "key blob truncated (chunks)");
+            std::vector<std::vector<uint32_t>> chunks(nch);
+            for (auto& chv : chunks) {
+                const uint32_t len = rd();
+                B2_REQUIRE(len <= n - i, B2S_ERR_BAD_ARG, "key blob truncated (chunk)");
+                chv.resize(len);
+                for (auto& x : chv) x = rd();
+            }
+            B2_REQUIRE((ni == 0) == (a.width_after == 0) && (a.width_after == 0 || a.width_after == nch + 1), B2S_ERR_BAD_ARG,
+                       "key: interaction / after-challenge shape mismatch");
+            a.num_chunks = nch;
+            auto up = [&](const std::vector<uint4>& prog) -> uint4* {
+                if (prog.empty()) return nullptr;
+                uint4* d = (uint4*)e->dmalloc(prog.size() * sizeof(uint4));
+                B2_CUDA(cudaMemcpyAsync(d, prog.data(), prog.size() * sizeof(uint4), cudaMemcpyHostToDevice, e->stream));
+                return d;
+            };
+            Compiled q = compile_dag(a, nodes, cidx, nullptr, nullptr);
+            a.program = std::move(q.program);
+            a.num_slots = q.slots_f; a.num_slots_e = q.slots_e; a.num_constraints = (uint32_t)cidx.size();
+            a.d_program = up(a.program);
+            if (ni) {
+                Compiled ip = compile_dag(a, nodes, {}, &inter, &chunks);
+                a.iprogram = std::move(ip.program);
+                a.islots = ip.slots_f;
+                a.d_iprogram = up(a.iprogram);
             }
         }
         B2_REQUIRE(i == n, B2S_ERR_BAD_ARG, "key blob: trailing words");
@@ -220,6 +320,7 @@ struct QuotientParams {
     const uint32_t* const* cols;   // LDE column base pointers, [preprocessed][part 0][part 1]...
     const uint32_t* publics;       // Montgomery
     const uint32_t* alpha_pows;    // [num_constraints][4], alpha^j
+    const uint32_t* ef_consts;     // LogUp challenges [2][4] then the AIR's exposed cumulative sum [4]
     uint32_t* out;                 // qd chunk matrices, each 4 columns x N rows, column-major, natural row order
     uint32_t n, b, lq;
     uint32_t gq;                   // generator of order 2^(n+lq)
@@ -229,7 +330,12 @@ struct QuotientParams {
 
 // Thread r owns LDE row r (r < N*qd: the rows of the quotient domain are a prefix of the bit-reversed LDE), so the
 // `local` reads are coalesced; the `next` row differs from r by one XOR mask for whole warps except at carries.
-template <int NSLOT>
+// Base-field values live in slot[], extension-field values (4 words) in eslot[]; both are thread-local arrays
+// indexed by the program, i.e. local memory whose accesses are coalesced across the warp (same index in every lane).
+B2_D Fp4 ld4(const uint32_t* s) { return Fp4(Fp::raw(s[0]), Fp::raw(s[1]), Fp::raw(s[2]), Fp::raw(s[3])); }
+B2_D void st4(uint32_t* s, const Fp4& v) { s[0] = v.c[0].v; s[1] = v.c[1].v; s[2] = v.c[2].v; s[3] = v.c[3].v; }
+
+template <int NSLOT, int NE>
 __global__ void __launch_bounds__(128) quotient_kernel(QuotientParams p) {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t lm = p.n + p.b;
@@ -246,6 +352,7 @@ __global__ void __launch_bounds__(128) quotient_kernel(QuotientParams p) {
     bool have_first = false, have_last = false;
     Fp is_first, is_last;
     uint32_t slot[NSLOT];
+    uint32_t eslot[NE * 4];
     Fp acc[4];
     for (uint32_t pc = 0; pc < p.prog_len; pc++) {
         const uint4 ins = __ldg(p.program + pc);
@@ -266,11 +373,33 @@ __global__ void __launch_bounds__(128) quotient_kernel(QuotientParams p) {
             case OP_SUB: slot[ins.y] = (Fp::raw(slot[ins.z]) - Fp::raw(slot[ins.w])).v; break;
             case OP_NEG: slot[ins.y] = (-Fp::raw(slot[ins.z])).v; break;
             case OP_MUL: slot[ins.y] = (Fp::raw(slot[ins.z]) * Fp::raw(slot[ins.w])).v; break;
-            default: {  // OP_ACC
+            case OP_ACC: {
                 const uint4 ap = __ldg(reinterpret_cast<const uint4*>(p.alpha_pows) + ins.w);
                 const Fp v = Fp::raw(slot[ins.z]);
                 acc[0] += v * Fp::raw(ap.x); acc[1] += v * Fp::raw(ap.y);
                 acc[2] += v * Fp::raw(ap.z); acc[3] += v * Fp::raw(ap.w);
+                break;
+            }
+            case OP_LOADP: {
+                uint32_t* d = eslot + 4 * ins.y;
+#pragma unroll
+                for (int e = 0; e < 4; e++) d[e] = __ldg(p.cols[ins.z + e] + rows[ins.w]);
+                break;
+            }
+            case OP_CHAL: st4(eslot + 4 * ins.y, ld4(p.ef_consts + 4 * ins.z)); break;
+            case OP_EXPOSED: st4(eslot + 4 * ins.y, ld4(p.ef_consts + 8 + 4 * ins.z)); break;
+            case OP_ADD_EE: st4(eslot + 4 * ins.y, ld4(eslot + 4 * ins.z) + ld4(eslot + 4 * ins.w)); break;
+            case OP_ADD_EF: st4(eslot + 4 * ins.y, ld4(eslot + 4 * ins.z) + Fp::raw(slot[ins.w])); break;
+            case OP_SUB_EE: st4(eslot + 4 * ins.y, ld4(eslot + 4 * ins.z) - ld4(eslot + 4 * ins.w)); break;
+            case OP_SUB_EF: st4(eslot + 4 * ins.y, ld4(eslot + 4 * ins.z) - Fp::raw(slot[ins.w])); break;
+            case OP_SUB_FE: st4(eslot + 4 * ins.y, -(ld4(eslot + 4 * ins.w) - Fp::raw(slot[ins.z]))); break;
+            case OP_NEG_E: st4(eslot + 4 * ins.y, -ld4(eslot + 4 * ins.z)); break;
+            case OP_MUL_EE: st4(eslot + 4 * ins.y, ld4(eslot + 4 * ins.z) * ld4(eslot + 4 * ins.w)); break;
+            case OP_MUL_EF: st4(eslot + 4 * ins.y, ld4(eslot + 4 * ins.z) * Fp::raw(slot[ins.w])); break;
+            default: {  // OP_ACC_E
+                const Fp4 t = ld4(eslot + 4 * ins.z) * ld4(p.alpha_pows + 4 * ins.w);
+#pragma unroll
+                for (int c = 0; c < 4; c++) acc[c] += t.c[c];
             }
         }
     }
@@ -281,21 +410,136 @@ __global__ void __launch_bounds__(128) quotient_kernel(QuotientParams p) {
     for (int c = 0; c < 4; c++) p.out[((uint64_t)qi * 4 + c) * N + row] = (acc[c] * iz).v;
 }
 
-template <int NSLOT>
+template <int NSLOT, int NE>
 static void launch_quotient_t(b2s_engine* e, const QuotientParams& p) {
     const uint32_t rows = 1u << (p.n + p.lq);
-    quotient_kernel<NSLOT><<<(rows + 127) / 128, 128, 0, e->stream>>>(p);
+    quotient_kernel<NSLOT, NE><<<(rows + 127) / 128, 128, 0, e->stream>>>(p);
     B2_CHECK_LAUNCH();
     e->launches[3]++;
 }
-static void launch_quotient(b2s_engine* e, uint32_t slots, const QuotientParams& p) {
-    if (slots <= 32) launch_quotient_t<32>(e, p);
-    else if (slots <= 128) launch_quotient_t<128>(e, p);
-    else if (slots <= 512) launch_quotient_t<512>(e, p);
-    else if (slots <= 2048) launch_quotient_t<2048>(e, p);
-    else if (slots <= 8192) launch_quotient_t<8192>(e, p);
+template <int NSLOT>
+static void launch_quotient_e(b2s_engine* e, uint32_t eslots, const QuotientParams& p) {
+    if (eslots <= 1) launch_quotient_t<NSLOT, 1>(e, p);
+    else if (eslots <= 64) launch_quotient_t<NSLOT, 64>(e, p);
+    else if (eslots <= 1024) launch_quotient_t<NSLOT, 1024>(e, p);
+    else fail(B2S_ERR_CONSTRAINT_DEGREE, "quotient: constraint program needs more than 1024 live extension-field values");
+}
+static void launch_quotient(b2s_engine* e, uint32_t slots, uint32_t eslots, const QuotientParams& p) {
+    if (slots <= 32) launch_quotient_e<32>(e, eslots, p);
+    else if (slots <= 128) launch_quotient_e<128>(e, eslots, p);
+    else if (slots <= 512) launch_quotient_e<512>(e, eslots, p);
+    else if (slots <= 2048) launch_quotient_e<2048>(e, eslots, p);
+    else if (slots <= 8192) launch_quotient_e<8192>(e, eslots, p);
     else fail(B2S_ERR_CONSTRAINT_DEGREE, "quotient: constraint program needs more than 8192 live values");
 }
+
+// ---- FRI-LogUp after-challenge trace (stark/mod.rs:307-358; formula: DESIGN.md 4) ----------------------------------
+struct LogupParams {
+    const uint4* program;
+    uint32_t prog_len;
+    const uint32_t* const* cols;   // TRACE column base pointers (height N), [preprocessed][cached parts][common]
+    const uint32_t* publics;
+    const uint32_t* betas;         // [max_fields + 1][4], beta^j
+    const uint32_t* consts;        // [num_interactions][4]: alpha + beta^len * (bus + 1)
+    uint32_t* out;                 // after-challenge matrix, 4*(chunks+1) columns x N rows, column-major
+    uint32_t* row_sums;            // 4 planes x N: sum over chunks of this row's reciprocal sums
+    uint32_t n;
+};
+// one thread per trace row (natural order): evaluates message fields and counts, then per chunk
+//   perm_c[row] = sum_{i in chunk} (+-count_i) / (alpha + sum_j beta^j field_ij + beta^len_i (bus_i + 1))
+template <int NSLOT>
+__global__ void __launch_bounds__(128) logup_kernel(LogupParams p) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t N = 1u << p.n;
+    if (r >= N) return;
+    const uint32_t rows[2] = {r, (r + 1) & (N - 1)};
+    uint32_t slot[NSLOT];
+    Fp4 den = Fp4::zero(), chunk = Fp4::zero(), total = Fp4::zero();
+    uint32_t c = 0;
+    for (uint32_t pc = 0; pc < p.prog_len; pc++) {
+        const uint4 ins = __ldg(p.program + pc);
+        switch (ins.x) {
+            case OP_LOAD: slot[ins.y] = __ldg(p.cols[ins.z] + rows[ins.w]); break;
+            case OP_PUBLIC: slot[ins.y] = __ldg(p.publics + ins.z); break;
+            case OP_CONST: slot[ins.y] = ins.z; break;
+            case OP_FIRST: slot[ins.y] = r == 0 ? R_MOD_P : 0u; break;
+            case OP_LAST: slot[ins.y] = r == N - 1 ? R_MOD_P : 0u; break;
+            case OP_TRANS: slot[ins.y] = r == N - 1 ? 0u : R_MOD_P; break;
+            case OP_ADD: slot[ins.y] = (Fp::raw(slot[ins.z]) + Fp::raw(slot[ins.w])).v; break;
+            case OP_SUB: slot[ins.y] = (Fp::raw(slot[ins.z]) - Fp::raw(slot[ins.w])).v; break;
+            case OP_NEG: slot[ins.y] = (-Fp::raw(slot[ins.z])).v; break;
+            case OP_MUL: slot[ins.y] = (Fp::raw(slot[ins.z]) * Fp::raw(slot[ins.w])).v; break;
+            case OP_IFIELD: den += ld4(p.betas + 4 * ins.w) * Fp::raw(slot[ins.z]); break;
+            default: {  // OP_IEND
+                den += ld4(p.consts + 4 * ins.w);
+                Fp cnt = Fp::raw(slot[ins.z]);
+                if (ins.y & 1) cnt = -cnt;
+                chunk += fp4_inv(den) * cnt;
+                den = Fp4::zero();
+                if (ins.y & 2) {
+#pragma unroll
+                    for (int e = 0; e < 4; e++) p.out[((uint64_t)4 * c + e) * N + r] = chunk.c[e].v;
+                    total += chunk;
+                    chunk = Fp4::zero();
+                    c++;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < 4; e++) p.row_sums[(uint64_t)e * N + r] = total.c[e].v;
+}
+static void launch_logup(b2s_engine* e, uint32_t slots, const LogupParams& p) {
+    const uint32_t N = 1u << p.n;
+    const dim3 grid((N + 127) / 128);
+    if (slots <= 32) logup_kernel<32><<<grid, 128, 0, e->stream>>>(p);
+    else if (slots <= 256) logup_kernel<256><<<grid, 128, 0, e->stream>>>(p);
+    else if (slots <= 2048) logup_kernel<2048><<<grid, 128, 0, e->stream>>>(p);
+    else fail(B2S_ERR_CONSTRAINT_DEGREE, "logup: interaction program needs more than 2048 live values");
+    B2_CHECK_LAUNCH();
+    e->launches[3]++;
+}
+
+// inclusive prefix sums (mod p) along each of the 4 planes: blocks of 1024 elements, block totals scanned recursively
+constexpr int SCAN_THREADS = 256, SCAN_ITEMS = 4, SCAN_BLOCK = SCAN_THREADS * SCAN_ITEMS;
+__global__ void __launch_bounds__(SCAN_THREADS) scan_block_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
+                                                                  uint32_t* __restrict__ totals, uint32_t n, uint32_t nblocks) {
+    __shared__ uint32_t sm[SCAN_THREADS];
+    const uint32_t plane = blockIdx.y;
+    const uint32_t base = blockIdx.x * SCAN_BLOCK + threadIdx.x * SCAN_ITEMS;
+    Fp v[SCAN_ITEMS];
+    Fp run = Fp::zero();
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        if (base + k < n) run += Fp::raw(in[(uint64_t)plane * n + base + k]);
+        v[k] = run;
+    }
+    sm[threadIdx.x] = run.v;
+    __syncthreads();
+    for (int off = 1; off < SCAN_THREADS; off <<= 1) {
+        Fp t = Fp::raw(sm[threadIdx.x]);
+        if ((int)threadIdx.x >= off) t += Fp::raw(sm[threadIdx.x - off]);
+        __syncthreads();
+        sm[threadIdx.x] = t.v;
+        __syncthreads();
+    }
+    const Fp prefix = threadIdx.x ? Fp::raw(sm[threadIdx.x - 1]) : Fp::zero();
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++)
+        if (base + k < n) out[(uint64_t)plane * n + base + k] = (v[k] + prefix).v;
+    if (totals && threadIdx.x == SCAN_THREADS - 1) totals[(uint64_t)plane * nblocks + blockIdx.x] = sm[SCAN_THREADS - 1];
+}
+__global__ void scan_add_kernel(uint32_t* __restrict__ data, const uint32_t* __restrict__ block_prefix, uint32_t n, uint32_t nblocks) {
+    const uint32_t plane = blockIdx.y;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t blk = i / SCAN_BLOCK;
+    if (!blk) return;
+    uint32_t* d = data + (uint64_t)plane * n + i;
+    *d = (Fp::raw(*d) + Fp::raw(block_prefix[(uint64_t)plane * nblocks + blk - 1])).v;
+}
+struct Scratch;
+static void scan_planes(b2s_engine* e, Scratch& scratch, const uint32_t* in, uint32_t* out, uint32_t n);
 
 // ---- out-of-domain evaluation (barycentric over LDE block 0) ---------------------------------------------------------
 // Block 0 of an LDE of a height-N trace holds p(x_i), x_i = g * w_N^{bitrev_n(i)}, i < N. For z off the coset:
@@ -454,6 +698,21 @@ struct Scratch {  // device buffers released when the proof is done (or abandone
     }
 };
 
+static void scan_planes(b2s_engine* e, Scratch& scratch, const uint32_t* in, uint32_t* out, uint32_t n) {
+    const uint32_t nblocks = (n + SCAN_BLOCK - 1) / SCAN_BLOCK;
+    uint32_t* totals = nblocks > 1 ? scratch.words((size_t)4 * nblocks) : nullptr;
+    scan_block_kernel<<<dim3(nblocks, 4), SCAN_THREADS, 0, e->stream>>>(in, out, totals, n, nblocks);
+    B2_CHECK_LAUNCH();
+    e->launches[3]++;
+    if (nblocks > 1) {
+        uint32_t* prefix = scratch.words((size_t)4 * nblocks);
+        scan_planes(e, scratch, totals, prefix, nblocks);
+        scan_add_kernel<<<dim3((n + 255) / 256, 4), 256, 0, e->stream>>>(out, prefix, n, nblocks);
+        B2_CHECK_LAUNCH();
+        e->launches[3]++;
+    }
+}
+
 struct ByteWriter {
     std::vector<uint8_t>& buf;
     void u32(uint32_t x) { for (int i = 0; i < 4; i++) buf.push_back((uint8_t)(x >> (8 * i))); }
@@ -489,6 +748,32 @@ static void upload_ef_powers(b2s_engine* e, uint32_t* d, const Fp4& base, size_t
     B2_CUDA(cudaStreamSynchronize(e->stream));  // h is a stack-lifetime buffer
 }
 
+// minimum proof-of-work witness for the transcript state `ch` (duplex.rs:122-130); advances the transcript
+static Fp grind_device(b2s_engine* e, Scratch& scratch, HostChallenger& ch, unsigned bits) {
+    B2_REQUIRE(bits < 31, B2S_ERR_BAD_ARG, "prove: proof-of-work bits too large");
+    uint32_t* d_res = scratch.words(1);
+    PowParams pp{};
+    for (int i = 0; i < 16; i++) pp.st[i] = ch.st[i].v;
+    pp.in_ptr = (uint32_t)ch.in_ptr;
+    pp.bits = bits;
+    uint32_t found = 0xFFFFFFFFu;
+    const uint32_t batch = 1u << 20;
+    for (uint64_t base = 0; base < P && found == 0xFFFFFFFFu; base += batch) {
+        pp.base = (uint32_t)base;
+        B2_CUDA(cudaMemsetAsync(d_res, 0xFF, 4, e->stream));
+        pow_grind_kernel<<<batch / 128, 128, 0, e->stream>>>(pp, batch, d_res);
+        B2_CHECK_LAUNCH();
+        e->launches[3]++;
+        e->permutations += batch;
+        B2_CUDA(cudaMemcpyAsync(&found, d_res, 4, cudaMemcpyDeviceToHost, e->stream));
+        B2_CUDA(cudaStreamSynchronize(e->stream));
+    }
+    B2_REQUIRE(found != 0xFFFFFFFFu, B2S_ERR_INTERNAL, "prove: no proof-of-work witness exists");
+    const Fp witness = Fp::from_canonical(found);
+    B2_REQUIRE(ch.check_witness(bits, witness), B2S_ERR_INTERNAL, "prove: device proof-of-work witness rejected by the host transcript");
+    return witness;
+}
+
 // ---- prove -------------------------------------------------------------------------------------------------------------------
 void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_airs, std::vector<uint8_t>& out) {
     B2_REQUIRE(pk->eng == e, B2S_ERR_BAD_ARG, "prove: key was loaded on a different engine");
@@ -521,6 +806,12 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             h = hc;
         }
         B2_REQUIRE(h && is_pow2(h), B2S_ERR_SHAPE, "prove: trace height must be a power of two");
+        if (k.width_after)
+            for (uint32_t p = 0; p < a.n_cached; p++) {
+                const b2s_matrix* t = a.cached_traces ? a.cached_traces[p] : nullptr;
+                B2_REQUIRE(t && t->width == k.cached_widths[p] && t->height == h, B2S_ERR_SHAPE,
+                           "prove: an AIR with interactions needs its cached main traces (cached_traces)");
+            }
         logn[i] = log2_exact(h);
         B2_REQUIRE(logn[i] + b <= TWO_ADICITY, B2S_ERR_SHAPE, "prove: trace too tall for this blowup");
         B2_REQUIRE(!k.width_prep || k.prep_log_height == logn[i], B2S_ERR_SHAPE, "prove: preprocessed trace height mismatch");
@@ -557,6 +848,90 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     }
     for (auto& c : main_commits) ch.observe_digest(c.data());
     for (size_t i = 0; i < n_airs; i++) ch.observe_canonical(logn[i]);
+
+    // ---- FRI-LogUp challenge phase (stark/mod.rs:307-358): PoW, two challenges, one after-challenge matrix per
+    // interacting AIR = [reciprocal sum of each chunk | running sum phi], all committed in one tree
+    bool phase = false;
+    for (auto* k : keys) phase |= k->width_after != 0;
+    Fp logup_witness;
+    Fp4 challenges[2];
+    std::vector<Fp4> cumsum(n_airs, Fp4::zero());
+    std::vector<size_t> after_of;
+    std::vector<b2s_matrix> after_views;
+    b2s_pcs_data* after_pcs = nullptr;
+    std::array<uint32_t, 8> after_commit{};
+    if (phase) {
+        StageScope ls(e, ST_QUOTIENT);
+        logup_witness = grind_device(e, scratch, ch, pk->log_up_pow_bits);
+        challenges[0] = ch.sample_ext();
+        challenges[1] = ch.sample_ext();
+        for (size_t i = 0; i < n_airs; i++) if (keys[i]->width_after) after_of.push_back(i);
+        after_views.reserve(after_of.size());
+        std::vector<uint32_t*> last_rows;
+        for (size_t i : after_of) {
+            const AirKeyDev& k = *keys[i];
+            const unsigned n = logn[i];
+            const uint64_t N = (uint64_t)1 << n;
+            std::vector<const uint32_t*> cols;
+            auto push_cols = [&](const b2s_matrix* m) { for (uint64_t c = 0; c < m->width; c++) cols.push_back(m->d + c * m->height); };
+            if (k.width_prep) push_cols(k.prep_trace);
+            for (uint32_t p = 0; p < airs[i].n_cached; p++) push_cols(airs[i].cached_traces[p]);
+            if (k.width_common) push_cols(airs[i].common_main);
+            // host constants: beta powers, per-interaction alpha + beta^len (bus + 1), public values
+            std::vector<uint32_t> hc;
+            Fp4 bp = Fp4::one();
+            std::vector<Fp4> betas(k.max_fields + 1);
+            for (uint32_t j = 0; j <= k.max_fields; j++) { betas[j] = bp; bp = bp * challenges[1]; }
+            for (auto& v : betas) for (int c = 0; c < 4; c++) hc.push_back(v.c[c].v);
+            const size_t consts_off = hc.size();
+            for (size_t t = 0; t < k.inter_bus.size(); t++) {
+                const Fp4 v = challenges[0] + betas[k.inter_len[t]] * Fp::from_canonical((k.inter_bus[t] + 1) % P);
+                for (int c = 0; c < 4; c++) hc.push_back(v.c[c].v);
+            }
+            const size_t pv_off = hc.size();
+            for (uint32_t j = 0; j < k.num_pv; j++) hc.push_back(Fp::from_canonical(airs[i].public_values[j]).v);
+            hc.push_back(0);
+            uint32_t* d_hc = scratch.words(hc.size());
+            const uint32_t** d_cols = (const uint32_t**)scratch.bytes(std::max<size_t>(cols.size(), 1) * sizeof(void*));
+            if (!cols.empty()) B2_CUDA(cudaMemcpyAsync(d_cols, cols.data(), cols.size() * sizeof(void*), cudaMemcpyHostToDevice, e->stream));
+            B2_CUDA(cudaMemcpyAsync(d_hc, hc.data(), hc.size() * 4, cudaMemcpyHostToDevice, e->stream));
+            B2_CUDA(cudaStreamSynchronize(e->stream));
+            LogupParams lp{};
+            lp.program = k.d_iprogram; lp.prog_len = (uint32_t)k.iprogram.size();
+            lp.cols = d_cols; lp.publics = d_hc + pv_off; lp.betas = d_hc; lp.consts = d_hc + consts_off;
+            lp.out = scratch.words((size_t)4 * k.width_after * N);
+            lp.row_sums = scratch.words((size_t)4 * N);
+            lp.n = n;
+            launch_logup(e, k.islots, lp);
+            uint32_t* phi = lp.out + (size_t)4 * k.num_chunks * N;
+            scan_planes(e, scratch, lp.row_sums, phi, (uint32_t)N);
+            last_rows.push_back(phi);
+            b2s_matrix v;
+            v.eng = e; v.d = lp.out; v.height = N; v.width = (uint64_t)4 * k.width_after; v.owned = false;
+            after_views.push_back(v);
+        }
+        // cumulative sums = last row of each phi column
+        {
+            std::vector<OpenDesc> descs;
+            for (size_t a = 0; a < after_of.size(); a++) {
+                const uint64_t N = (uint64_t)1 << logn[after_of[a]];
+                descs.push_back(OpenDesc{last_rows[a], N, N - 1, 4, (uint32_t)(4 * a)});
+            }
+            std::vector<uint32_t> sums(4 * after_of.size());
+            gather_rows(e, descs, sums.size(), sums.data());
+            for (size_t a = 0; a < after_of.size(); a++) {
+                Fp4& cs = cumsum[after_of[a]];
+                for (int c = 0; c < 4; c++) cs.c[c] = Fp::from_canonical(sums[4 * a + c]);
+                ch.observe_ext(cs);
+            }
+        }
+        std::vector<const b2s_matrix*> ptrs;
+        for (auto& v : after_views) ptrs.push_back(&v);
+        after_pcs = commit_matrices(e, ptrs.data(), nullptr, ptrs.size());
+        scratch.pcs.push_back(after_pcs);
+        root_monty(e, after_pcs, after_commit.data());
+        ch.observe_digest(after_commit.data());
+    }
     const Fp4 alpha = ch.sample_ext();
 
     // ---- quotient (stark/mod.rs:366-416; fri/domain.rs:59-155)
@@ -585,6 +960,14 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
                 size_t pos = std::find(common_of.begin(), common_of.end(), i) - common_of.begin();
                 push_cols(common_pcs->mats[pos]);
             }
+            std::vector<uint32_t> efc(12, 0);
+            if (k.width_after) {
+                size_t pos = std::find(after_of.begin(), after_of.end(), i) - after_of.begin();
+                push_cols(after_pcs->mats[pos]);
+                for (int c = 0; c < 4; c++) { efc[c] = challenges[0].c[c].v; efc[4 + c] = challenges[1].c[c].v; efc[8 + c] = cumsum[i].c[c].v; }
+            }
+            uint32_t* d_efc = scratch.words(12);
+            B2_CUDA(cudaMemcpyAsync(d_efc, efc.data(), 48, cudaMemcpyHostToDevice, e->stream));
             const uint32_t** d_cols = (const uint32_t**)scratch.bytes(std::max<size_t>(cols.size(), 1) * sizeof(void*));
             uint32_t* d_pv = scratch.words(std::max<uint32_t>(k.num_pv, 1));
             std::vector<uint32_t> pv(std::max<uint32_t>(k.num_pv, 1), 0);
@@ -594,7 +977,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             B2_CUDA(cudaStreamSynchronize(e->stream));
             QuotientParams qp{};
             qp.program = k.d_program; qp.prog_len = (uint32_t)k.program.size();
-            qp.cols = d_cols; qp.publics = d_pv; qp.alpha_pows = d_apow;
+            qp.cols = d_cols; qp.publics = d_pv; qp.alpha_pows = d_apow; qp.ef_consts = d_efc;
             qp.out = scratch.words(((size_t)4 << lq) * N);
             qp.n = n; qp.b = b; qp.lq = lq;
             const Fp gq = two_adic_generator(n + lq);
@@ -610,7 +993,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
                 qp.inv_zh[j] = fp_inv(zh).v;
                 wpow *= wq;
             }
-            launch_quotient(e, k.num_slots, qp);
+            launch_quotient(e, k.num_slots, k.num_slots_e, qp);
             Fp sh = Fp::raw(M_GENERATOR);
             for (uint32_t j = 0; j < (1u << lq); j++) {
                 b2s_matrix v;
@@ -647,6 +1030,12 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     {
         Round r{common_pcs, {}};
         for (size_t m = 0; m < common_of.size(); m++) r.mats.push_back(trace_mat(common_pcs->mats[m], common_of[m]));
+        rounds.push_back(r);
+    }
+    const size_t after_round = rounds.size();
+    if (phase) {
+        Round r{after_pcs, {}};
+        for (size_t m = 0; m < after_of.size(); m++) r.mats.push_back(trace_mat(after_pcs->mats[m], after_of[m]));
         rounds.push_back(r);
     }
     const size_t quotient_round = rounds.size();
@@ -802,31 +1191,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     }
     ch.observe_ext(final_poly);
     // (iv) proof of work: minimum witness (duplex.rs:122-130)
-    Fp pow_witness;
-    {
-        const unsigned bits = e->params.proof_of_work_bits;
-        B2_REQUIRE(bits < 31, B2S_ERR_BAD_ARG, "prove: proof_of_work_bits too large");
-        uint32_t* d_res = scratch.words(1);
-        PowParams pp{};
-        for (int i = 0; i < 16; i++) pp.st[i] = ch.st[i].v;
-        pp.in_ptr = (uint32_t)ch.in_ptr;
-        pp.bits = bits;
-        uint32_t found = 0xFFFFFFFFu;
-        const uint32_t batch = 1u << 20;
-        for (uint64_t base = 0; base < P && found == 0xFFFFFFFFu; base += batch) {
-            pp.base = (uint32_t)base;
-            B2_CUDA(cudaMemsetAsync(d_res, 0xFF, 4, e->stream));
-            pow_grind_kernel<<<batch / 128, 128, 0, e->stream>>>(pp, batch, d_res);
-            B2_CHECK_LAUNCH();
-            e->launches[3]++;
-            e->permutations += batch;
-            B2_CUDA(cudaMemcpyAsync(&found, d_res, 4, cudaMemcpyDeviceToHost, e->stream));
-            B2_CUDA(cudaStreamSynchronize(e->stream));
-        }
-        B2_REQUIRE(found != 0xFFFFFFFFu, B2S_ERR_INTERNAL, "prove: no proof-of-work witness exists");
-        pow_witness = Fp::from_canonical(found);
-        B2_REQUIRE(ch.check_witness(bits, pow_witness), B2S_ERR_INTERNAL, "prove: device proof-of-work witness rejected by the host transcript");
-    }
+    const Fp pow_witness = grind_device(e, scratch, ch, e->params.proof_of_work_bits);
     // (v) queries: every opening of every query in one gather (two_adic_pcs.rs:170-372; fri/mod.rs:72-135)
     const unsigned nq = e->params.num_queries;
     std::vector<uint32_t> indices(nq);
@@ -863,7 +1228,8 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     w.u32(1);  // CODEC_VERSION
     w.u32((uint32_t)main_commits.size());
     for (auto& c : main_commits) w.digest_monty(c.data());
-    w.u32(0);  // after_challenge commitments: no challenge phase
+    w.u32(phase ? 1 : 0);  // after_challenge commitments: one per challenge phase
+    if (phase) w.digest_monty(after_commit.data());
     w.digest_monty(quotient_commit.data());
     // FriProof
     w.u32((uint32_t)fri_commits.size());
@@ -906,7 +1272,11 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     for (size_t r = first_cached; r < common_round; r++) { w.u32(1); adjacent(rounds[r].mats[0]); }
     w.u32((uint32_t)rounds[common_round].mats.size());
     for (auto& m : rounds[common_round].mats) adjacent(m);
-    w.u32(0);  // after_challenge phases
+    w.u32(phase ? 1 : 0);  // after_challenge phases
+    if (phase) {
+        w.u32((uint32_t)rounds[after_round].mats.size());
+        for (auto& m : rounds[after_round].mats) adjacent(m);
+    }
     w.u32((uint32_t)n_airs);
     {
         size_t m = 0;
@@ -921,12 +1291,13 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     for (size_t i = 0; i < n_airs; i++) {
         w.u32(airs[i].air_id);
         w.u32(1u << logn[i]);
-        w.u32(0);  // exposed_values_after_challenge
+        if (keys[i]->width_after) { w.u32(1); w.u32(1); w.ef(cumsum[i]); }  // exposed_values_after_challenge: [phase][value]
+        else w.u32(0);
         w.u32(airs[i].n_public_values);
         w.words(airs[i].public_values, airs[i].n_public_values);
     }
     out.push_back(0);       // RapPhaseSeqKind::FriLogUp
-    w.u32(0xFFFFFFFFu);     // no logup witness
+    if (phase) w.f(logup_witness); else w.u32(0xFFFFFFFFu);
     B2_CUDA(cudaStreamSynchronize(e->stream));
 }
 

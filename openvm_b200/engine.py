@@ -163,11 +163,13 @@ class ProvingKey:
 @dataclass
 class AirProvingContext:
     """AirProvingContext{cached_mains, common_main, public_values} for one AIR (crates/vm/src/arch/vm.rs:588-599).
-    cached_mains are PcsData objects returned by device.commit([trace])."""
+    cached_mains are PcsData objects returned by device.commit([trace]); cached_traces the device matrices they
+    were committed from (CommittedTraceData carries both), needed only by AIRs with interactions."""
     air_id: int
     common_main: object = None
     public_values: object = ()
     cached_mains: tuple = ()
+    cached_traces: tuple = ()
 
 
 class B2Device:
@@ -310,6 +312,12 @@ class B2Engine:
             arr[i].air_id = a.air_id
             arr[i].n_cached = len(a.cached_mains)
             arr[i].cached = C.cast(cached, C.POINTER(C.c_void_p))
+            if a.cached_traces:
+                if len(a.cached_traces) != len(a.cached_mains):
+                    raise ValueError("cached_traces must match cached_mains")
+                traces = (C.c_void_p * len(a.cached_traces))(*[t._h for t in a.cached_traces])
+                keep.append(traces)
+                arr[i].cached_traces = C.cast(traces, C.POINTER(C.c_void_p))
             arr[i].common_main = a.common_main._h if a.common_main is not None else None
             arr[i].public_values = pv.ctypes.data_as(C.POINTER(C.c_uint32))
             arr[i].n_public_values = pv.size

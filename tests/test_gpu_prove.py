@@ -22,15 +22,15 @@ def gpu_prove(eng, key, inputs, air_objs):
     ctx, keep = [], []
     for air_id, mats, pvs in inputs:
         a = air_objs[air_id]
-        cached = []
+        cached, traces = [], []
         for m in mats[:len(a.cached_widths)]:
             dm = dev.transport_matrix_to_device(m)
             _, pcs = dev.commit([dm])
             cached.append(pcs)
-            keep.append(dm)
+            traces.append(dm)
         common = dev.transport_matrix_to_device(mats[-1])
         keep.append(common)
-        ctx.append(AirProvingContext(air_id, common, pvs, tuple(cached)))
+        ctx.append(AirProvingContext(air_id, common, pvs, tuple(cached), tuple(traces) if a.interactions else ()))
     proof = eng.prove(pk, ctx)
     pk.free()
     return proof
@@ -93,3 +93,68 @@ def test_blowup2_wide_chain(orc):
         eng.close()
     assert orc.stark_verify(key, proof, b, queries, pow_bits) is None
     assert proof == orc.stark_prove(key, [(0, parts, pv)], b, queries, pow_bits)
+
+
+# ---- FRI-LogUp challenge phase ------------------------------------------------------------------------------------------
+NONE = np.zeros(0, dtype=np.uint32)
+
+
+def check_same(orc, eng, key, inputs, air_objs, b, queries, pow_bits, expect=None):
+    proof = gpu_prove(eng, key, inputs, air_objs)
+    res = orc.stark_verify(key, proof, b, queries, pow_bits)
+    if expect is None:
+        assert res is None
+    else:
+        assert expect in res
+    assert proof == orc.stark_prove(key, inputs, b, queries, pow_bits)
+    return proof
+
+
+def test_logup_sender_receiver_bytes(orc):
+    from test_oracle_stark import interaction_traces
+    b, queries, pow_bits = 1, 5, 4
+    air_objs = [airs.fibonacci_air(), airs.dummy_interaction_air(2, True), airs.dummy_interaction_air(2, False)]
+    key = airs.key_blob(air_objs, log_up_pow_bits=5)
+    send, recv = interaction_traces(64, 128, 2, seed=4)
+    t0, pv0 = airs.fibonacci_trace(32)
+    inputs = [(0, [t0], pv0), (1, [send], NONE), (2, [recv], NONE)]
+    eng = make_engine(b, queries, pow_bits)
+    try:
+        check_same(orc, eng, key, inputs, air_objs, b, queries, pow_bits)
+        check_same(orc, eng, key, inputs[:1], air_objs, b, queries, pow_bits)   # no interacting AIR -> no phase
+        send2, recv2 = interaction_traces(64, 128, 2, seed=4, unbalanced=True)
+        check_same(orc, eng, key, [inputs[0], (1, [send2], NONE), (2, [recv2], NONE)], air_objs, b, queries, pow_bits,
+                   expect="NonZeroCumulativeSum")
+    finally:
+        eng.close()
+
+
+def test_logup_two_interactions_per_chunk_bytes(orc):
+    b, queries, pow_bits = 1, 4, 2
+    air_objs = [airs.lookup_chain_air(6), airs.lookup_chain_receiver()]
+    key = airs.key_blob(air_objs, log_up_pow_bits=3)
+    parts, pv = airs.chain_trace(air_objs[0], 64, seed=3)
+    recv = np.zeros((64, 4), dtype=np.uint32)
+    recv[:, 0] = 1
+    recv[:, 1:4] = parts[-1][::-1, 0:3]
+    eng = make_engine(b, queries, pow_bits)
+    try:
+        check_same(orc, eng, key, [(0, parts, pv), (1, [recv], NONE)], air_objs, b, queries, pow_bits)
+    finally:
+        eng.close()
+
+
+@pytest.mark.parametrize("n,b", [(64, 1), (1 << 13, 2)])
+def test_logup_prep_cached_rotated_fields_bytes(orc, n, b):
+    queries, pow_bits = 4, 3
+    a0 = airs.lookup_chain_air_parts(6, n, seed=2)
+    a1 = airs.multi_receiver_air([2, 3], 5)
+    air_objs = [a0, a1]
+    key = build_key(orc, air_objs, b)
+    parts, pv = airs.chain_trace(a0, n, seed=8)
+    recv = airs.lookup_chain_parts_receiver_trace(a0, parts)
+    eng = make_engine(b, queries, pow_bits)
+    try:
+        check_same(orc, eng, key, [(0, parts, pv), (1, [recv], NONE)], air_objs, b, queries, pow_bits)
+    finally:
+        eng.close()

@@ -161,3 +161,18 @@ def test_logup_two_interactions_per_chunk_with_constraints(orc):
     bad = recv.copy(); bad[5, 2] = (int(bad[5, 2]) + 1) % P
     p2 = orc.stark_prove(key, [(0, parts, pv), (1, [bad], none)], b, 4, 2)
     assert "NonZeroCumulativeSum" in orc.stark_verify(key, p2, b, 4, 2)
+
+
+@pytest.mark.parametrize("n,b", [(64, 1), (256, 2)])
+def test_logup_prep_cached_rotated_fields(orc, n, b):
+    a0 = airs.lookup_chain_air_parts(6, n, seed=2)
+    a1 = airs.multi_receiver_air([2, 3], 5)
+    key = build_key(orc, [a0, a1], b)
+    parts, pv = airs.chain_trace(a0, n, seed=8)
+    recv = airs.lookup_chain_parts_receiver_trace(a0, parts)
+    none = np.zeros(0, dtype=np.uint32)
+    proof = orc.stark_prove(key, [(0, parts, pv), (1, [recv], none)], b, 4, 3)
+    assert orc.stark_verify(key, proof, b, 4, 3) is None
+    bad = recv.copy(); bad[3, 6] = (int(bad[3, 6]) + 1) % P
+    p2 = orc.stark_prove(key, [(0, parts, pv), (1, [bad], none)], b, 4, 3)
+    assert "NonZeroCumulativeSum" in orc.stark_verify(key, p2, b, 4, 3)
