@@ -189,6 +189,21 @@ typedef struct {
 int32_t b2s_prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_airs, uint8_t** proof_bytes,
                   size_t* proof_len);
 
+/* Replay aid: the reference grinds in parallel and returns ANY valid witness, this library the minimum
+ * one. To reproduce a reference proof byte for byte, pass the witnesses found in that proof (canonical values);
+ * B2S_POW_SEARCH restores the search. A supplied witness that does not satisfy the transcript fails the proof. */
+#define B2S_POW_SEARCH 0xFFFFFFFFu
+int32_t b2s_engine_set_pow_witnesses(b2s_engine* e, uint32_t logup_witness, uint32_t fri_witness);
+
+/* engine.verify(&vk, &proof) -> Result<(), VerificationError>    crates/vm/src/arch/vm.rs:1074,1127;
+ *                                                                crates/sdk/src/lib.rs:735-737
+ * Decodes the wire-format proof (crates/sdk/src/codec.rs:332-642) and runs MultiTraceStarkVerifier::verify as
+ * restated in-tree (extensions/native/recursion/src/stark/mod.rs:108-1173) with the engine's FRI parameters against
+ * the verifying-key part of `pk`. Host-side like the reference's (milliseconds of sequential transcript work).
+ * Returns B2S_OK, or B2S_ERR_VERIFY_FAILED with b2s_last_error naming the reference's VerificationError variant
+ * (InvalidProofShape, InvalidOpeningArgument, InvalidPowWitness, NonZeroCumulativeSum, OodEvaluationMismatch ...). */
+int32_t b2s_verify(b2s_engine* e, const b2s_pk* pk, const uint8_t* proof_bytes, size_t proof_len);
+
 /* ---- primitives run on the device, for known-answer / parity tests ------------------------------------ */
 /* n states of 16 canonical words, permuted in place on the GPU */
 int32_t b2s_poseidon2_permute(b2s_engine* e, uint32_t* host_states, size_t n_states);

@@ -13,7 +13,9 @@ from .engine import (  # noqa: F401
     AirProvingContext,
     FriParameters,
     B2StarkError,
+    VerificationError,
     library_path,
 )
 
-__all__ = ["B2Engine", "B2Device", "DeviceMatrix", "PcsData", "ProvingKey", "AirProvingContext", "FriParameters", "B2StarkError", "library_path"]
+__all__ = ["B2Engine", "B2Device", "DeviceMatrix", "PcsData", "ProvingKey", "AirProvingContext", "FriParameters", "B2StarkError", "VerificationError",
+           "library_path"]

@@ -22,6 +22,9 @@ class Metrics(C.Structure):
                 ("poseidon2_permutations", C.c_uint64)]
 
 
+ERR_VERIFY_FAILED = -6
+
+
 class AirCtx(C.Structure):
     _fields_ = [("air_id", C.c_uint32), ("n_cached", C.c_uint32), ("cached", C.POINTER(C.c_void_p)),
                 ("cached_traces", C.POINTER(C.c_void_p)), ("common_main", C.c_void_p), ("public_values", C.POINTER(C.c_uint32)),
@@ -60,6 +63,8 @@ SIGNATURES = {
     "b2s_pcs_free": (None, [vp]),
     "b2s_pk_load": (C.c_int32, [vp, vp, C.c_size_t, C.POINTER(vp)]),
     "b2s_pk_free": (None, [vp]),
+    "b2s_engine_set_pow_witnesses": (C.c_int32, [vp, C.c_uint32, C.c_uint32]),
+    "b2s_verify": (C.c_int32, [vp, vp, C.c_char_p, C.c_size_t]),
     "b2s_prove": (C.c_int32, [vp, vp, vp, C.c_size_t, C.POINTER(vp), C.POINTER(C.c_size_t)]),
     "b2s_poseidon2_permute": (C.c_int32, [vp, vp, C.c_size_t]),
     "b2s_bench_modmul": (C.c_int32, [vp, C.c_uint64, C.c_uint32, C.c_int32, C.POINTER(C.c_double)]),

@@ -436,6 +436,24 @@ int32_t b2s_prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size
     });
 }
 
+int32_t b2s_engine_set_pow_witnesses(b2s_engine* e, uint32_t logup_witness, uint32_t fri_witness) {
+    if (!e) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] {
+        B2_REQUIRE((logup_witness == B2S_POW_SEARCH || logup_witness < P) && (fri_witness == B2S_POW_SEARCH || fri_witness < P),
+                   B2S_ERR_BAD_ARG, "pow witnesses must be canonical field elements or B2S_POW_SEARCH");
+        e->pow_override[0] = logup_witness;
+        e->pow_override[1] = fri_witness;
+    });
+}
+
+int32_t b2s_verify(b2s_engine* e, const b2s_pk* pk, const uint8_t* proof_bytes, size_t proof_len) {
+    if (!e || !pk || !proof_bytes) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] {
+        B2_REQUIRE(pk->eng == e, B2S_ERR_BAD_ARG, "verify: key was loaded on a different engine");
+        verify(e, pk, proof_bytes, proof_len);
+    });
+}
+
 size_t b2s_pcs_num_matrices(const b2s_pcs_data* d) { return d ? d->mats.size() : 0; }
 uint32_t b2s_pcs_log_max_height(const b2s_pcs_data* d) { return d ? d->log_max_height : 0; }
 const b2s_matrix* b2s_pcs_matrix(const b2s_pcs_data* d, size_t i) { return (d && i < d->mats.size()) ? d->mats[i] : nullptr; }

@@ -64,6 +64,7 @@ struct b2s_engine {
     std::vector<cudaEvent_t> event_pool;
     uint64_t launches[4] = {0, 0, 0, 0};  // lde, leaf, compress, other
     uint64_t permutations = 0;
+    uint32_t pow_override[2] = {0xFFFFFFFFu, 0xFFFFFFFFu};  // [logup, fri]; 0xFFFFFFFF = search for the minimum witness
     std::map<unsigned, b2::TwiddleSet*> twiddles;  // by log size
     std::map<uint64_t, b2::ScaleSet*> scales;      // by (logn, log_blowup, shift_in)
 
@@ -112,6 +113,9 @@ struct AirKeyDev {
     uint4* d_iprogram = nullptr;
     uint32_t islots = 0, num_chunks = 0, max_fields = 0;
     std::vector<uint32_t> inter_bus, inter_len;
+    // symbolic constraints as loaded ({kind, a, b, c} per node), kept for the verifier's evaluation at zeta
+    std::vector<uint4> nodes;
+    std::vector<uint32_t> constraint_idx;
     uint32_t total_cols() const {
         uint32_t t = width_prep + width_common;
         for (uint32_t w : cached_widths) t += w;
@@ -173,6 +177,7 @@ void gather_rows(b2s_engine* e, const std::vector<OpenDesc>& descs, size_t total
 // prover.cu
 b2s_pk* pk_load(b2s_engine* e, const uint32_t* words, size_t n);
 void pk_free(b2s_pk* pk);
+void verify(const b2s_engine* e, const b2s_pk* pk, const uint8_t* proof, size_t len);
 void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_airs, std::vector<uint8_t>& out);
 // api.cu helpers shared with the prover
 b2s_matrix* new_matrix(b2s_engine* e, uint64_t height, uint64_t width);

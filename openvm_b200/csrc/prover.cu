@@ -287,6 +287,8 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n) {
             B2_REQUIRE((ni == 0) == (a.width_after == 0) && (a.width_after == 0 || a.width_after == nch + 1), B2S_ERR_BAD_ARG,
                        "key: interaction / after-challenge shape mismatch");
             a.num_chunks = nch;
+            for (auto& nd : nodes) a.nodes.push_back(make_uint4(nd.kind, nd.a, nd.b, nd.c));
+            a.constraint_idx = cidx;
             auto up = [&](const std::vector<uint4>& prog) -> uint4* {
                 if (prog.empty()) return nullptr;
                 uint4* d = (uint4*)e->dmalloc(prog.size() * sizeof(uint4));
@@ -749,8 +751,13 @@ static void upload_ef_powers(b2s_engine* e, uint32_t* d, const Fp4& base, size_t
 }
 
 // minimum proof-of-work witness for the transcript state `ch` (duplex.rs:122-130); advances the transcript
-static Fp grind_device(b2s_engine* e, Scratch& scratch, HostChallenger& ch, unsigned bits) {
+static Fp grind_device(b2s_engine* e, Scratch& scratch, HostChallenger& ch, unsigned bits, uint32_t override_witness) {
     B2_REQUIRE(bits < 31, B2S_ERR_BAD_ARG, "prove: proof-of-work bits too large");
+    if (override_witness != 0xFFFFFFFFu) {
+        const Fp w = Fp::from_canonical(override_witness);
+        B2_REQUIRE(ch.check_witness(bits, w), B2S_ERR_BAD_ARG, "prove: the supplied proof-of-work witness does not satisfy the transcript");
+        return w;
+    }
     uint32_t* d_res = scratch.words(1);
     PowParams pp{};
     for (int i = 0; i < 16; i++) pp.st[i] = ch.st[i].v;
@@ -862,7 +869,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     std::array<uint32_t, 8> after_commit{};
     if (phase) {
         StageScope ls(e, ST_QUOTIENT);
-        logup_witness = grind_device(e, scratch, ch, pk->log_up_pow_bits);
+        logup_witness = grind_device(e, scratch, ch, pk->log_up_pow_bits, e->pow_override[0]);
         challenges[0] = ch.sample_ext();
         challenges[1] = ch.sample_ext();
         for (size_t i = 0; i < n_airs; i++) if (keys[i]->width_after) after_of.push_back(i);
@@ -1191,7 +1198,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     }
     ch.observe_ext(final_poly);
     // (iv) proof of work: minimum witness (duplex.rs:122-130)
-    const Fp pow_witness = grind_device(e, scratch, ch, e->params.proof_of_work_bits);
+    const Fp pow_witness = grind_device(e, scratch, ch, e->params.proof_of_work_bits, e->pow_override[1]);
     // (v) queries: every opening of every query in one gather (two_adic_pcs.rs:170-372; fri/mod.rs:72-135)
     const unsigned nq = e->params.num_queries;
     std::vector<uint32_t> indices(nq);

@@ -1,0 +1,498 @@
+// b2s_verify: StarkEngine::verify(&vk, &proof) for BabyBearPoseidon2Config.
+//
+// Replaces (reference, external): openvm-stark-backend `MultiTraceStarkVerifier::verify` called at
+// crates/vm/src/arch/vm.rs:1074,1127 and crates/sdk/src/lib.rs:735-737. The reference verifies on the host in a few
+// milliseconds and so does this file: it is sequential transcript work (a few thousand Poseidon2 permutations), no
+// device kernel is involved and none would help. Follows the in-tree twin step by step:
+//   extensions/native/recursion/src/stark/mod.rs:130-834   transcript, opening rounds
+//   extensions/native/recursion/src/stark/mod.rs:903-1126  constraint folding, quotient recombination
+//   extensions/native/recursion/src/fri/two_adic_pcs.rs:41-376, fri/mod.rs:33-299  PCS / FRI / MMCS verify_batch
+//   extensions/native/recursion/src/fri/domain.rs:59-155   selectors and zerofiers
+//   crates/sdk/src/codec.rs:332-642                        proof decoding
+#include "common.cuh"
+#include "host_challenger.hpp"
+
+#include <algorithm>
+#include <array>
+
+namespace b2 {
+namespace {
+
+[[noreturn]] void reject(const std::string& why) { fail(B2S_ERR_VERIFY_FAILED, why); }
+
+using Digest = std::array<Fp, 8>;
+
+struct AdjacentOpened { std::vector<Fp4> local, next; };
+struct BatchOpening { std::vector<std::vector<Fp>> opened_values; std::vector<Digest> opening_proof; };
+struct CommitPhaseStep { Fp4 sibling_value; std::vector<Digest> opening_proof; };
+struct QueryProof { std::vector<BatchOpening> input_proof; std::vector<CommitPhaseStep> commit_phase_openings; };
+struct AirProofData {
+    uint32_t air_id = 0, degree = 0;
+    std::vector<std::vector<Fp4>> exposed;
+    std::vector<Fp> public_values;
+};
+struct DecodedProof {
+    std::vector<Digest> main_commits, after_commits, fri_commits;
+    Digest quotient_commit;
+    std::vector<QueryProof> queries;
+    std::vector<Fp4> final_poly;
+    Fp pow_witness;
+    std::vector<AdjacentOpened> opened_prep;
+    std::vector<std::vector<AdjacentOpened>> opened_main, opened_after;
+    std::vector<std::vector<std::vector<Fp4>>> opened_quotient;
+    std::vector<AirProofData> per_air;
+    bool has_logup_witness = false;
+    Fp logup_witness;
+};
+
+// crates/sdk/src/codec.rs:272-320: lengths and field elements are u32 LE, EF = 4 words, digest = 8 words
+struct ProofReader {
+    const uint8_t* p;
+    size_t n, i = 0;
+    uint32_t u32() {
+        if (i + 4 > n) reject("InvalidProofShape: proof truncated");
+        uint32_t x = (uint32_t)p[i] | ((uint32_t)p[i + 1] << 8) | ((uint32_t)p[i + 2] << 16) | ((uint32_t)p[i + 3] << 24);
+        i += 4;
+        return x;
+    }
+    uint32_t len() {
+        uint32_t l = u32();
+        if ((size_t)l > n - i) reject("InvalidProofShape: length prefix exceeds the proof");
+        return l;
+    }
+    Fp f() {
+        uint32_t x = u32();
+        if (x >= P) reject("InvalidProofShape: non-canonical field element");
+        return Fp::from_canonical(x);
+    }
+    Fp4 ef() { Fp4 e; for (int k = 0; k < 4; k++) e.c[k] = f(); return e; }
+    Digest digest() { Digest d; for (int k = 0; k < 8; k++) d[k] = f(); return d; }
+    std::vector<Fp4> efs() { std::vector<Fp4> v(len()); for (auto& e : v) e = ef(); return v; }
+    std::vector<Fp> fs() { std::vector<Fp> v(len()); for (auto& e : v) e = f(); return v; }
+    std::vector<Digest> digests() { std::vector<Digest> v(len()); for (auto& d : v) d = digest(); return v; }
+    AdjacentOpened adj() { AdjacentOpened a; a.local = efs(); a.next = efs(); return a; }
+    std::vector<AdjacentOpened> adjs() { std::vector<AdjacentOpened> v(len()); for (auto& a : v) a = adj(); return v; }
+};
+
+DecodedProof decode(const uint8_t* bytes, size_t n) {
+    ProofReader r{bytes, n};
+    if (r.u32() != 1) reject("InvalidProofShape: codec version");
+    DecodedProof p;
+    p.main_commits = r.digests();
+    p.after_commits = r.digests();
+    p.quotient_commit = r.digest();
+    p.fri_commits = r.digests();
+    p.queries.resize(r.len());
+    for (auto& q : p.queries) {
+        q.input_proof.resize(r.len());
+        for (auto& b : q.input_proof) {
+            b.opened_values.resize(r.len());
+            for (auto& v : b.opened_values) v = r.fs();
+            b.opening_proof = r.digests();
+        }
+        q.commit_phase_openings.resize(r.len());
+        for (auto& s : q.commit_phase_openings) { s.sibling_value = r.ef(); s.opening_proof = r.digests(); }
+    }
+    p.final_poly = r.efs();
+    p.pow_witness = r.f();
+    p.opened_prep = r.adjs();
+    p.opened_main.resize(r.len());
+    for (auto& part : p.opened_main) part = r.adjs();
+    p.opened_after.resize(r.len());
+    for (auto& ph : p.opened_after) ph = r.adjs();
+    p.opened_quotient.resize(r.len());
+    for (auto& air : p.opened_quotient) {
+        air.resize(r.len());
+        for (auto& chunk : air) chunk = r.efs();
+    }
+    p.per_air.resize(r.len());
+    for (auto& a : p.per_air) {
+        a.air_id = r.u32();
+        a.degree = r.u32();
+        a.exposed.resize(r.len());
+        for (auto& v : a.exposed) v = r.efs();
+        a.public_values = r.fs();
+    }
+    if (r.i >= r.n || r.p[r.i++] != 0) reject("InvalidProofShape: rap phase kind");
+    const uint32_t wv = r.u32();
+    if (wv != 0xFFFFFFFFu) {
+        if (wv >= P) reject("InvalidProofShape: non-canonical logup witness");
+        p.has_logup_witness = true;
+        p.logup_witness = Fp::from_canonical(wv);
+    }
+    if (r.i != r.n) reject("InvalidProofShape: trailing bytes");
+    return p;
+}
+
+// PaddingFreeSponge<16, 8, 8> and TruncatedPermutation (crates/vm/src/arch/hasher/poseidon2.rs:33-43)
+struct HostHasher {
+    HostPoseidon2 perm;
+    Digest hash_rows(const std::vector<const std::vector<Fp>*>& rows) const {
+        Fp st[16];
+        int k = 0;
+        for (auto* row : rows)
+            for (Fp x : *row) {
+                st[k++] = x;
+                if (k == 8) { perm.permute(st); k = 0; }
+            }
+        if (k) perm.permute(st);
+        Digest d;
+        for (int j = 0; j < 8; j++) d[j] = st[j];
+        return d;
+    }
+    Digest compress(const Digest& l, const Digest& r) const {
+        Fp st[16];
+        for (int j = 0; j < 8; j++) { st[j] = l[j]; st[8 + j] = r[j]; }
+        perm.permute(st);
+        Digest d;
+        for (int j = 0; j < 8; j++) d[j] = st[j];
+        return d;
+    }
+};
+
+// Mmcs::verify_batch over matrices of mixed power-of-two heights (fri/mod.rs:185-299; poseidon2/README.md:33-41)
+bool verify_batch(const HostHasher& hh, const Digest& commit, const std::vector<unsigned>& log_heights, uint64_t index,
+                  const std::vector<std::vector<Fp>>& rows, const std::vector<Digest>& proof) {
+    const size_t n = log_heights.size();
+    if (rows.size() != n || n == 0) return false;
+    unsigned lmax = 0;
+    for (unsigned l : log_heights) lmax = std::max(lmax, l);
+    if (proof.size() != lmax) return false;
+    auto rows_at = [&](unsigned l) {
+        std::vector<const std::vector<Fp>*> v;
+        for (size_t k = 0; k < n; k++) if (log_heights[k] == l) v.push_back(&rows[k]);
+        return v;
+    };
+    Digest node = hh.hash_rows(rows_at(lmax));
+    for (unsigned i = 0; i < lmax; i++) {
+        node = ((index >> i) & 1) ? hh.compress(proof[i], node) : hh.compress(node, proof[i]);
+        auto inject = rows_at(lmax - 1 - i);
+        if (!inject.empty()) node = hh.compress(node, hh.hash_rows(inject));
+    }
+    for (int j = 0; j < 8; j++) if (node[j] != commit[j]) return false;
+    return true;
+}
+
+struct VerifyMat {
+    unsigned log_n;
+    std::vector<Fp4> points;
+    std::vector<const std::vector<Fp4>*> values;  // [point] -> columns
+};
+struct VerifyRound {
+    Digest commit;
+    std::vector<VerifyMat> mats;
+};
+
+Fp4 from_base(Fp x) { return Fp4(x); }
+Fp4 monomial_sum(const std::vector<Fp4>& v, size_t off) {  // sum_e v[off + e] * x^e  (stark/mod.rs:1035-1047)
+    Fp4 r = Fp4::zero();
+    for (int e = 0; e < 4; e++) {
+        Fp4 mono = Fp4::zero();
+        mono.c[e] = Fp::one();
+        r += mono * v[off + e];
+    }
+    return r;
+}
+
+// verify_two_adic_pcs + verify_query (two_adic_pcs.rs:41-376; fri/mod.rs:33-170)
+void verify_pcs(const HostHasher& hh, const std::vector<VerifyRound>& rounds, const DecodedProof& proof, unsigned log_max_height,
+                const b2s_fri_params& fp, HostChallenger& ch) {
+    const unsigned b = fp.log_blowup;
+    if (proof.final_poly.size() != 1) reject("InvalidProofShape: final_poly");
+    const Fp4 final_poly = proof.final_poly[0];
+    for (auto& r : rounds)
+        for (auto& m : r.mats)
+            for (auto* pt : m.values)
+                for (auto& v : *pt) ch.observe_ext(v);
+    const Fp4 alpha = ch.sample_ext();
+    if (proof.queries.size() != fp.num_queries) reject("InvalidProofShape: query count");
+    if (proof.fri_commits.size() != log_max_height) reject("InvalidProofShape: commit phase");
+    std::vector<Fp4> betas;
+    for (auto& c : proof.fri_commits) {
+        for (int j = 0; j < 8; j++) ch.observe(c[j]);
+        betas.push_back(ch.sample_ext());
+    }
+    ch.observe_ext(final_poly);
+    if (!ch.check_witness(fp.proof_of_work_bits, proof.pow_witness)) reject("InvalidPowWitness");
+    const unsigned L = log_max_height + b;
+    for (auto& qp : proof.queries) {
+        const uint64_t index = ch.sample_bits(L);
+        std::vector<Fp4> ro(TWO_ADICITY + 2, Fp4::zero()), alpha_pow(TWO_ADICITY + 2, Fp4::one());
+        if (qp.input_proof.size() != rounds.size()) reject("InvalidProofShape: input_proof");
+        for (size_t ri = 0; ri < rounds.size(); ri++) {
+            const VerifyRound& r = rounds[ri];
+            const BatchOpening& bo = qp.input_proof[ri];
+            if (bo.opened_values.size() != r.mats.size()) reject("InvalidProofShape: opened_values");
+            unsigned log_batch_max = 0;
+            std::vector<unsigned> log_heights;
+            for (auto& m : r.mats) { log_batch_max = std::max(log_batch_max, m.log_n + b); log_heights.push_back(m.log_n + b); }
+            for (size_t mi = 0; mi < r.mats.size(); mi++) {
+                const VerifyMat& m = r.mats[mi];
+                const unsigned h = m.log_n + b;
+                const Fp x = Fp::raw(M_GENERATOR) * fp_pow(two_adic_generator(h), bitrev32((uint32_t)(index >> (L - h)), h));
+                const std::vector<Fp>& px = bo.opened_values[mi];
+                for (size_t pi = 0; pi < m.points.size(); pi++) {
+                    const std::vector<Fp4>& pz = *m.values[pi];
+                    if (pz.size() != px.size()) reject("InvalidProofShape: opened row width");
+                    Fp4 acc = Fp4::zero(), ap = Fp4::one();
+                    for (size_t t = 0; t < pz.size(); t++) { acc += (pz[t] - px[t]) * ap; ap = ap * alpha; }
+                    ro[h] += acc * fp4_inv(m.points[pi] - x) * alpha_pow[h];
+                    alpha_pow[h] = alpha_pow[h] * ap;
+                }
+            }
+            if (!verify_batch(hh, r.commit, log_heights, index >> (L - log_batch_max), bo.opened_values, bo.opening_proof))
+                reject("InvalidOpeningArgument: input batch");
+        }
+        Fp4 folded = ro[L];
+        Fp x = fp_pow(two_adic_generator(L), bitrev32((uint32_t)index, L));
+        if (qp.commit_phase_openings.size() != proof.fri_commits.size()) reject("InvalidProofShape: commit_phase_openings");
+        for (size_t i = 0; i < proof.fri_commits.size(); i++) {
+            const unsigned log_folded = L - (unsigned)i - 1;
+            const CommitPhaseStep& st = qp.commit_phase_openings[i];
+            const unsigned bit = (index >> i) & 1;
+            Fp4 evals[2] = {folded, folded};
+            evals[bit ^ 1] = st.sibling_value;
+            std::vector<std::vector<Fp>> row(1);
+            for (int k = 0; k < 2; k++) for (int c = 0; c < 4; c++) row[0].push_back(evals[k].c[c]);
+            if (!verify_batch(hh, proof.fri_commits[i], {log_folded}, index >> (i + 1), row, st.opening_proof))
+                reject("InvalidOpeningArgument: commit phase");
+            const Fp xs0 = bit ? -x : x, xs1 = bit ? x : -x;
+            folded = evals[0] + (evals[1] - evals[0]) * (betas[i] - xs0) * fp_inv(xs1 - xs0);
+            x = x * x;
+            folded += betas[i] * betas[i] * ro[log_folded];
+        }
+        if (folded != final_poly) reject("FinalPolyMismatch");
+    }
+}
+
+}  // namespace
+
+// every node of the symbolic DAG at the out-of-domain point, folded Horner-style over the constraint list
+// (stark/mod.rs:1023-1085)
+struct ZetaInputs {
+    const std::vector<Fp4>* prep[2] = {nullptr, nullptr};
+    std::vector<const std::vector<Fp4>*> main[2];
+    std::vector<Fp4> perm[2];
+    const std::vector<Fp>* publics = nullptr;
+    Fp4 challenges[2];
+    Fp4 exposed;
+    bool has_phase = false;
+    Fp4 is_first, is_last, is_transition;
+};
+
+static Fp4 fold_constraints(const AirKeyDev& k, const ZetaInputs& in, const Fp4& alpha) {
+    const size_t n = k.nodes.size();
+    std::vector<Fp4> v(n, Fp4::zero());
+    auto bad = [&]() { reject("InvalidProofShape: constraint DAG refers to a value the proof does not carry"); };
+    for (size_t i = 0; i < n; i++) {
+        const uint4 nd = k.nodes[i];
+        switch (nd.x) {
+            case 0: v[i] = Fp4(Fp::from_canonical(nd.y % P)); break;
+            case 1:
+                if (nd.z > 1 || !in.prep[nd.z] || nd.y >= in.prep[nd.z]->size()) bad();
+                v[i] = (*in.prep[nd.z])[nd.y];
+                break;
+            case 2:
+                if (nd.z > 1 || nd.w >= in.main[nd.z].size() || nd.y >= in.main[nd.z][nd.w]->size()) bad();
+                v[i] = (*in.main[nd.z][nd.w])[nd.y];
+                break;
+            case 3:
+                if (nd.z > 1 || nd.y >= in.perm[nd.z].size()) bad();
+                v[i] = in.perm[nd.z][nd.y];
+                break;
+            case 4:
+                if (nd.y >= in.publics->size()) bad();
+                v[i] = Fp4((*in.publics)[nd.y]);
+                break;
+            case 5:
+                if (nd.y > 1 || !in.has_phase) bad();
+                v[i] = in.challenges[nd.y];
+                break;
+            case 6:
+                if (nd.y != 0 || !in.has_phase) bad();
+                v[i] = in.exposed;
+                break;
+            case 7: v[i] = in.is_first; break;
+            case 8: v[i] = in.is_last; break;
+            case 9: v[i] = in.is_transition; break;
+            case 10: case 11: case 13:
+                if (nd.y >= i || nd.z >= i) bad();
+                v[i] = nd.x == 10 ? v[nd.y] + v[nd.z] : nd.x == 11 ? v[nd.y] - v[nd.z] : v[nd.y] * v[nd.z];
+                break;
+            case 12:
+                if (nd.y >= i) bad();
+                v[i] = -v[nd.y];
+                break;
+            default: bad();
+        }
+    }
+    Fp4 acc = Fp4::zero();
+    for (uint32_t c : k.constraint_idx) acc = acc * alpha + v[c];
+    return acc;
+}
+
+void verify(const b2s_engine* e, const b2s_pk* pk, const uint8_t* bytes, size_t len) {
+    const b2s_fri_params& fp = e->params;
+    const unsigned b = fp.log_blowup;
+    const DecodedProof proof = decode(bytes, len);
+    HostHasher hh;
+    HostChallenger ch;
+    const size_t na = proof.per_air.size();
+    if (na == 0) reject("InvalidProofShape: no AIRs");
+    std::vector<const AirKeyDev*> keys(na);
+    std::vector<unsigned> logn(na);
+    for (size_t i = 0; i < na; i++) {
+        const AirProofData& a = proof.per_air[i];
+        if (a.air_id >= pk->airs.size() || (i && a.air_id <= proof.per_air[i - 1].air_id)) reject("InvalidProofShape: air ids");
+        const AirKeyDev& k = pk->airs[a.air_id];
+        keys[i] = &k;
+        if (a.public_values.size() != k.num_pv) reject("InvalidProofShape: public values");
+        if (!a.degree || (a.degree & (a.degree - 1))) reject("InvalidProofShape: degree");
+        logn[i] = log2_exact(a.degree);
+        if (logn[i] + b > TWO_ADICITY) reject("InvalidProofShape: degree too large");
+        if (k.width_prep && k.prep_log_height != logn[i]) reject("InvalidProofShape: degree differs from the preprocessed trace");
+        if (k.width_after) {
+            if (a.exposed.size() != 1 || a.exposed[0].size() != 1) reject("InvalidProofShape: exposed values");
+        } else if (!a.exposed.empty()) {
+            reject("InvalidProofShape: exposed values without interactions");
+        }
+    }
+    // transcript prefix (stark/mod.rs:140-149, 231-254)
+    for (int j = 0; j < 8; j++) ch.observe(Fp::raw(pk->pre_hash[j]));
+    ch.observe_canonical((uint32_t)na);
+    for (auto& a : proof.per_air) ch.observe_canonical(a.air_id);
+    for (auto& a : proof.per_air) for (Fp v : a.public_values) ch.observe(v);
+    size_t num_cached = 0, num_prep = 0, num_after = 0;
+    for (auto* k : keys) {
+        if (k->width_prep) { ch.observe_digest(k->prep_commit); num_prep++; }
+        num_cached += k->cached_widths.size();
+        num_after += k->width_after ? 1 : 0;
+    }
+    if (proof.main_commits.size() != num_cached + 1) reject("InvalidProofShape: main commits");
+    const bool phase = num_after != 0;
+    if (phase != !proof.after_commits.empty() || phase != !proof.opened_after.empty() || phase != proof.has_logup_witness ||
+        proof.after_commits.size() > 1 || proof.opened_after.size() > 1)
+        reject("InvalidProofShape: challenge phase");
+    for (auto& c : proof.main_commits) for (int j = 0; j < 8; j++) ch.observe(c[j]);
+    for (unsigned l : logn) ch.observe_canonical(l);
+    Fp4 challenges[2];
+    if (phase) {  // stark/mod.rs:307-358, 1129-1160
+        if (!ch.check_witness(pk->log_up_pow_bits, proof.logup_witness)) reject("InvalidLogUpPowWitness");
+        challenges[0] = ch.sample_ext();
+        challenges[1] = ch.sample_ext();
+        Fp4 total = Fp4::zero();
+        for (size_t i = 0; i < na; i++)
+            if (keys[i]->width_after) {
+                const Fp4& cs = proof.per_air[i].exposed[0][0];
+                ch.observe_ext(cs);
+                total += cs;
+            }
+        if (total != Fp4::zero()) reject("NonZeroCumulativeSum");
+        for (int j = 0; j < 8; j++) ch.observe(proof.after_commits[0][j]);
+    }
+    const Fp4 alpha = ch.sample_ext();
+    for (int j = 0; j < 8; j++) ch.observe(proof.quotient_commit[j]);
+    const Fp4 zeta = ch.sample_ext();
+
+    // opening rounds: [preprocessed per AIR][cached mains][common main][after challenge][quotient]
+    if (proof.opened_prep.size() != num_prep || proof.opened_main.size() != num_cached + 1 || proof.opened_quotient.size() != na)
+        reject("InvalidProofShape: opened values");
+    std::vector<VerifyRound> rounds;
+    auto trace_mat = [&](size_t i, const AdjacentOpened& ov, size_t width) {
+        if (ov.local.size() != width || ov.next.size() != width) reject("InvalidProofShape: opened width");
+        return VerifyMat{logn[i], {zeta, zeta * two_adic_generator(logn[i])}, {&ov.local, &ov.next}};
+    };
+    auto digest_of = [](const uint32_t* monty8) { Digest d; for (int j = 0; j < 8; j++) d[j] = Fp::raw(monty8[j]); return d; };
+    size_t pi = 0, mc = 0, cm = 0, am = 0;
+    for (size_t i = 0; i < na; i++)
+        if (keys[i]->width_prep) {
+            rounds.push_back(VerifyRound{digest_of(keys[i]->prep_commit), {trace_mat(i, proof.opened_prep[pi], keys[i]->width_prep)}});
+            pi++;
+        }
+    VerifyRound common_round;
+    const std::vector<AdjacentOpened>& common_vals = proof.opened_main[num_cached];
+    unsigned log_max_height = 0;
+    for (size_t i = 0; i < na; i++) {
+        const AirKeyDev& k = *keys[i];
+        log_max_height = std::max(log_max_height, logn[i]);
+        for (uint32_t w : k.cached_widths) {
+            if (proof.opened_main[mc].size() != 1) reject("InvalidProofShape: cached main");
+            rounds.push_back(VerifyRound{proof.main_commits[mc], {trace_mat(i, proof.opened_main[mc][0], w)}});
+            mc++;
+        }
+        if (k.width_common) {
+            if (cm >= common_vals.size()) reject("InvalidProofShape: common main");
+            common_round.mats.push_back(trace_mat(i, common_vals[cm++], k.width_common));
+        }
+    }
+    if (cm != common_vals.size() || cm == 0) reject("InvalidProofShape: common main count");
+    common_round.commit = proof.main_commits[num_cached];
+    rounds.push_back(common_round);
+    if (phase) {
+        VerifyRound ar;
+        ar.commit = proof.after_commits[0];
+        if (proof.opened_after[0].size() != num_after) reject("InvalidProofShape: after-challenge openings");
+        for (size_t i = 0; i < na; i++)
+            if (keys[i]->width_after) ar.mats.push_back(trace_mat(i, proof.opened_after[0][am++], (size_t)4 * keys[i]->width_after));
+        rounds.push_back(ar);
+    }
+    VerifyRound qround;
+    qround.commit = proof.quotient_commit;
+    for (size_t i = 0; i < na; i++) {
+        if (proof.opened_quotient[i].size() != ((size_t)1 << keys[i]->log_qd)) reject("InvalidProofShape: quotient chunks");
+        for (auto& chunk : proof.opened_quotient[i]) {
+            if (chunk.size() != 4) reject("InvalidProofShape: quotient chunk width");
+            qround.mats.push_back(VerifyMat{logn[i], {zeta}, {&chunk}});
+        }
+    }
+    rounds.push_back(qround);
+    verify_pcs(hh, rounds, proof, log_max_height, fp, ch);
+
+    // constraints at zeta against the recombined quotient (stark/mod.rs:903-1126; fri/domain.rs:59-155)
+    pi = mc = cm = am = 0;
+    for (size_t i = 0; i < na; i++) {
+        const AirKeyDev& k = *keys[i];
+        const unsigned n = logn[i];
+        ZetaInputs in;
+        if (k.width_prep) { in.prep[0] = &proof.opened_prep[pi].local; in.prep[1] = &proof.opened_prep[pi].next; pi++; }
+        for (size_t p = 0; p < k.cached_widths.size(); p++) {
+            in.main[0].push_back(&proof.opened_main[mc][0].local);
+            in.main[1].push_back(&proof.opened_main[mc][0].next);
+            mc++;
+        }
+        if (k.width_common) { in.main[0].push_back(&common_vals[cm].local); in.main[1].push_back(&common_vals[cm].next); cm++; }
+        if (k.width_after) {
+            const AdjacentOpened& ov = proof.opened_after[0][am++];
+            const std::vector<Fp4>* src[2] = {&ov.local, &ov.next};
+            for (int o = 0; o < 2; o++)
+                for (uint32_t c = 0; c < k.width_after; c++) in.perm[o].push_back(monomial_sum(*src[o], (size_t)4 * c));
+            in.has_phase = true;
+            in.challenges[0] = challenges[0];
+            in.challenges[1] = challenges[1];
+            in.exposed = proof.per_air[i].exposed[0][0];
+        }
+        in.publics = &proof.per_air[i].public_values;
+        const Fp ginv = fp_inv(two_adic_generator(n));
+        const Fp4 zh = fp4_pow(zeta, (uint64_t)1 << n) - Fp::one();
+        in.is_first = zh * fp4_inv(zeta - Fp::one());
+        in.is_last = zh * fp4_inv(zeta - ginv);
+        in.is_transition = zeta - ginv;
+        const Fp4 folded = fold_constraints(k, in, alpha);
+        // quotient chunk j lives on the coset GENERATOR * w_{N qd}^j * H_N; recombine with the Lagrange-like zerofier ratios
+        const size_t qd = (size_t)1 << k.log_qd;
+        const Fp gq = two_adic_generator(n + k.log_qd);
+        std::vector<Fp> shifts(qd);
+        for (size_t j = 0; j < qd; j++) shifts[j] = Fp::raw(M_GENERATOR) * fp_pow(gq, j);
+        auto zp_at = [&](Fp shift, const Fp4& point) { return fp4_pow(point * fp_inv(shift), (uint64_t)1 << n) - Fp::one(); };
+        Fp4 quotient = Fp4::zero();
+        for (size_t ci = 0; ci < qd; ci++) {
+            Fp4 zps = Fp4::one();
+            for (size_t j = 0; j < qd; j++)
+                if (j != ci) zps = zps * zp_at(shifts[j], zeta) * fp4_inv(zp_at(shifts[j], Fp4(shifts[ci])));
+            quotient += zps * monomial_sum(proof.opened_quotient[i][ci], 0);
+        }
+        if (folded * fp4_inv(zh) != quotient) reject("OodEvaluationMismatch");
+    }
+}
+
+}  // namespace b2

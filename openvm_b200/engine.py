@@ -27,6 +27,10 @@ class B2StarkError(RuntimeError):
         self.status = status
 
 
+class VerificationError(Exception):
+    """openvm_stark_backend::verifier::VerificationError (variant name in the message)."""
+
+
 def library_path():
     return _lib.LIB_PATH
 
@@ -326,6 +330,21 @@ class B2Engine:
         data = C.string_at(out.value, ln.value)
         self._lib.b2s_free(out)
         return data
+
+    def verify(self, pk, proof):
+        """StarkEngine::verify(&vk, &proof) (crates/vm/src/arch/vm.rs:1074,1127): returns None, or raises
+        VerificationError carrying the reference's error variant name."""
+        proof = bytes(proof)
+        st = self._lib.b2s_verify(self._h, pk._h, proof, len(proof))
+        if st == _lib.ERR_VERIFY_FAILED:
+            raise VerificationError((self._lib.b2s_last_error(self._h) or b"").decode())
+        self._check(st)
+
+    def set_pow_witnesses(self, logup_witness=None, fri_witness=None):
+        """Replay aid: use the given proof-of-work witnesses instead of searching for the minimum ones."""
+        s = 0xFFFFFFFF
+        self._check(self._lib.b2s_engine_set_pow_witnesses(self._h, s if logup_witness is None else logup_witness,
+                                                           s if fri_witness is None else fri_witness))
 
     def device(self):
         return self._device

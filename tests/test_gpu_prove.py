@@ -15,6 +15,19 @@ def make_engine(b, queries, pow_bits):
     return B2Engine.new(FriParameters(log_blowup=b, num_queries=queries, proof_of_work_bits=pow_bits))
 
 
+def gpu_verify(eng, key, proof):
+    """product-side verifier (b2s_verify): None or the VerificationError text"""
+    from openvm_b200 import VerificationError
+    pk = eng.device().transport_pk_to_device(key)
+    try:
+        eng.verify(pk, proof)
+        return None
+    except VerificationError as ex:
+        return str(ex)
+    finally:
+        pk.free()
+
+
 def gpu_prove(eng, key, inputs, air_objs):
     from openvm_b200 import AirProvingContext
     dev = eng.device()
@@ -77,6 +90,9 @@ def test_multi_air_proof_bytes(orc):
         bad[0][7, 2] = (int(bad[0][7, 2]) + 1) % P
         proof3 = gpu_prove(eng, key, [inputs[0], inputs[1], (2, bad, pv2), inputs[3]], air_objs)
         assert "OodEvaluationMismatch" in orc.stark_verify(key, proof3, b, queries, pow_bits)
+        # the library's own verifier agrees with the restated reference verifier
+        assert gpu_verify(eng, key, proof) is None and gpu_verify(eng, key, proof2) is None
+        assert "OodEvaluationMismatch" in gpu_verify(eng, key, proof3)
     finally:
         eng.close()
 
@@ -102,10 +118,11 @@ NONE = np.zeros(0, dtype=np.uint32)
 def check_same(orc, eng, key, inputs, air_objs, b, queries, pow_bits, expect=None):
     proof = gpu_prove(eng, key, inputs, air_objs)
     res = orc.stark_verify(key, proof, b, queries, pow_bits)
+    mine = gpu_verify(eng, key, proof)
     if expect is None:
-        assert res is None
+        assert res is None and mine is None
     else:
-        assert expect in res
+        assert expect in res and expect in mine
     assert proof == orc.stark_prove(key, inputs, b, queries, pow_bits)
     return proof
 
@@ -156,5 +173,81 @@ def test_logup_prep_cached_rotated_fields_bytes(orc, n, b):
     eng = make_engine(b, queries, pow_bits)
     try:
         check_same(orc, eng, key, [(0, parts, pv), (1, [recv], NONE)], air_objs, b, queries, pow_bits)
+    finally:
+        eng.close()
+
+
+def test_verify_agrees_with_oracle_on_tampered_proofs(orc):
+    b, queries, pow_bits = 1, 3, 2
+    air_objs = [airs.lookup_chain_air(6), airs.lookup_chain_receiver()]
+    key = airs.key_blob(air_objs, log_up_pow_bits=3)
+    parts, pv = airs.chain_trace(air_objs[0], 64, seed=3)
+    recv = np.zeros((64, 4), dtype=np.uint32)
+    recv[:, 0] = 1
+    recv[:, 1:4] = parts[-1][::-1, 0:3]
+    eng = make_engine(b, queries, pow_bits)
+    try:
+        proof = gpu_prove(eng, key, [(0, parts, pv), (1, [recv], NONE)], air_objs)
+        pk = eng.device().transport_pk_to_device(key)
+        from openvm_b200 import VerificationError
+        eng.verify(pk, proof)
+        rng = np.random.default_rng(11)
+        for pos in rng.integers(4, len(proof), size=60):
+            q = bytearray(proof)
+            q[pos] ^= 1 << int(rng.integers(0, 8))
+            want = orc.stark_verify(key, bytes(q), b, queries, pow_bits)
+            try:
+                eng.verify(pk, bytes(q))
+                got = None
+            except VerificationError as ex:
+                got = str(ex)
+            assert (want is None) == (got is None), (pos, want, got)
+            if want is not None:
+                kind = want.split(":")[0]
+                kind = "InvalidProofShape" if kind == "proof" else kind    # the oracle's decoder errors
+                assert got.startswith(kind), (pos, want, got)
+        with pytest.raises(VerificationError):
+            eng.verify(pk, proof[:-1])
+        # other FRI parameters: reject
+        eng2 = make_engine(b, queries + 1, pow_bits)
+        try:
+            pk2 = eng2.device().transport_pk_to_device(key)
+            with pytest.raises(VerificationError):
+                eng2.verify(pk2, proof)
+            pk2.free()
+        finally:
+            eng2.close()
+        pk.free()
+    finally:
+        eng.close()
+
+
+def test_pow_witness_override(orc):
+    """replay aid: any valid witness is accepted; the default is the minimum one"""
+    b, queries, pow_bits = 1, 3, 6
+    air = airs.fibonacci_air()
+    key = build_key(orc, [air], b)
+    trace, pvs = airs.fibonacci_trace(64)
+    eng = make_engine(b, queries, pow_bits)
+    try:
+        proof = gpu_prove(eng, key, [(0, [trace], pvs)], [air])
+        assert gpu_verify(eng, key, proof) is None
+        # the default is the minimum witness: every smaller candidate is rejected, some larger one is accepted too
+        from openvm_b200 import B2StarkError
+        found = None
+        for cand in range(0, 4096):
+            eng.set_pow_witnesses(None, cand)
+            try:
+                p2 = gpu_prove(eng, key, [(0, [trace], pvs)], [air])
+            except B2StarkError:
+                continue
+            if p2 != proof:
+                found = cand
+                assert gpu_verify(eng, key, p2) is None
+                assert orc.stark_verify(key, p2, b, queries, pow_bits) is None
+                break
+        assert found is not None
+        eng.set_pow_witnesses(None, None)
+        assert gpu_prove(eng, key, [(0, [trace], pvs)], [air]) == proof
     finally:
         eng.close()
