@@ -261,15 +261,17 @@ def main():
         peng = B2Engine.new(FriParameters.standard_with_100_bits_conjectured_security(b), local_rank)
         pdev = peng.device()
         shapes = A.segment_shapes(args.proof_scale_log)
-        air_objs = [A.chain_air(w) for _, w in shapes]
-        key = A.build_key(air_objs, None)
+        air_objs = [A.segment_air(w) for _, w in shapes]
+        key = A.build_key(air_objs, None, log_up_pow_bits=16)
         pk = pdev.transport_pk_to_device(key)
-        ctx, cells = [], 0
+        ctx, cells, perm_cells = [], 0, 0
         for i, (lh, w) in enumerate(shapes):
             parts, pv = A.chain_trace(air_objs[i], 1 << lh, seed=100 * rank + i)
             ctx.append(AirProvingContext(i, pdev.transport_matrix_to_device(parts[-1]), pv))
             cells += w << lh
+            perm_cells += (4 * (len(air_objs[i].chunks) + 1)) << lh
         proof = peng.prove(pk, ctx)
+        peng.verify(pk, proof)   # the library's own verifier (b2s_verify); raises if the proof is not accepted
         peng.reset_metrics()
         barrier()
         pstream = torch.cuda.ExternalStream(peng.stream, device=local_rank)
@@ -287,8 +289,9 @@ def main():
             t = torch.tensor([pms, wall], device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             pms, wall = float(t[0].item()), float(t[1].item())
-        seg = {"workload": f"shape-replay RV32IM segment: {len(shapes)} chain AIRs (degree-3 constraints, quotient degree 2), "
-                           f"{cells} main cells, FRI log_blowup {b}, {peng.fri_params().num_queries} queries, 16 PoW bits",
+        seg = {"workload": f"shape-replay RV32IM segment: {len(shapes)} chain AIRs with LogUp interactions (degree-3 constraints, "
+                           f"quotient degree 2), {cells} main cells + {perm_cells} after-challenge cells, FRI log_blowup {b}, "
+                           f"{peng.fri_params().num_queries} queries, 16 + 16 PoW bits; proof accepted by b2s_verify",
                "device_ms_per_proof": pms, "wall_ms_per_proof": wall, "segments_per_s": world * 1e3 / wall,
                "proof_bytes": len(proof),
                "stage_ms": {"main_trace_commit_time_ms+quotient_poly_commit_time_ms": pmet["commit_total_ms"] / args.steps,
@@ -304,8 +307,8 @@ def main():
             orc = oracle_binding.load()
             sl = args.proof_scale_log - 5
             sshapes = A.segment_shapes(sl)
-            sair = [A.chain_air(w) for _, w in sshapes]
-            skey = A.build_key(sair, None)
+            sair = [A.segment_air(w) for _, w in sshapes]
+            skey = A.build_key(sair, None, log_up_pow_bits=16)
             sin, scells = [], 0
             for i, (lh, w) in enumerate(sshapes):
                 parts, pv = A.chain_trace(sair[i], 1 << lh, seed=i)

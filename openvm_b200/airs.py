@@ -310,3 +310,18 @@ def lookup_chain_parts_receiver_trace(air, parts):
     t[:, 5] = prep0
     t[:, 6] = np.roll(common[:, 0], -1)
     return t[::-1].copy()
+
+
+def segment_air(width):
+    """One chip of the shape-replay segment: chain_air plus LogUp traffic shaped like an OpenVM chip's (BaseAlu:
+    36 main columns and 20 extension-field permutation columns in crates/prof/data/metrics.example.json). Chunk c holds
+    two interactions on bus c: send (x_j, x_{j+1}) of this row and receive the same pair of the NEXT row, so the bus
+    balances over the cyclic trace while every row's reciprocal sum is non-trivial. Degree 3 -> quotient degree 2."""
+    a = chain_air(width)
+    d = a.dag
+    k = max(1, width // 2) if width <= 100 else width // 10
+    for c in range(k):
+        j = c % (width - 1)
+        a.add_interaction(c, [d.main(j), d.main(j + 1)], d.const(1), True)
+        a.add_interaction(c, [d.main(j, 1), d.main(j + 1, 1)], d.const(1), False)
+    return a.finalize_logup(2)

@@ -12,6 +12,7 @@ Names and argument meaning follow the (external) openvm-stark-backend traits as 
 Everything here forwards to libb2stark.so through ctypes; numpy arrays are only host buffers.
 """
 import ctypes as C
+import weakref
 from dataclasses import dataclass
 
 import numpy as np
@@ -61,6 +62,7 @@ class DeviceMatrix:
         self._engine = engine
         self._h = handle
         self._borrowed = borrowed
+        engine._track(self)
 
     @property
     def height(self):
@@ -97,6 +99,7 @@ class PcsData:
     def __init__(self, engine, handle):
         self._engine = engine
         self._h = handle
+        engine._track(self)
 
     @property
     def log_max_height(self):
@@ -151,6 +154,7 @@ class ProvingKey:
     def __init__(self, engine, handle):
         self._engine = engine
         self._h = handle
+        engine._track(self)
 
     def free(self):
         if self._h:
@@ -286,6 +290,7 @@ class B2Engine:
     def __init__(self, fri_params=FriParameters(), cuda_device=0):
         self._lib = _lib.load()
         self._h = C.c_void_p()
+        self._live = weakref.WeakSet()
         p = _lib.FriParams(fri_params.log_blowup, fri_params.log_final_poly_len, fri_params.num_queries,
                            fri_params.proof_of_work_bits)
         st = self._lib.b2s_engine_new(C.byref(p), cuda_device, C.byref(self._h))
@@ -387,8 +392,15 @@ class B2Engine:
             msg = self._lib.b2s_last_error(self._h)
             raise B2StarkError(status, msg.decode() if msg else "")
 
+    def _track(self, obj):
+        self._live.add(obj)
+
     def close(self):
+        """Frees the engine and every matrix / PcsData / key still alive on it (their handles point into the engine)."""
         if self._h:
+            for obj in list(self._live):
+                obj.free()
+            self._live.clear()
             self._lib.b2s_engine_free(self._h)
             self._h = None
 

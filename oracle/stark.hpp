@@ -116,44 +116,50 @@ inline Proof stark_prove(const KeyBlob& key, const std::vector<AirInput>& airs, 
             ColMatrix prepm;
             if (k.width_prep) prepm = to_col_major(k.prep, N, k.width_prep);
             ColMatrix pm(N, 4 * (nch + 1));
+            std::vector<EF> row_sums(N);
+            parallel_for(N, threads, [&](size_t lo, size_t hi) {
+                for (size_t r = lo; r < hi; r++) {
+                    const size_t rr[2] = {r, (r + 1) % N};
+                    std::vector<std::vector<F>> rows[2];
+                    std::vector<F> prow[2];
+                    EvalInputs<F> in;
+                    for (int o = 0; o < 2; o++) {
+                        for (size_t p = 0; p < k.num_parts(); p++) {
+                            const ColMatrix& m = p < airs[i].cached.size() ? airs[i].cached[p] : airs[i].common;
+                            rows[o].emplace_back(m.width);
+                            for (size_t c = 0; c < m.width; c++) rows[o][p][c] = m.at(rr[o], c);
+                        }
+                        for (auto& v : rows[o]) in.main[o].push_back(v.data());
+                        if (k.width_prep) {
+                            prow[o].resize(k.width_prep);
+                            for (size_t c = 0; c < k.width_prep; c++) prow[o][c] = prepm.at(rr[o], c);
+                            in.prep[o] = prow[o].data();
+                        }
+                    }
+                    in.publics = airs[i].public_values.data();
+                    in.is_first = F(r == 0 ? 1 : 0); in.is_last = F(r == N - 1 ? 1 : 0); in.is_transition = F(r == N - 1 ? 0 : 1);
+                    std::vector<EF> v = eval_dag_nodes(k, in);
+                    EF row_sum;
+                    for (size_t c = 0; c < nch; c++) {
+                        EF s;
+                        for (uint32_t ii : k.chunks[c]) {
+                            const Interaction& it = k.interactions[ii];
+                            EF den = challenges[0];
+                            for (size_t j = 0; j < it.fields.size(); j++) den += betas[j] * v[it.fields[j]];
+                            den += betas[it.fields.size()] * F(it.bus + 1);
+                            EF cnt = v[it.count_node];
+                            if (it.type) cnt = -cnt;
+                            s += cnt * einv(den);
+                        }
+                        for (int e = 0; e < 4; e++) pm.at(r, 4 * c + e) = s.c[e];
+                        row_sum += s;
+                    }
+                    row_sums[r] = row_sum;
+                }
+            });
             EF phi;
             for (size_t r = 0; r < N; r++) {
-                const size_t rr[2] = {r, (r + 1) % N};
-                std::vector<std::vector<F>> rows[2];
-                std::vector<F> prow[2];
-                EvalInputs<F> in;
-                for (int o = 0; o < 2; o++) {
-                    for (size_t p = 0; p < k.num_parts(); p++) {
-                        const ColMatrix& m = p < airs[i].cached.size() ? airs[i].cached[p] : airs[i].common;
-                        rows[o].emplace_back(m.width);
-                        for (size_t c = 0; c < m.width; c++) rows[o][p][c] = m.at(rr[o], c);
-                    }
-                    for (auto& v : rows[o]) in.main[o].push_back(v.data());
-                    if (k.width_prep) {
-                        prow[o].resize(k.width_prep);
-                        for (size_t c = 0; c < k.width_prep; c++) prow[o][c] = prepm.at(rr[o], c);
-                        in.prep[o] = prow[o].data();
-                    }
-                }
-                in.publics = airs[i].public_values.data();
-                in.is_first = F(r == 0 ? 1 : 0); in.is_last = F(r == N - 1 ? 1 : 0); in.is_transition = F(r == N - 1 ? 0 : 1);
-                std::vector<EF> v = eval_dag_nodes(k, in);
-                EF row_sum;
-                for (size_t c = 0; c < nch; c++) {
-                    EF s;
-                    for (uint32_t ii : k.chunks[c]) {
-                        const Interaction& it = k.interactions[ii];
-                        EF den = challenges[0];
-                        for (size_t j = 0; j < it.fields.size(); j++) den += betas[j] * v[it.fields[j]];
-                        den += betas[it.fields.size()] * F(it.bus + 1);
-                        EF cnt = v[it.count_node];
-                        if (it.type) cnt = -cnt;
-                        s += cnt * einv(den);
-                    }
-                    for (int e = 0; e < 4; e++) pm.at(r, 4 * c + e) = s.c[e];
-                    row_sum += s;
-                }
-                phi += row_sum;
+                phi += row_sums[r];
                 for (int e = 0; e < 4; e++) pm.at(r, 4 * nch + e) = phi.c[e];
             }
             cumsum[i] = phi;
