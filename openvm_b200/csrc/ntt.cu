@@ -450,6 +450,32 @@ struct Plan {
 };
 static Plan make_plan(unsigned n) {
     Plan pl;
+    // B2S_NTT_PLAN="n:d1,d2,...,dk" (tuning aid): strided digits d1.. and the contiguous digit dk for log length n
+    if (const char* env = getenv("B2S_NTT_PLAN")) {
+        unsigned en = 0;
+        int used = 0;
+        if (sscanf(env, "%u:%n", &en, &used) == 1 && en == n) {
+            std::vector<unsigned> d;
+            const char* q = env + used;
+            while (*q) {
+                char* end;
+                unsigned v = (unsigned)strtoul(q, &end, 10);
+                if (end == q) break;
+                d.push_back(v);
+                q = *end == ',' ? end + 1 : end;
+            }
+            unsigned sum = 0;
+            bool ok = !d.empty() && d.back() >= 1 && d.back() <= 13;
+            for (size_t i = 0; i < d.size(); i++) { sum += d[i]; if (i + 1 < d.size() && (d[i] < 1 || d[i] > K1_MAX_D)) ok = false; }
+            // a strided pass needs at least 5 low bits below it (32 adjacent positions per tile row)
+            if (ok && sum == n && d.back() >= 5) {
+                pl.strided.assign(d.begin(), d.end() - 1);
+                pl.contig = d.back();
+                return pl;
+            }
+            fail(B2S_ERR_BAD_ARG, "B2S_NTT_PLAN: digits must sum to the log length (strided 1..9, contiguous 5..13)");
+        }
+    }
     if (n <= 12) {
         pl.contig = n;
     } else if (n <= 22) {

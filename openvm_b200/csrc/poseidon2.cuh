@@ -18,28 +18,41 @@ namespace b2 {
 // code body serves all eight full rounds; indexed by the loop counter -> LDC with a register index)
 static __constant__ uint32_t P2C_EXT[8][16] = B2_P2_EXT_ALL;
 static __constant__ uint32_t P2C_PARTIAL[13] = B2_P2_PARTIAL;
-static __constant__ uint32_t P2C_DIAG[16] = B2_P2_DIAG;
 
-// Montgomery product whose  m = lo * (-p^-1)  step runs on the ALU pipe as shifts/adds instead of a 4-cycle IMAD
-// on fmaheavy: -p^-1 = 2^31 - 2^27 - 1 (mod 2^32). Used for a fraction of the S-box products to balance the two
-// pipes (ncu: fmaheavy 87 % busy, alu 53 %, profiles/r1c).
-B2_D Fp mul_alu(Fp a, Fp b) {
-    const uint64_t t = (uint64_t)a.v * b.v;
-    const uint32_t lo = (uint32_t)t;
-    uint32_t m;  // inline PTX so the compiler does not fold the shifts back into a multiply by 0x77ffffff
-    asm("{\n\t.reg .u32 a, b;\n\tshl.b32 a, %1, 31;\n\tshl.b32 b, %1, 27;\n\tsub.u32 a, a, b;\n\tsub.u32 %0, a, %1;\n\t}"
-        : "=r"(m) : "r"(lo));
-    const uint64_t u = t + (uint64_t)m * P;
-    const uint32_t r = (uint32_t)(u >> 32);
-    const uint32_t s = r - P;
-    return Fp::raw(s < r ? s : r);
+// Signed Montgomery product (a, b in (-p, p) as int32 -> a*b*2^-32 in (-p, p)): r = hi(t) - hi(m*p) with
+// m = lo(t) * p^-1 needs no final correction because |t| < 2^31 p keeps both high words within p/2. A chain of
+// products therefore costs 3 multiplies + 1 subtract each instead of 3 + 2 (the unsigned form corrects into [0, p)
+// after every product). The fmaheavy pipe carries the multiplies either way; this trims the ALU side so that ptxas
+// can move more of the additions it currently issues as IMAD.IADD off the multiply pipe (profiles/r1c: fmaheavy 87 %).
+B2_D int32_t smont(int32_t a, int32_t b) {
+    const int64_t t = (int64_t)a * b;
+    const uint32_t m = (uint32_t)t * P_INV;
+    const int32_t u = __mulhi((int32_t)m, (int32_t)P);
+    return (int32_t)(t >> 32) - u;
 }
-template <int MASK>
-B2_D Fp sbox7(Fp x) {
-    Fp x2 = (MASK & 1) ? mul_alu(x, x) : x * x;
-    Fp x3 = (MASK & 2) ? mul_alu(x2, x) : x2 * x;
-    Fp x4 = (MASK & 4) ? mul_alu(x2, x2) : x2 * x2;
-    return (MASK & 8) ? mul_alu(x3, x4) : x3 * x4;
+// x -> (x + rc)^7 for x, rc in [0, p): the constant is added as rc - p, which lands in (-p, p) with one 3-input add,
+// the four products run signed, and a single add-min brings the result back to [0, p)
+B2_D Fp sbox7_rc(Fp x, uint32_t rc) {
+    const int32_t y = (int32_t)(x.v + rc - P);
+    const int32_t y2 = smont(y, y);
+    const int32_t y3 = smont(y2, y);
+    const int32_t y4 = smont(y2, y2);
+    const uint32_t y7 = (uint32_t)smont(y3, y4);
+    const uint32_t c = y7 + P;
+    return Fp::raw(c < y7 ? c : y7);
+}
+
+// x * 2^-K mod p without a Montgomery product: p = 15 * 2^27 + 1 gives 2^-27 = -15, so 2^-K = -15 * 2^(27-K) and
+//   x * 2^-K = (x >> K) - 15 * 2^(27-K) * (x mod 2^K)      (second term < 15 * 2^27 < p)
+// one 2-cycle IMAD instead of a 10-cycle product on the multiply pipe. NEG gives -(x * 2^-K).
+template <int K, bool NEG>
+B2_D Fp mul_2exp_neg(Fp x) {
+    static_assert(K >= 1 && K <= 27, "K");
+    const uint32_t lo = x.v & ((1u << K) - 1), hi = x.v >> K;
+    const uint32_t t = lo * (15u << (27 - K));
+    const uint32_t r = NEG ? t - hi : hi - t;
+    const uint32_t c = r + P;
+    return Fp::raw(c < r ? c : r);
 }
 
 // [[2,3,1,1],[1,2,3,1],[1,1,2,3],[3,1,1,2]] on four lanes: 7 additions + 2 doublings
@@ -74,8 +87,8 @@ B2_D Fp fp_halve(Fp a) {
 }
 
 // internal layer: s_i <- sum(s) + d_i * s_i   with d = (-2, 1, 2, 1/2, 3, 4, -1/2, -3, -4, 2^-8, 1/4, 1/8, 2^-27, -2^-8, -1/16, -2^-27)
-// The small-integer and 1/2 multiples are done with additions/shifts on the ALU pipe (the fmaheavy pipe, which
-// carries the Montgomery products, is the busier one); the negative-power-of-two entries use Montgomery products.
+// No Montgomery product at all: small-integer and 1/2 multiples are additions/shifts, the 2^-k entries use the
+// shape of p (mul_2exp_neg); the fmaheavy pipe, which carries the S-box products, is the busier one.
 B2_D void p2_internal(Fp (&s)[16]) {
     Fp part = ((s[1] + s[2]) + (s[3] + s[4])) + ((s[5] + s[6]) + (s[7] + s[8])) +
               (((s[9] + s[10]) + (s[11] + s[12])) + ((s[13] + s[14]) + s[15]));
@@ -95,21 +108,19 @@ B2_D void p2_internal(Fp (&s)[16]) {
         s[7] = full - (d7 + s[7]);
         s[8] = full - fp_double(d8);
     }
-#pragma unroll
-    for (int i = 9; i < 16; i++) s[i] = full + s[i] * Fp::raw(P2C_DIAG[i]);
+    s[9] = full + mul_2exp_neg<8, false>(s[9]);
+    s[10] = full + mul_2exp_neg<2, false>(s[10]);
+    s[11] = full + mul_2exp_neg<3, false>(s[11]);
+    s[12] = full + mul_2exp_neg<27, false>(s[12]);
+    s[13] = full + mul_2exp_neg<8, true>(s[13]);
+    s[14] = full + mul_2exp_neg<4, true>(s[14]);
+    s[15] = full + mul_2exp_neg<27, true>(s[15]);
 }
 
 // The whole permutation as  E S0 E S1 E S2 E S3 E [P x 13] S4 E S5 E S6 E S7 E  with one code body per layer type
 // (E external layer, S_r add-constants + x^7 on all lanes, P partial round). Loops are kept rolled on purpose:
 // fully unrolled, one permutation is ~100 KB of SASS, which thrashes the instruction cache (ncu: stall
 // no_instruction dominant, profiles/r1a_ncu_full_summary.md); rolled it is ~9 KB.
-#ifndef B2_P2_FULL_MASK
-#define B2_P2_FULL_MASK 0
-#endif
-#ifndef B2_P2_PARTIAL_MASK
-#define B2_P2_PARTIAL_MASK 0
-#endif
-template <int FULL_MASK = B2_P2_FULL_MASK, int PARTIAL_MASK = B2_P2_PARTIAL_MASK>
 B2_D void poseidon2_permute(Fp (&s)[16]) {
 #pragma unroll 1
     for (int r = 0; r < 9; r++) {
@@ -117,13 +128,13 @@ B2_D void poseidon2_permute(Fp (&s)[16]) {
         if (r == 4) {
 #pragma unroll 1
             for (int q = 0; q < 13; q++) {
-                s[0] = sbox7<PARTIAL_MASK>(s[0] + Fp::raw(P2C_PARTIAL[q]));
+                s[0] = sbox7_rc(s[0], P2C_PARTIAL[q]);
                 p2_internal(s);
             }
         }
         if (r < 8) {
 #pragma unroll
-            for (int i = 0; i < 16; i++) s[i] = sbox7<FULL_MASK>(s[i] + Fp::raw(P2C_EXT[r][i]));
+            for (int i = 0; i < 16; i++) s[i] = sbox7_rc(s[i], P2C_EXT[r][i]);
         }
     }
 }

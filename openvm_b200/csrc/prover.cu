@@ -25,6 +25,7 @@
 
 #include <algorithm>
 #include <array>
+#include <chrono>
 #include <map>
 
 namespace b2 {
@@ -717,12 +718,20 @@ static void scan_planes(b2s_engine* e, Scratch& scratch, const uint32_t* in, uin
 
 struct ByteWriter {
     std::vector<uint8_t>& buf;
-    void u32(uint32_t x) { for (int i = 0; i < 4; i++) buf.push_back((uint8_t)(x >> (8 * i))); }
+    void u32(uint32_t x) {  // little-endian host (x86-64 / aarch64): the wire format is the in-memory word
+        const size_t at = buf.size();
+        buf.resize(at + 4);
+        memcpy(buf.data() + at, &x, 4);
+    }
     void f(Fp x) { u32(x.to_canonical()); }
     void ef(const Fp4& e) { for (int i = 0; i < 4; i++) f(e.c[i]); }
     void efs(const std::vector<Fp4>& v) { u32((uint32_t)v.size()); for (auto& e : v) ef(e); }
     void digest_monty(const uint32_t* d) { for (int i = 0; i < 8; i++) f(Fp::raw(d[i])); }
-    void words(const uint32_t* w, size_t n) { for (size_t i = 0; i < n; i++) u32(w[i]); }  // already canonical
+    void words(const uint32_t* w, size_t n) {  // already canonical
+        const size_t at = buf.size();
+        buf.resize(at + 4 * n);
+        if (n) memcpy(buf.data() + at, w, 4 * n);
+    }
 };
 
 struct RoundMat {
@@ -781,11 +790,30 @@ static Fp grind_device(b2s_engine* e, Scratch& scratch, HostChallenger& ch, unsi
     return witness;
 }
 
+// B2S_PROVE_TRACE=1: wall-clock marks of the host thread through one proof (stderr); the stream is drained at each mark
+struct HostTrace {
+    b2s_engine* e;
+    bool on;
+    std::chrono::steady_clock::time_point t0, last;
+    explicit HostTrace(b2s_engine* e_) : e(e_), on(getenv("B2S_PROVE_TRACE") != nullptr) { t0 = last = std::chrono::steady_clock::now(); }
+    void mark(const char* what) {
+        if (!on) return;
+        auto a = std::chrono::steady_clock::now();
+        cudaStreamSynchronize(e->stream);
+        auto b = std::chrono::steady_clock::now();
+        fprintf(stderr, "[b2s trace] %-28s host %8.3f ms  drain %8.3f ms  (t = %8.3f ms)\n", what,
+                std::chrono::duration<double, std::milli>(a - last).count(), std::chrono::duration<double, std::milli>(b - a).count(),
+                std::chrono::duration<double, std::milli>(b - t0).count());
+        last = b;
+    }
+};
+
 // ---- prove -------------------------------------------------------------------------------------------------------------------
 void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_airs, std::vector<uint8_t>& out) {
     B2_REQUIRE(pk->eng == e, B2S_ERR_BAD_ARG, "prove: key was loaded on a different engine");
     StageScope total_scope(e, ST_PROVE);
     Scratch scratch(e);
+    HostTrace trace(e);
     const unsigned b = e->params.log_blowup;
     HostChallenger ch;
     std::vector<unsigned> logn(n_airs);
@@ -856,6 +884,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     for (auto& c : main_commits) ch.observe_digest(c.data());
     for (size_t i = 0; i < n_airs; i++) ch.observe_canonical(logn[i]);
 
+    trace.mark("main commit");
     // ---- FRI-LogUp challenge phase (stark/mod.rs:307-358): PoW, two challenges, one after-challenge matrix per
     // interacting AIR = [reciprocal sum of each chunk | running sum phi], all committed in one tree
     bool phase = false;
@@ -941,6 +970,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     }
     const Fp4 alpha = ch.sample_ext();
 
+    trace.mark("logup phase");
     // ---- quotient (stark/mod.rs:366-416; fri/domain.rs:59-155)
     std::vector<b2s_matrix> chunk_views;   // one N x 4 matrix per (AIR, chunk)
     std::vector<Fp> chunk_shifts;
@@ -1012,6 +1042,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             }
         }
     }
+    trace.mark("quotient eval");
     std::vector<const b2s_matrix*> chunk_ptrs;
     for (auto& v : chunk_views) chunk_ptrs.push_back(&v);
     b2s_pcs_data* quotient_pcs = commit_matrices(e, chunk_ptrs.data(), chunk_shifts.data(), chunk_ptrs.size());
@@ -1021,6 +1052,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     ch.observe_digest(quotient_commit.data());
     const Fp4 zeta = ch.sample_ext();
 
+    trace.mark("quotient commit");
     // ---- opening rounds: [preprocessed per AIR][cached mains][common main][quotient]  (stark/mod.rs:418-698)
     StageScope open_scope(e, ST_OPENING);
     std::vector<Round> rounds;
@@ -1104,6 +1136,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             rm.values[j.p] = std::move(vals);
         }
     }
+    trace.mark("ood values");
     // observed round -> matrix -> point -> column (two_adic_pcs.rs:63-95)
     for (auto& r : rounds)
         for (auto& m : r.mats)
@@ -1111,6 +1144,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
                 for (auto& v : pt) ch.observe_ext(v);
     const Fp4 fri_alpha = ch.sample_ext();
 
+    trace.mark("observe opened values");
     // (ii) reduced openings per LDE log height; the alpha power runs on per height (two_adic_pcs.rs:175-196, 313-325)
     const unsigned L = log_max_height + b;
     std::map<unsigned, uint32_t*> ro;
@@ -1146,6 +1180,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             }
     }
 
+    trace.mark("reduced openings");
     // (iii) FRI commit phase (two_adic_pcs.rs:111-130; fri/mod.rs:139-165)
     std::vector<b2s_pcs_data*> fri_trees;
     std::vector<b2s_matrix*> fri_leaves;
@@ -1184,6 +1219,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
         e->launches[3]++;
         folded = next;
     }
+    trace.mark("fri commit phase");
     // final polynomial: log_final_poly_len = 0, the constant (two_adic_pcs.rs:52-58)
     Fp4 final_poly;
     {
@@ -1199,6 +1235,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     ch.observe_ext(final_poly);
     // (iv) proof of work: minimum witness (duplex.rs:122-130)
     const Fp pow_witness = grind_device(e, scratch, ch, e->params.proof_of_work_bits, e->pow_override[1]);
+    trace.mark("final poly + pow");
     // (v) queries: every opening of every query in one gather (two_adic_pcs.rs:170-372; fri/mod.rs:72-135)
     const unsigned nq = e->params.num_queries;
     std::vector<uint32_t> indices(nq);
@@ -1229,8 +1266,10 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     std::vector<uint32_t> opened(off);
     gather_rows(e, descs, off, opened.data());
 
+    trace.mark("query gather");
     // ---- proof bytes (crates/sdk/src/codec.rs:92-330) -------------------------------------------------------------------
     out.clear();
+    out.reserve(opened.size() * 4 + (1u << 16));
     ByteWriter w{out};
     w.u32(1);  // CODEC_VERSION
     w.u32((uint32_t)main_commits.size());
@@ -1306,6 +1345,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     out.push_back(0);       // RapPhaseSeqKind::FriLogUp
     if (phase) w.f(logup_witness); else w.u32(0xFFFFFFFFu);
     B2_CUDA(cudaStreamSynchronize(e->stream));
+    trace.mark("encode");
 }
 
 }  // namespace b2

@@ -218,12 +218,11 @@ double bench_modmul(b2s_engine* e, uint64_t threads, uint32_t iters, int ilp) {
     return ms;
 }
 
-template <int FULL_MASK>
 __global__ void __launch_bounds__(128) poseidon2_bench_kernel(uint32_t* sink, uint32_t iters) {
     Fp s[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) s[k] = Fp::raw((threadIdx.x * 2654435761u + k * 40503u + blockIdx.x) % P);
-    for (uint32_t i = 0; i < iters; i++) poseidon2_permute<FULL_MASK, 0>(s);
+    for (uint32_t i = 0; i < iters; i++) poseidon2_permute(s);
     uint32_t acc = 0;
 #pragma unroll
     for (int k = 0; k < 16; k++) acc ^= s[k].v;
@@ -234,19 +233,7 @@ double bench_poseidon2(b2s_engine* e, uint64_t threads, uint32_t iters) {
     cudaEvent_t a = e->get_event(), b = e->get_event();
     unsigned blocks = (unsigned)((threads + 127) / 128);
     B2_CUDA(cudaEventRecord(a, e->stream));
-    // B2S_P2_MASK selects which of the four S-box products use the ALU-side reduction (tuning knob for the bench only)
-    int mask = B2_P2_FULL_MASK;
-    if (const char* env = getenv("B2S_P2_MASK")) mask = atoi(env);
-    switch (mask) {
-        case 0: poseidon2_bench_kernel<0><<<blocks, 128, 0, e->stream>>>(sink, iters); break;
-        case 1: poseidon2_bench_kernel<1><<<blocks, 128, 0, e->stream>>>(sink, iters); break;
-        case 4: poseidon2_bench_kernel<4><<<blocks, 128, 0, e->stream>>>(sink, iters); break;
-        case 5: poseidon2_bench_kernel<5><<<blocks, 128, 0, e->stream>>>(sink, iters); break;
-        case 8: poseidon2_bench_kernel<8><<<blocks, 128, 0, e->stream>>>(sink, iters); break;
-        case 9: poseidon2_bench_kernel<9><<<blocks, 128, 0, e->stream>>>(sink, iters); break;
-        case 13: poseidon2_bench_kernel<13><<<blocks, 128, 0, e->stream>>>(sink, iters); break;
-        default: poseidon2_bench_kernel<15><<<blocks, 128, 0, e->stream>>>(sink, iters); break;
-    }
+    poseidon2_bench_kernel<<<blocks, 128, 0, e->stream>>>(sink, iters);
     B2_CHECK_LAUNCH();
     B2_CUDA(cudaEventRecord(b, e->stream));
     B2_CUDA(cudaEventSynchronize(b));

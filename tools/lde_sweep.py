@@ -17,7 +17,7 @@ def run(log_h, width, b, reps=5):
     ms = met["lde_ms"] / reps
     n = (1 << log_h) * width
     bf = n * log_h / 2 * (1 + (1 << b))
-    print(f"log_h={log_h} w={width} b={b} group={os.environ.get('B2S_LDE_GROUP_ELEMS','default')}: {ms:.3f} ms, "
+    print(f"log_h={log_h} w={width} b={b} group={os.environ.get('B2S_LDE_GROUP_ELEMS','default')} plan={os.environ.get('B2S_NTT_PLAN','default')}: {ms:.3f} ms, "
           f"{bf / ms / 1e6:.1f} G butterflies/s, launches/rep {met['lde_launches'] / reps:.0f}", flush=True)
     m.free(); eng.close()
 

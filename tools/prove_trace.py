@@ -1,0 +1,22 @@
+"""Host/device timeline of one shape-replay segment proof (B2S_PROVE_TRACE marks from prover.cu)."""
+import os, sys, time
+os.environ["B2S_PROVE_TRACE"] = "1"
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from openvm_b200 import B2Engine, FriParameters, AirProvingContext, airs as A
+
+eng = B2Engine.new(FriParameters.standard_with_100_bits_conjectured_security(1))
+dev = eng.device()
+shapes = A.segment_shapes(int(sys.argv[1]) if len(sys.argv) > 1 else 0)
+air_objs = [A.segment_air(w) for _, w in shapes]
+pk = dev.transport_pk_to_device(A.build_key(air_objs, None, log_up_pow_bits=16))
+ctx = []
+for i, (lh, w) in enumerate(shapes):
+    parts, pv = A.chain_trace(air_objs[i], 1 << lh, seed=i)
+    ctx.append(AirProvingContext(i, dev.transport_matrix_to_device(parts[-1]), pv))
+for it in range(3):
+    print(f"--- proof {it}", file=sys.stderr)
+    t = time.perf_counter()
+    proof = eng.prove(pk, ctx)
+    print(f"wall {1e3 * (time.perf_counter() - t):.2f} ms, {len(proof)} bytes", file=sys.stderr)
+eng.verify(pk, proof)
+eng.close()
