@@ -476,17 +476,39 @@ static Plan make_plan(unsigned n) {
             fail(B2S_ERR_BAD_ARG, "B2S_NTT_PLAN: digits must sum to the log length (strided 1..9, contiguous 5..13)");
         }
     }
-    if (n <= 12) {
+    // Every round of a pass is one trip through shared memory around a radix-2^R register block, R <= 4: the cost of a
+    // plan is its number of rounds, sum of ceil(d / 4) (measured, tools/gpu_plan_sweep.sh: n = 20 as 8 + 12 = 5 rounds
+    // runs in 5.98 ms, 9 + 11 = 6 rounds in 7.46 ms; n = 24 as 8 + 8 + 8 beats 6 + 6 + 12). Fewest passes first, then
+    // fewest rounds, then the most even digits.
+    auto rounds = [](unsigned d) { return (d + 3) / 4; };
+    if (n <= 13) {
         pl.contig = n;
-    } else if (n <= 22) {
-        unsigned d1 = std::min<unsigned>(K1_MAX_D, n / 2);
-        pl.strided = {d1};
-        pl.contig = n - d1;
-    } else {
-        unsigned rest = n - 12;
-        pl.strided = {(rest + 1) / 2, rest / 2};
-        pl.contig = 12;
+        return pl;
     }
+    unsigned best_cost = ~0u, best_spread = ~0u;
+    if (n <= K1_MAX_D + 13) {
+        for (unsigned d1 = 4; d1 <= K1_MAX_D; d1++) {
+            if (n < d1 + 5 || n - d1 > 13) continue;
+            const unsigned d2 = n - d1, cost = rounds(d1) + rounds(d2), spread = d1 > d2 ? d1 - d2 : d2 - d1;
+            if (cost < best_cost || (cost == best_cost && spread < best_spread)) {
+                best_cost = cost; best_spread = spread;
+                pl.strided = {d1};
+                pl.contig = d2;
+            }
+        }
+        return pl;
+    }
+    for (unsigned d1 = 4; d1 <= K1_MAX_D; d1++)
+        for (unsigned d2 = 4; d2 <= d1; d2++) {
+            if (n < d1 + d2 + 5 || n - d1 - d2 > 13) continue;
+            const unsigned d3 = n - d1 - d2, cost = rounds(d1) + rounds(d2) + rounds(d3);
+            const unsigned hi = std::max(d1, d3), lo = std::min(d2, d3), spread = hi - lo;
+            if (cost < best_cost || (cost == best_cost && spread < best_spread)) {
+                best_cost = cost; best_spread = spread;
+                pl.strided = {d1, d2};
+                pl.contig = d3;
+            }
+        }
     return pl;
 }
 

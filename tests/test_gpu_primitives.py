@@ -44,11 +44,11 @@ def test_synthetic_fill_matches_oracle(engine, orc):
     assert np.array_equal(d.to_host(), orc.fill_synthetic(512, 5, 0xB200000000000001))
 
 
-# every digit plan: 1 pass (<=9), 2 passes (10..18), 3 passes (19..); odd splits; blowups 1..3
+# every digit plan: 1 pass (<= 13), 2 passes (14..22), 3 passes (23..); odd splits; blowups 1..3
 @pytest.mark.parametrize("logn,width,b", [
     (0, 3, 1), (1, 2, 1), (2, 5, 2), (3, 1, 1), (5, 7, 1), (8, 3, 2), (9, 4, 1),
     (10, 3, 1), (11, 2, 2), (13, 5, 1), (16, 2, 1), (17, 3, 2), (18, 1, 3),
-    (19, 2, 1), (20, 3, 1), (21, 1, 2),
+    (12, 3, 1), (14, 2, 1), (15, 1, 2), (19, 2, 1), (20, 3, 1), (21, 1, 2), (22, 1, 1), (23, 1, 1),
 ])
 def test_coset_lde(engine, orc, logn, width, b):
     m = rand(1 << logn, width)
