@@ -229,10 +229,10 @@ def main():
         dev.download_raw(trace, host.data_ptr(), layout="col", repr="monty")
 
         def e2e_step():
-            m = dev.upload_raw(host.data_ptr(), H, width, layout="col", repr="monty")
-            r, pcs = dev.commit([m])  # root comes back to the host inside commit (32 B D2H)
+            # b2s_commit_host: upload of column groups overlapped with LDE + hashing of the previous group; the root
+            # comes back to the host inside the call (32 B D2H)
+            r, pcs = dev.commit_host(host_ptr=host.data_ptr(), height=H, width=width, layout="col", repr="monty")
             pcs.free()
-            m.free()
             return r
 
         r0 = e2e_step()

@@ -120,6 +120,14 @@ void b2s_matrix_free(b2s_matrix* m);
  * root8 receives the commitment as 8 canonical words. The PcsData retains the LDE matrices. */
 int32_t b2s_commit(b2s_engine* e, const b2s_matrix* const* mats, size_t n_mats, uint32_t root8[8],
                    b2s_pcs_data** out);
+
+/* transport_matrix_to_device + commit for one tall host-resident trace, as one pipelined call
+ * (crates/vm/src/arch/vm.rs:731-735 issues the two back to back): column groups are uploaded on a second stream
+ * while the previous group is extended and hashed, so the PCIe transfer is hidden behind the arithmetic. The result
+ * is identical to b2s_matrix_upload + b2s_commit; the trace itself is not kept on the device (the PcsData holds the
+ * LDE). `host` should be pinned for the copy to overlap; layout / repr as for b2s_matrix_upload. */
+int32_t b2s_commit_host(b2s_engine* e, const uint32_t* host, uint64_t height, uint64_t width, int32_t layout,
+                        int32_t repr, uint32_t root8[8], b2s_pcs_data** out);
 /* the two halves of commit, exposed for parity tests and for the quotient / FRI commit-phase callers:
  * coset LDE of evaluations over shift_in*H_N (shift_in canonical; 1 for traces) ... */
 int32_t b2s_coset_lde(b2s_engine* e, const b2s_matrix* in, uint32_t log_blowup, uint32_t shift_in,

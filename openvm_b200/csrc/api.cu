@@ -121,6 +121,83 @@ void free_pcs(b2s_pcs_data* d) {
     delete d;
 }
 
+// One tall host-resident trace -> (LDE, Merkle tree), with the upload hidden behind the arithmetic: column groups are
+// copied on a second stream into a double buffer while the previous group is extended and absorbed into the per-row
+// sponge states. LDE and hashing are multiply-bound, so PCIe (~55 GB/s) is the faster side: for
+// 2^24 x 256 a group is 39 ms of copy against 56 ms of arithmetic. The trace itself is not kept on the device.
+b2s_pcs_data* commit_host_streamed(b2s_engine* e, const uint32_t* host, uint64_t N, uint64_t W, int layout, int repr) {
+    StageScope total(e, ST_COMMIT);
+    B2_REQUIRE(is_pow2(N) && W > 0, B2S_ERR_SHAPE, "commit: height must be a power of two and width > 0");
+    const uint32_t lb = e->params.log_blowup;
+    const unsigned logn = log2_exact(N);
+    B2_REQUIRE(logn + lb <= TWO_ADICITY, B2S_ERR_SHAPE, "commit: trace too tall for this blowup");
+    const uint64_t M = N << lb;
+    uint64_t G = (((uint64_t)1 << 26) / N) & ~(uint64_t)7;
+    if (G < 8) G = 8;
+    if (G > W) G = W;
+    const uint64_t ngroups = (W + G - 1) / G;
+    const bool row_major = layout == B2S_LAYOUT_ROW_MAJOR;
+    if (!e->copy_stream) B2_CUDA(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+    b2s_pcs_data* d = new b2s_pcs_data();
+    d->eng = e;
+    uint32_t *stage[2] = {nullptr, nullptr}, *raw[2] = {nullptr, nullptr}, *state = nullptr, *leaf = nullptr;
+    cudaEvent_t copied[2] = {e->get_event(), e->get_event()}, consumed[2] = {e->get_event(), e->get_event()};
+    auto cleanup = [&]() {
+        for (int k = 0; k < 2; k++) {
+            e->dfree(stage[k], G * N * 4);
+            if (raw[k]) e->dfree(raw[k], G * N * 4);
+            e->event_pool.push_back(copied[k]);
+            e->event_pool.push_back(consumed[k]);
+        }
+        if (state) e->dfree(state, M * 64);
+    };
+    try {
+        b2s_matrix* lde = new_matrix(e, M, W);
+        d->mats.push_back(lde);
+        d->owns.push_back(true);
+        for (int k = 0; k < 2; k++) {
+            stage[k] = (uint32_t*)e->dmalloc(G * N * 4);
+            if (row_major) raw[k] = (uint32_t*)e->dmalloc(G * N * 4);
+        }
+        if (ngroups > 1) state = (uint32_t*)e->dmalloc(M * 64);
+        leaf = (uint32_t*)e->dmalloc(M * 32);
+        // the buffers come from the stream-ordered allocator of e->stream: order the copy stream behind them
+        B2_CUDA(cudaEventRecord(consumed[0], e->stream));
+        B2_CUDA(cudaStreamWaitEvent(e->copy_stream, consumed[0], 0));
+        for (uint64_t g = 0; g < ngroups; g++) {
+            const uint64_t c0 = g * G, gw = std::min(G, W - c0);
+            const int k = (int)(g & 1);
+            if (g >= 2) B2_CUDA(cudaStreamWaitEvent(e->copy_stream, consumed[k], 0));
+            if (row_major)
+                B2_CUDA(cudaMemcpy2DAsync(raw[k], gw * 4, host + c0, W * 4, gw * 4, N, cudaMemcpyHostToDevice, e->copy_stream));
+            else
+                B2_CUDA(cudaMemcpyAsync(stage[k], host + c0 * N, gw * N * 4, cudaMemcpyHostToDevice, e->copy_stream));
+            B2_CUDA(cudaEventRecord(copied[k], e->copy_stream));
+            B2_CUDA(cudaStreamWaitEvent(e->stream, copied[k], 0));
+            if (row_major) transpose_to_colmajor(e, raw[k], stage[k], N, gw, repr == B2S_REPR_CANONICAL);
+            else if (repr == B2S_REPR_CANONICAL) convert_repr(e, stage[k], gw * N, true);
+            {
+                StageScope sc(e, ST_LDE);
+                lde_columns(e, stage[k], N, logn, gw, lb, Fp::one(), lde->d + c0 * M, M);
+            }
+            B2_CUDA(cudaEventRecord(consumed[k], e->stream));
+            leaf_absorb(e, lde->d + c0 * M, (uint32_t)gw, M, state, leaf, g == 0, g + 1 == ngroups);
+        }
+        B2_CUDA(cudaStreamSynchronize(e->copy_stream));
+        mmcs_build(e, d, leaf);
+        leaf = nullptr;
+    } catch (...) {
+        cudaStreamSynchronize(e->copy_stream);
+        cudaStreamSynchronize(e->stream);
+        if (leaf) e->dfree(leaf, M * 32);
+        cleanup();
+        free_pcs(d);
+        throw;
+    }
+    cleanup();
+    return d;
+}
+
 b2s_pcs_data* commit_matrices(b2s_engine* e, const b2s_matrix* const* mats, const Fp* shifts, size_t n) {
     StageScope total(e, ST_COMMIT);
     b2s_pcs_data* d = new b2s_pcs_data();
@@ -192,6 +269,7 @@ void b2s_engine_free(b2s_engine* e) {
     }
     for (auto ev : e->event_pool) cudaEventDestroy(ev);
     cudaStreamSynchronize(e->stream);
+    if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
     if (e->own_stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -433,6 +511,30 @@ int32_t b2s_prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size
         memcpy(buf, bytes.data(), bytes.size());
         *proof_bytes = buf;
         *proof_len = bytes.size();
+    });
+}
+
+int32_t b2s_commit_host(b2s_engine* e, const uint32_t* host, uint64_t height, uint64_t width, int32_t layout, int32_t repr,
+                        uint32_t* root8, b2s_pcs_data** out) {
+    if (!e || !host || !out) return B2S_ERR_BAD_ARG;
+    *out = nullptr;
+    return guarded(e, [&] {
+        B2_REQUIRE((layout == B2S_LAYOUT_ROW_MAJOR || layout == B2S_LAYOUT_COL_MAJOR) &&
+                       (repr == B2S_REPR_CANONICAL || repr == B2S_REPR_MONTY),
+                   B2S_ERR_BAD_ARG, "commit_host: bad layout / representation");
+        b2s_pcs_data* d = commit_host_streamed(e, host, height, width, layout, repr);
+        if (root8) {
+            try {
+                uint32_t r[8];
+                B2_CUDA(cudaMemcpyAsync(r, d->layers.back(), 32, cudaMemcpyDeviceToHost, e->stream));
+                B2_CUDA(cudaStreamSynchronize(e->stream));
+                for (int k = 0; k < 8; k++) root8[k] = Fp::raw(r[k]).to_canonical();
+            } catch (...) {
+                free_pcs(d);
+                throw;
+            }
+        }
+        *out = d;
     });
 }
 

@@ -64,6 +64,7 @@ struct b2s_engine {
     std::vector<cudaEvent_t> event_pool;
     uint64_t launches[4] = {0, 0, 0, 0};  // lde, leaf, compress, other
     uint64_t permutations = 0;
+    cudaStream_t copy_stream = nullptr;                     // host -> device staging of the streaming commit
     uint32_t pow_override[2] = {0xFFFFFFFFu, 0xFFFFFFFFu};  // [logup, fri]; 0xFFFFFFFF = search for the minimum witness
     std::map<unsigned, b2::TwiddleSet*> twiddles;  // by log size
     std::map<uint64_t, b2::ScaleSet*> scales;      // by (logn, log_blowup, shift_in)
@@ -155,7 +156,9 @@ void lde_columns(b2s_engine* e, const uint32_t* in, uint64_t in_col_stride, unsi
 void free_twiddles(b2s_engine* e);
 void free_scales(b2s_engine* e);
 // merkle.cu
-void mmcs_build(b2s_engine* e, b2s_pcs_data* d);
+void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer = nullptr);
+void leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_t n, uint32_t* state, uint32_t* out, bool first,
+                 bool last);
 void poseidon2_permute_states(b2s_engine* e, uint32_t* d_states, size_t n);
 void convert_repr(b2s_engine* e, uint32_t* d, size_t n, bool to_monty);
 void transpose_to_colmajor(b2s_engine* e, const uint32_t* d_rowmajor, uint32_t* d_colmajor, uint64_t height,

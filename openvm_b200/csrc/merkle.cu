@@ -110,10 +110,59 @@ __global__ void __launch_bounds__(TAIL_THREADS, 1) tree_tail_kernel(TailParams p
     }
 }
 
+// Streaming leaf sponge for a tall matrix whose columns arrive in groups (commit_host_streamed, api.cu): absorbs
+// columns [0, ncols) of `base` (column stride = n) into the per-row sponge states. `state` holds the 16 words of every
+// row as word-planes between groups (read unless `first`, written unless `last`); the last group writes the digest
+// planes to `out`. Every group but the last has ncols % 8 == 0, so a group boundary is always a permutation boundary.
+__global__ void __launch_bounds__(HASH_THREADS, HASH_MIN_BLOCKS)
+    leaf_absorb_kernel(const uint32_t* __restrict__ base, uint32_t ncols, uint64_t n, uint32_t* __restrict__ state,
+                       uint32_t* __restrict__ out, int first, int last) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fp s[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) s[k] = first ? Fp::zero() : Fp::raw(state[(uint64_t)k * n + i]);
+    const uint32_t chunks = (ncols + 7) >> 3;
+    uint32_t nxt[8];
+    auto fetch = [&](uint32_t chunk) {
+        const uint32_t c = chunk << 3;
+#pragma unroll
+        for (int k = 0; k < 8; k++) nxt[k] = (c + k < ncols) ? __ldg(base + (uint64_t)(c + k) * n + i) : 0u;
+    };
+    if (chunks) fetch(0);
+#pragma unroll 1
+    for (uint32_t it = 0; it < chunks; it++) {
+        const uint32_t c = it << 3;
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+            if (c + k < ncols) s[k] = Fp::raw(nxt[k]);
+        if (it + 1 < chunks) fetch(it + 1);
+        poseidon2_permute(s);
+    }
+    if (last) {
+#pragma unroll
+        for (int w = 0; w < 8; w++) out[(uint64_t)w * n + i] = s[w].v;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 16; k++) state[(uint64_t)k * n + i] = s[k].v;
+    }
+}
+
 static inline unsigned grid_for(uint64_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
 
-// Build the tree of d->mats (any heights). Fills d->layers.
-void mmcs_build(b2s_engine* e, b2s_pcs_data* d) {
+void leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_t n, uint32_t* state, uint32_t* out, bool first,
+                 bool last) {
+    StageScope sc(e, ST_LEAF);
+    leaf_absorb_kernel<<<grid_for(n, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(base, ncols, n, state, out, first ? 1 : 0,
+                                                                                   last ? 1 : 0);
+    B2_CHECK_LAUNCH();
+    e->launches[1]++;
+    e->permutations += n * ((ncols + 7) / 8);
+}
+
+// Build the tree of d->mats (any heights). Fills d->layers. `leaf_layer` (optional): digest planes of the tallest height
+// group, already computed by the streaming sponge; the tree takes ownership of it.
+void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
     B2_REQUIRE(!d->mats.empty(), B2S_ERR_BAD_ARG, "mmcs: no matrices");
     uint64_t hmax = 0;
     for (auto* m : d->mats) {
@@ -143,7 +192,10 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d) {
     // leaves
     d->layers.clear();
     d->layer_nodes.clear();
-    {
+    if (leaf_layer) {
+        d->layers.push_back(leaf_layer);
+        d->layer_nodes.push_back(hmax);
+    } else {
         StageScope sc(e, ST_LEAF);
         uint32_t* leaf = (uint32_t*)e->dmalloc(hmax * 32);
         uint32_t nc = (uint32_t)groups[hmax].size();

@@ -253,6 +253,21 @@ class B2Device:
                                    root.ctypes.data_as(_lib.u32p), C.byref(out)))
         return root, PcsData(e, out)
 
+    def commit_host(self, matrix=None, layout="row", repr="canonical", host_ptr=None, height=None, width=None):
+        """transport_matrix_to_device + commit of one tall host trace as a pipelined call (b2s_commit_host): the upload
+        of column groups overlaps the LDE and hashing of the previous group. Either `matrix` (a (height, width) array,
+        or (width, height) for layout 'col') or a raw `host_ptr` with height / width (e.g. pinned torch memory)."""
+        e = self._e
+        if matrix is not None:
+            a = np.ascontiguousarray(matrix, dtype=np.uint32)
+            height, width = a.shape if layout == "row" else a.shape[::-1]
+            host_ptr = a.ctypes.data
+        root = np.zeros(8, dtype=np.uint32)
+        out = C.c_void_p()
+        e._check(e._lib.b2s_commit_host(e._h, host_ptr, height, width, 0 if layout == "row" else 1,
+                                        0 if repr == "canonical" else 1, root.ctypes.data, C.byref(out)))
+        return root, PcsData(e, out)
+
     def coset_lde(self, matrix, log_blowup, shift=1):
         e = self._e
         out = C.c_void_p()

@@ -99,3 +99,26 @@ def test_commit_full_scale_properties(engine):
         sib = proof[lvl]
         node = orc.compress(sib, node) if (idx >> lvl) & 1 else orc.compress(node, sib)
     assert np.array_equal(node, r1)
+
+
+@pytest.mark.parametrize("h,w,layout,repr_", [
+    (1 << 10, 5, "row", "canonical"), (1 << 12, 40, "col", "canonical"), (1 << 16, 19, "row", "canonical"),
+    (1 << 23, 24, "col", "canonical"),   # 3 column groups of 8: state carried across groups
+    (1 << 22, 50, "row", "canonical"),   # 4 groups of 16, ragged last group, strided 2-D copies
+    (1, 3, "row", "canonical"),
+])
+def test_commit_host_streamed_equals_upload_then_commit(engine, h, w, layout, repr_):
+    """b2s_commit_host (pipelined upload + LDE + streaming sponge) == b2s_matrix_upload + b2s_commit: same root, same
+    opening at a few indices (rows of the retained LDE and the authentication path)."""
+    dev = engine.device()
+    rng = np.random.default_rng(h ^ w)
+    m = rng.integers(0, P, size=(h, w), dtype=np.uint32)
+    src = m if layout == "row" else np.ascontiguousarray(m.T)
+    r1, p1 = dev.commit_host(src, layout=layout, repr=repr_)
+    dm = dev.transport_matrix_to_device(m)
+    r2, p2 = dev.commit([dm])
+    assert list(r1) == list(r2)
+    for idx in (0, 1, (h << 1) - 1, (h << 1) // 3):
+        (rows1, proof1), (rows2, proof2) = p1.open_batch(idx), p2.open_batch(idx)
+        assert np.array_equal(rows1[0], rows2[0]) and np.array_equal(proof1, proof2)
+    p1.free(); p2.free(); dm.free()
