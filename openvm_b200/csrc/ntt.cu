@@ -255,35 +255,57 @@ __global__ void __launch_bounds__(K1_THREADS) ntt_strided_kernel(PassParams p) {
     const uint32_t* in = p.in + (uint64_t)col * p.in_col_stride + (p.in_block ? blk_off : 0);
     uint32_t* out = p.out + (uint64_t)col * p.out_col_stride + blk_off;
 
+    // Staging moves 16 bytes per thread and iteration (LDG.128 / STG.128): the index arithmetic, which is a quarter of
+    // all instructions of a pass when done per word (profiles/r1c), is paid once per four words.
     if constexpr (GATHER) {
         const Fp sc = Fp::raw(p.scale);
-        for (uint32_t e = tid; e < (32u << D); e += K1_THREADS) {
-            const uint32_t r = e & ((1u << D) - 1), t = e >> D;
-            const uint32_t ilo = (chunk << 5) + t;
-            const uint64_t run = (uint64_t)(__brev(ilo) >> (32 - low_bits)) << D;
-            x[r * PITCH + t] = (Fp::raw(in[run + r]) * sc).v;
+        if constexpr (D >= 2) {
+            // a warp covers 2^A 16-byte pieces of 2^(5-A) runs: full 128-byte lines from global memory, and the four
+            // transposed stores land in banks 4a + b (pitch 33), all different for A = 3
+            constexpr int A = (D - 2) < 3 ? (D - 2) : 3;
+            for (uint32_t e = tid; e < (8u << D); e += K1_THREADS) {
+                const uint32_t a = e & ((1u << A) - 1), b = (e >> A) & ((1u << (5 - A)) - 1);
+                const uint32_t c = (e >> 5) & ((1u << (D - 2 - A)) - 1), d = e >> (D + 3 - A);
+                const uint32_t r = ((c << A) | a) << 2, t = (d << (5 - A)) | b;
+                const uint32_t ilo = (chunk << 5) + t;
+                const uint64_t run = (uint64_t)(__brev(ilo) >> (32 - low_bits)) << D;
+                const uint4 v = *reinterpret_cast<const uint4*>(in + run + r);
+                uint32_t* xd = x + r * PITCH + t;
+                xd[0] = (Fp::raw(v.x) * sc).v;
+                xd[PITCH] = (Fp::raw(v.y) * sc).v;
+                xd[2 * PITCH] = (Fp::raw(v.z) * sc).v;
+                xd[3 * PITCH] = (Fp::raw(v.w) * sc).v;
+            }
+        } else {
+            for (uint32_t e = tid; e < (32u << D); e += K1_THREADS) {
+                const uint32_t r = e & ((1u << D) - 1), t = e >> D;
+                const uint32_t ilo = (chunk << 5) + t;
+                const uint64_t run = (uint64_t)(__brev(ilo) >> (32 - low_bits)) << D;
+                x[r * PITCH + t] = (Fp::raw(in[run + r]) * sc).v;
+            }
         }
     } else {
         const uint64_t base = ((uint64_t)top << (n - p.t0)) + ((uint64_t)chunk << 5);
-        for (uint32_t e = tid; e < (32u << D); e += K1_THREADS) {
-            const uint32_t t = e & 31, r = e >> 5;
-            x[r * PITCH + t] = in[base + ((uint64_t)r << low_bits) + t];
+        for (uint32_t e = tid; e < (8u << D); e += K1_THREADS) {
+            const uint32_t q = (e & 7) << 2, r = e >> 3;
+            *reinterpret_cast<uint4*>(x + r * PITCH + q) = *reinterpret_cast<const uint4*>(in + base + ((uint64_t)r << low_bits) + q);
         }
     }
     __syncthreads();
     K1Rounds<D, 0, GATHER>::run(x, z, (1u << p.t0) + top);
     if constexpr (GATHER) {
         const uint64_t base = (uint64_t)chunk << 5;
-        for (uint32_t e = tid; e < (32u << D); e += K1_THREADS) {
-            const uint32_t t = e & 31, r = e >> 5;
+        for (uint32_t e = tid; e < (8u << D); e += K1_THREADS) {
+            const uint32_t q = (e & 7) << 2, r = e >> 3;
             const uint32_t row = D ? (__brev(r) >> (32 - D)) : 0u;
-            out[base + ((uint64_t)row << low_bits) + t] = x[r * PITCH + t];
+            const uint32_t* xs = x + r * PITCH + q;
+            *reinterpret_cast<uint4*>(out + base + ((uint64_t)row << low_bits) + q) = make_uint4(xs[0], xs[1], xs[2], xs[3]);
         }
     } else {
         const uint64_t base = ((uint64_t)top << (n - p.t0)) + ((uint64_t)chunk << 5);
-        for (uint32_t e = tid; e < (32u << D); e += K1_THREADS) {
-            const uint32_t t = e & 31, r = e >> 5;
-            out[base + ((uint64_t)r << low_bits) + t] = x[r * PITCH + t];
+        for (uint32_t e = tid; e < (8u << D); e += K1_THREADS) {
+            const uint32_t q = (e & 7) << 2, r = e >> 3;
+            *reinterpret_cast<uint4*>(out + base + ((uint64_t)r << low_bits) + q) = *reinterpret_cast<const uint4*>(x + r * PITCH + q);
         }
     }
 }
@@ -351,15 +373,29 @@ __global__ void __launch_bounds__(K2Cfg<D>::THREADS) ntt_contig_kernel(PassParam
     const uint64_t run0 = (uint64_t)blockIdx.x * C::RPC;
     const Fp sc = Fp::raw(p.scale);
 
-    for (uint32_t e = tid; e < ((uint32_t)C::RPC << D); e += C::THREADS) {
-        const uint32_t rs = e >> D, w = e & ((1u << D) - 1);
+    // 16 bytes per thread and iteration when the run is at least 4 words (see ntt_strided_kernel)
+    constexpr int V = D >= 2 ? 4 : 1;
+    constexpr int LV = D >= 2 ? 2 : 0;
+    for (uint32_t e = tid; e < ((uint32_t)C::RPC << (D - LV)); e += C::THREADS) {
+        const uint32_t rs = e >> (D - LV), w = (e & ((1u << (D - LV)) - 1)) << LV;
         const uint64_t g = run0 + rs;
         if (g >= total_runs) break;
         const uint64_t col = g >> log_rpc, rho = g & (((uint64_t)1 << log_rpc) - 1);
-        Fp v = Fp::raw(p.in[col * p.in_col_stride + in_off + (rho << D) + w]);
-        if (p.scale) v = v * sc;
-        const uint32_t slot = (p.reverse_load && D) ? (__brev(w) >> (32 - D)) : w;
-        x[rs * C::PITCH + phys(slot)] = v.v;
+        const uint32_t* src = p.in + col * p.in_col_stride + in_off + (rho << D) + w;
+        uint32_t v[V];
+        if constexpr (V == 4) {
+            const uint4 q = *reinterpret_cast<const uint4*>(src);
+            v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+        } else {
+            v[0] = src[0];
+        }
+        uint32_t* xr = x + rs * C::PITCH;
+#pragma unroll
+        for (int j = 0; j < V; j++) {
+            const uint32_t val = p.scale ? (Fp::raw(v[j]) * sc).v : v[j];
+            const uint32_t slot = (p.reverse_load && D) ? (__brev(w + j) >> (32 - D)) : w + j;
+            xr[phys(slot)] = val;
+        }
     }
     __syncthreads();
     {
@@ -368,12 +404,15 @@ __global__ void __launch_bounds__(K2Cfg<D>::THREADS) ntt_contig_kernel(PassParam
         const uint32_t rho = (uint32_t)(g & (((uint64_t)1 << log_rpc) - 1));
         K2Rounds<D, 0>::run(x + rs * C::PITCH, z, (1u << p.t0) + rho, tr, g < total_runs);
     }
-    for (uint32_t e = tid; e < ((uint32_t)C::RPC << D); e += C::THREADS) {
-        const uint32_t rs = e >> D, w = e & ((1u << D) - 1);
+    for (uint32_t e = tid; e < ((uint32_t)C::RPC << (D - LV)); e += C::THREADS) {
+        const uint32_t rs = e >> (D - LV), w = (e & ((1u << (D - LV)) - 1)) << LV;
         const uint64_t g = run0 + rs;
         if (g >= total_runs) break;
         const uint64_t col = g >> log_rpc, rho = g & (((uint64_t)1 << log_rpc) - 1);
-        p.out[col * p.out_col_stride + blk_off + (rho << D) + w] = x[rs * C::PITCH + phys(w)];
+        uint32_t* dst = p.out + col * p.out_col_stride + blk_off + (rho << D) + w;
+        const uint32_t* xs = x + rs * C::PITCH + phys(w);  // w % 4 == 0: the four words share one group of 32
+        if constexpr (V == 4) *reinterpret_cast<uint4*>(dst) = make_uint4(xs[0], xs[1], xs[2], xs[3]);
+        else dst[0] = xs[0];
     }
 }
 
