@@ -132,7 +132,7 @@ b2s_pcs_data* commit_host_streamed(b2s_engine* e, const uint32_t* host, uint64_t
     const unsigned logn = log2_exact(N);
     B2_REQUIRE(logn + lb <= TWO_ADICITY, B2S_ERR_SHAPE, "commit: trace too tall for this blowup");
     const uint64_t M = N << lb;
-    uint64_t G = (((uint64_t)1 << 26) / N) & ~(uint64_t)7;
+    uint64_t G = (((uint64_t)1 << 27) / N) & ~(uint64_t)7;
     if (G < 8) G = 8;
     if (G > W) G = W;
     const uint64_t ngroups = (W + G - 1) / G;

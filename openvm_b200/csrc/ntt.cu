@@ -573,9 +573,9 @@ void lde_columns(b2s_engine* e, const uint32_t* in, uint64_t in_col_stride, unsi
     ScaleSet* sc = get_scales(e, logn, log_blowup, shift_in);
     const Plan pl = make_plan(logn);
 
-    // column group: bounded coefficient workspace (256 MiB), large enough that every launch fills the chip several
+    // column group: bounded coefficient workspace (512 MiB), large enough that every launch fills the chip several
     // times over (the passes are multiply-bound, not HBM-bound, so L2 residency of the group does not matter)
-    uint64_t group_elems = (uint64_t)1 << 26;
+    uint64_t group_elems = (uint64_t)1 << 27;
     if (const char* env = getenv("B2S_LDE_GROUP_ELEMS")) group_elems = strtoull(env, nullptr, 10);
     uint64_t G = group_elems / N;
     if (G < 1) G = 1;
