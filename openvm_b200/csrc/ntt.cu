@@ -370,7 +370,25 @@ __global__ void __launch_bounds__(K2Cfg<D>::THREADS) ntt_contig_kernel(PassParam
     const uint64_t in_off = p.in_block ? blk_off : 0;
     const uint32_t* __restrict__ z = p.z + ((size_t)cz << n);
     const uint32_t tid = threadIdx.x;
+    // Runs are numbered column-fastest (g = rho * width + col): the runs of one block, and neighbouring blocks, work on
+    // the same sub-problem rho of different columns and therefore read the same twiddles (L1 / L2 hits instead of one
+    // pass over the 2^n-word table per column; r1e capture: the contiguous pass read 2x its data from DRAM).
     const uint64_t run0 = (uint64_t)blockIdx.x * C::RPC;
+    const uint32_t rho0 = (uint32_t)(run0 / p.width), col0 = (uint32_t)(run0 % p.width);
+    auto locate = [&](uint32_t rs, uint32_t& col, uint32_t& rho) {
+        const uint32_t c = col0 + rs;
+        if ((p.width & (p.width - 1)) == 0) {  // column groups are powers of two except a ragged last one
+            col = c & (p.width - 1);
+            rho = rho0 + (c >> (31 - __clz(p.width)));
+        } else if (p.width >= (uint32_t)C::RPC) {
+            const uint32_t wrap = c >= p.width ? 1u : 0u;
+            col = c - wrap * p.width;
+            rho = rho0 + wrap;
+        } else {
+            col = c % p.width;
+            rho = rho0 + c / p.width;
+        }
+    };
     const Fp sc = Fp::raw(p.scale);
 
     // 16 bytes per thread and iteration when the run is at least 4 words (see ntt_strided_kernel)
@@ -380,8 +398,9 @@ __global__ void __launch_bounds__(K2Cfg<D>::THREADS) ntt_contig_kernel(PassParam
         const uint32_t rs = e >> (D - LV), w = (e & ((1u << (D - LV)) - 1)) << LV;
         const uint64_t g = run0 + rs;
         if (g >= total_runs) break;
-        const uint64_t col = g >> log_rpc, rho = g & (((uint64_t)1 << log_rpc) - 1);
-        const uint32_t* src = p.in + col * p.in_col_stride + in_off + (rho << D) + w;
+        uint32_t col, rho;
+        locate(rs, col, rho);
+        const uint32_t* src = p.in + (uint64_t)col * p.in_col_stride + in_off + ((uint64_t)rho << D) + w;
         uint32_t v[V];
         if constexpr (V == 4) {
             const uint4 q = *reinterpret_cast<const uint4*>(src);
@@ -401,15 +420,17 @@ __global__ void __launch_bounds__(K2Cfg<D>::THREADS) ntt_contig_kernel(PassParam
     {
         const uint32_t rs = tid / C::TPR, tr = tid % C::TPR;
         const uint64_t g = run0 + rs;
-        const uint32_t rho = (uint32_t)(g & (((uint64_t)1 << log_rpc) - 1));
+        uint32_t col, rho;
+        locate(rs, col, rho);
         K2Rounds<D, 0>::run(x + rs * C::PITCH, z, (1u << p.t0) + rho, tr, g < total_runs);
     }
     for (uint32_t e = tid; e < ((uint32_t)C::RPC << (D - LV)); e += C::THREADS) {
         const uint32_t rs = e >> (D - LV), w = (e & ((1u << (D - LV)) - 1)) << LV;
         const uint64_t g = run0 + rs;
         if (g >= total_runs) break;
-        const uint64_t col = g >> log_rpc, rho = g & (((uint64_t)1 << log_rpc) - 1);
-        uint32_t* dst = p.out + col * p.out_col_stride + blk_off + (rho << D) + w;
+        uint32_t col, rho;
+        locate(rs, col, rho);
+        uint32_t* dst = p.out + (uint64_t)col * p.out_col_stride + blk_off + ((uint64_t)rho << D) + w;
         const uint32_t* xs = x + rs * C::PITCH + phys(w);  // w % 4 == 0: the four words share one group of 32
         if constexpr (V == 4) *reinterpret_cast<uint4*>(dst) = make_uint4(xs[0], xs[1], xs[2], xs[3]);
         else dst[0] = xs[0];
