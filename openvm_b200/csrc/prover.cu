@@ -26,6 +26,7 @@
 #include <algorithm>
 #include <array>
 #include <chrono>
+#include <deque>
 #include <map>
 
 namespace b2 {
@@ -684,7 +685,24 @@ struct Scratch {  // device buffers released when the proof is done (or abandone
     b2s_engine* e;
     std::vector<std::pair<void*, size_t>> bufs;
     std::vector<b2s_pcs_data*> pcs;
+    std::deque<std::vector<uint32_t>> host_words;        // sources of asynchronous uploads, alive until the proof is done
+    std::deque<std::vector<const uint32_t*>> host_ptrs;
     explicit Scratch(b2s_engine* e_) : e(e_) {}
+    // upload without a stream round trip: the host copy moves into the scratch and outlives the copy
+    uint32_t* upload(std::vector<uint32_t>&& h) {
+        host_words.push_back(std::move(h));
+        const std::vector<uint32_t>& v = host_words.back();
+        uint32_t* d = words(std::max<size_t>(v.size(), 1));
+        if (!v.empty()) B2_CUDA(cudaMemcpyAsync(d, v.data(), v.size() * 4, cudaMemcpyHostToDevice, e->stream));
+        return d;
+    }
+    const uint32_t** upload(std::vector<const uint32_t*>&& h) {
+        host_ptrs.push_back(std::move(h));
+        const std::vector<const uint32_t*>& v = host_ptrs.back();
+        const uint32_t** d = (const uint32_t**)bytes(std::max<size_t>(v.size(), 1) * sizeof(void*));
+        if (!v.empty()) B2_CUDA(cudaMemcpyAsync(d, v.data(), v.size() * sizeof(void*), cudaMemcpyHostToDevice, e->stream));
+        return d;
+    }
     uint32_t* words(size_t n) {
         void* p = e->dmalloc(n * 4);
         bufs.push_back({p, n * 4});
@@ -927,11 +945,8 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             const size_t pv_off = hc.size();
             for (uint32_t j = 0; j < k.num_pv; j++) hc.push_back(Fp::from_canonical(airs[i].public_values[j]).v);
             hc.push_back(0);
-            uint32_t* d_hc = scratch.words(hc.size());
-            const uint32_t** d_cols = (const uint32_t**)scratch.bytes(std::max<size_t>(cols.size(), 1) * sizeof(void*));
-            if (!cols.empty()) B2_CUDA(cudaMemcpyAsync(d_cols, cols.data(), cols.size() * sizeof(void*), cudaMemcpyHostToDevice, e->stream));
-            B2_CUDA(cudaMemcpyAsync(d_hc, hc.data(), hc.size() * 4, cudaMemcpyHostToDevice, e->stream));
-            B2_CUDA(cudaStreamSynchronize(e->stream));
+            uint32_t* d_hc = scratch.upload(std::move(hc));
+            const uint32_t** d_cols = scratch.upload(std::move(cols));
             LogupParams lp{};
             lp.program = k.d_iprogram; lp.prog_len = (uint32_t)k.iprogram.size();
             lp.cols = d_cols; lp.publics = d_hc + pv_off; lp.betas = d_hc; lp.consts = d_hc + consts_off;
@@ -1003,15 +1018,11 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
                 push_cols(after_pcs->mats[pos]);
                 for (int c = 0; c < 4; c++) { efc[c] = challenges[0].c[c].v; efc[4 + c] = challenges[1].c[c].v; efc[8 + c] = cumsum[i].c[c].v; }
             }
-            uint32_t* d_efc = scratch.words(12);
-            B2_CUDA(cudaMemcpyAsync(d_efc, efc.data(), 48, cudaMemcpyHostToDevice, e->stream));
-            const uint32_t** d_cols = (const uint32_t**)scratch.bytes(std::max<size_t>(cols.size(), 1) * sizeof(void*));
-            uint32_t* d_pv = scratch.words(std::max<uint32_t>(k.num_pv, 1));
+            uint32_t* d_efc = scratch.upload(std::move(efc));
             std::vector<uint32_t> pv(std::max<uint32_t>(k.num_pv, 1), 0);
             for (uint32_t j = 0; j < k.num_pv; j++) pv[j] = Fp::from_canonical(airs[i].public_values[j]).v;
-            if (!cols.empty()) B2_CUDA(cudaMemcpyAsync(d_cols, cols.data(), cols.size() * sizeof(void*), cudaMemcpyHostToDevice, e->stream));
-            B2_CUDA(cudaMemcpyAsync(d_pv, pv.data(), pv.size() * 4, cudaMemcpyHostToDevice, e->stream));
-            B2_CUDA(cudaStreamSynchronize(e->stream));
+            uint32_t* d_pv = scratch.upload(std::move(pv));
+            const uint32_t** d_cols = scratch.upload(std::move(cols));
             QuotientParams qp{};
             qp.program = k.d_program; qp.prog_len = (uint32_t)k.program.size();
             qp.cols = d_cols; qp.publics = d_pv; qp.alpha_pows = d_apow; qp.ef_consts = d_efc;
