@@ -263,18 +263,34 @@ __global__ void __launch_bounds__(K1_THREADS) ntt_strided_kernel(PassParams p) {
             // a warp covers 2^A 16-byte pieces of 2^(5-A) runs: full 128-byte lines from global memory, and the four
             // transposed stores land in banks 4a + b (pitch 33), all different for A = 3
             constexpr int A = (D - 2) < 3 ? (D - 2) : 3;
-            for (uint32_t e = tid; e < (8u << D); e += K1_THREADS) {
-                const uint32_t a = e & ((1u << A) - 1), b = (e >> A) & ((1u << (5 - A)) - 1);
-                const uint32_t c = (e >> 5) & ((1u << (D - 2 - A)) - 1), d = e >> (D + 3 - A);
-                const uint32_t r = ((c << A) | a) << 2, t = (d << (5 - A)) | b;
-                const uint32_t ilo = (chunk << 5) + t;
-                const uint64_t run = (uint64_t)(__brev(ilo) >> (32 - low_bits)) << D;
-                const uint4 v = *reinterpret_cast<const uint4*>(in + run + r);
-                uint32_t* xd = x + r * PITCH + t;
-                xd[0] = (Fp::raw(v.x) * sc).v;
-                xd[PITCH] = (Fp::raw(v.y) * sc).v;
-                xd[2 * PITCH] = (Fp::raw(v.z) * sc).v;
-                xd[3 * PITCH] = (Fp::raw(v.w) * sc).v;
+            constexpr uint32_t TOTAL = 8u << D;
+            constexpr int BATCH = TOTAL / K1_THREADS >= 8 ? 8 : (TOTAL / K1_THREADS ? TOTAL / K1_THREADS : 1);
+            for (uint32_t e0 = 0; e0 < TOTAL; e0 += BATCH * K1_THREADS) {
+                uint4 buf[BATCH];
+#pragma unroll
+                for (int k = 0; k < BATCH; k++) {
+                    const uint32_t e = e0 + k * K1_THREADS + tid;
+                    const uint32_t a = e & ((1u << A) - 1), b = (e >> A) & ((1u << (5 - A)) - 1);
+                    const uint32_t c = (e >> 5) & ((1u << (D - 2 - A)) - 1), d = e >> (D + 3 - A);
+                    const uint32_t r = ((c << A) | a) << 2, t = (d << (5 - A)) | b;
+                    const uint32_t ilo = (chunk << 5) + t;
+                    const uint64_t run = (uint64_t)(__brev(ilo) >> (32 - low_bits)) << D;
+                    if (e < TOTAL) buf[k] = *reinterpret_cast<const uint4*>(in + run + r);
+                }
+#pragma unroll
+                for (int k = 0; k < BATCH; k++) {
+                    const uint32_t e = e0 + k * K1_THREADS + tid;
+                    const uint32_t a = e & ((1u << A) - 1), b = (e >> A) & ((1u << (5 - A)) - 1);
+                    const uint32_t c = (e >> 5) & ((1u << (D - 2 - A)) - 1), d = e >> (D + 3 - A);
+                    const uint32_t r = ((c << A) | a) << 2, t = (d << (5 - A)) | b;
+                    if (e < TOTAL) {
+                        uint32_t* xd = x + r * PITCH + t;
+                        xd[0] = (Fp::raw(buf[k].x) * sc).v;
+                        xd[PITCH] = (Fp::raw(buf[k].y) * sc).v;
+                        xd[2 * PITCH] = (Fp::raw(buf[k].z) * sc).v;
+                        xd[3 * PITCH] = (Fp::raw(buf[k].w) * sc).v;
+                    }
+                }
             }
         } else {
             for (uint32_t e = tid; e < (32u << D); e += K1_THREADS) {
@@ -285,10 +301,25 @@ __global__ void __launch_bounds__(K1_THREADS) ntt_strided_kernel(PassParams p) {
             }
         }
     } else {
+        // all loads of a batch are issued before the first store (up to 8 x 16 bytes in flight per thread): the loop
+        // as written per element was one dependent LDG -> STS round trip per iteration (r1e: long_scoreboard 5.6)
         const uint64_t base = ((uint64_t)top << (n - p.t0)) + ((uint64_t)chunk << 5);
-        for (uint32_t e = tid; e < (8u << D); e += K1_THREADS) {
-            const uint32_t q = (e & 7) << 2, r = e >> 3;
-            *reinterpret_cast<uint4*>(x + r * PITCH + q) = *reinterpret_cast<const uint4*>(in + base + ((uint64_t)r << low_bits) + q);
+        constexpr uint32_t TOTAL = 8u << D;
+        constexpr int BATCH = TOTAL / K1_THREADS >= 8 ? 8 : (TOTAL / K1_THREADS ? TOTAL / K1_THREADS : 1);
+        for (uint32_t e0 = 0; e0 < TOTAL; e0 += BATCH * K1_THREADS) {
+            uint4 buf[BATCH];
+#pragma unroll
+            for (int k = 0; k < BATCH; k++) {
+                const uint32_t e = e0 + k * K1_THREADS + tid;
+                const uint32_t q = (e & 7) << 2, r = e >> 3;
+                if (e < TOTAL) buf[k] = *reinterpret_cast<const uint4*>(in + base + ((uint64_t)r << low_bits) + q);
+            }
+#pragma unroll
+            for (int k = 0; k < BATCH; k++) {
+                const uint32_t e = e0 + k * K1_THREADS + tid;
+                const uint32_t q = (e & 7) << 2, r = e >> 3;
+                if (e < TOTAL) *reinterpret_cast<uint4*>(x + r * PITCH + q) = buf[k];
+            }
         }
     }
     __syncthreads();
@@ -394,26 +425,39 @@ __global__ void __launch_bounds__(K2Cfg<D>::THREADS) ntt_contig_kernel(PassParam
     // 16 bytes per thread and iteration when the run is at least 4 words (see ntt_strided_kernel)
     constexpr int V = D >= 2 ? 4 : 1;
     constexpr int LV = D >= 2 ? 2 : 0;
-    for (uint32_t e = tid; e < ((uint32_t)C::RPC << (D - LV)); e += C::THREADS) {
-        const uint32_t rs = e >> (D - LV), w = (e & ((1u << (D - LV)) - 1)) << LV;
-        const uint64_t g = run0 + rs;
-        if (g >= total_runs) break;
-        uint32_t col, rho;
-        locate(rs, col, rho);
-        const uint32_t* src = p.in + (uint64_t)col * p.in_col_stride + in_off + ((uint64_t)rho << D) + w;
-        uint32_t v[V];
-        if constexpr (V == 4) {
-            const uint4 q = *reinterpret_cast<const uint4*>(src);
-            v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
-        } else {
-            v[0] = src[0];
-        }
-        uint32_t* xr = x + rs * C::PITCH;
+    constexpr uint32_t TOTAL = (uint32_t)C::RPC << (D - LV);
+    constexpr int BATCH = TOTAL / C::THREADS >= 4 ? 4 : (TOTAL / C::THREADS ? TOTAL / C::THREADS : 1);
+    for (uint32_t e0 = 0; e0 < TOTAL; e0 += BATCH * C::THREADS) {
+        uint32_t v[BATCH][V];
 #pragma unroll
-        for (int j = 0; j < V; j++) {
-            const uint32_t val = p.scale ? (Fp::raw(v[j]) * sc).v : v[j];
-            const uint32_t slot = (p.reverse_load && D) ? (__brev(w + j) >> (32 - D)) : w + j;
-            xr[phys(slot)] = val;
+        for (int k = 0; k < BATCH; k++) {  // all loads of the batch in flight before the first use
+            const uint32_t e = e0 + k * C::THREADS + tid;
+            const uint32_t rs = e >> (D - LV), w = (e & ((1u << (D - LV)) - 1)) << LV;
+            uint32_t col, rho;
+            locate(rs, col, rho);
+            if (e < TOTAL && run0 + rs < total_runs) {
+                const uint32_t* src = p.in + (uint64_t)col * p.in_col_stride + in_off + ((uint64_t)rho << D) + w;
+                if constexpr (V == 4) {
+                    const uint4 q = *reinterpret_cast<const uint4*>(src);
+                    v[k][0] = q.x; v[k][1] = q.y; v[k][2] = q.z; v[k][3] = q.w;
+                } else {
+                    v[k][0] = src[0];
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < BATCH; k++) {
+            const uint32_t e = e0 + k * C::THREADS + tid;
+            const uint32_t rs = e >> (D - LV), w = (e & ((1u << (D - LV)) - 1)) << LV;
+            if (e < TOTAL && run0 + rs < total_runs) {
+                uint32_t* xr = x + rs * C::PITCH;
+#pragma unroll
+                for (int j = 0; j < V; j++) {
+                    const uint32_t val = p.scale ? (Fp::raw(v[k][j]) * sc).v : v[k][j];
+                    const uint32_t slot = (p.reverse_load && D) ? (__brev(w + j) >> (32 - D)) : w + j;
+                    xr[phys(slot)] = val;
+                }
+            }
         }
     }
     __syncthreads();
