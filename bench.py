@@ -221,8 +221,22 @@ def main():
 
     # ---- end to end through the C ABI from pinned host memory
     e2e = None
+    nbytes = H * width * 4
     if not args.no_e2e:
-        nbytes = H * width * 4
+        # every rank holds its own host copy of the trace: refuse to drive the box out of memory
+        try:
+            avail = [int(l.split()[1]) * 1024 for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0]
+        except Exception:
+            avail = None
+        local_world = int(os.environ.get("LOCAL_WORLD_SIZE", world))
+        short = avail is not None and avail < 1.25 * nbytes * local_world
+        if world > 1:
+            t = torch.tensor([1.0 if short else 0.0], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            short = bool(t.item() > 0)
+        if short:
+            e2e = {"skipped": f"host memory: {avail} bytes available for {local_world} ranks x {nbytes} bytes"}
+    if not args.no_e2e and e2e is None:
         try:
             host = torch.empty(H * width, dtype=torch.int32, pin_memory=True)
         except RuntimeError:
