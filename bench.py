@@ -171,6 +171,25 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    # stdout carries exactly one JSON line: libraries that print there (NCCL's version banner) go to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    # run each rank on the CPUs next to its GPU, so that the pinned host buffer of the end-to-end leg is allocated on the
+    # GPU's NUMA node (8 ranks streaming 16 GiB each otherwise cross the socket interconnect)
+    all_cpus = os.sched_getaffinity(0)
+    numa = None
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            h = pynvml.nvmlDeviceGetHandleByUUID("GPU-" + str(torch.cuda.get_device_properties(local_rank).uuid))
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        numa = sorted(os.sched_getaffinity(0))
+    except Exception:
+        pass
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -373,7 +392,8 @@ def main():
                 parts, pv = A.chain_trace(sair[i], 1 << lh, seed=i)
                 sin.append((i, parts, pv))
                 scells += w << lh
-            threads = os.cpu_count() or 1
+            os.sched_setaffinity(0, all_cpus)
+            threads = len(all_cpus)
             t0 = time.perf_counter()
             sproof = orc.stark_prove(skey, sin, b, peng.fri_params().num_queries, 16, threads=threads)
             cpu_ms = (time.perf_counter() - t0) * 1e3
@@ -417,7 +437,8 @@ def main():
         }
         cpu = None
         if not args.no_cpu:
-            threads = os.cpu_count() or 1
+            os.sched_setaffinity(0, all_cpus)
+            threads = len(all_cpus)
             s = args.cpu_sample_log_height
             dt = cpu_oracle_sample(s, width, b, threads)
             cpu = {"value": algorithmic_bytes(s, width, b) / dt / 1e9, "unit": UNIT, "cores": threads, "kind": "port",
@@ -428,6 +449,7 @@ def main():
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
             "data": "synthetic",
             "config": {"workload": workload_name(log_h, width, b), "segments_per_gpu": 1,
+                       "cpu_affinity": f"rank 0 pinned to {len(numa)} CPUs next to its GPU" if numa else "unpinned",
                        "l2": "inputs (16 GiB trace, 32 GiB LDE) are far larger than the 126 MB L2; no flush needed",
                        "fri": {"log_blowup": b}},
             "roofline": roofline, "roofline_lde": roofline_lde, "int_pipe": int_pipe, "cpu_baseline": cpu,
@@ -437,7 +459,7 @@ def main():
                                   "compress_ms": met["compress_ms"] / steps},
             "root": [int(x) for x in root],
         }
-        print(json.dumps(line), flush=True)
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
     trace.free()
     eng.close()
     if world > 1:
