@@ -212,6 +212,13 @@ int32_t b2s_engine_set_pow_witnesses(b2s_engine* e, uint32_t logup_witness, uint
  * (InvalidProofShape, InvalidOpeningArgument, InvalidPowWitness, NonZeroCumulativeSum, OodEvaluationMismatch ...). */
 int32_t b2s_verify(b2s_engine* e, const b2s_pk* pk, const uint8_t* proof_bytes, size_t proof_len);
 
+/* The quotient kernels of an AIR are generated as PTX from its constraint DAG when the key is loaded and compiled by
+ * the driver (openvm_b200/csrc/qjit.cu; B2S_QUOTIENT_JIT=0 selects the interpreter instead). This entry point returns
+ * that PTX text for AIR `air_index` of a key blob without touching a device (release with b2s_free): tests assemble
+ * it with ptxas for sm_100a. */
+int32_t b2s_debug_quotient_ptx(const uint32_t* key_words, size_t n_words, uint32_t log_blowup, uint32_t air_index,
+                               char** ptx_out);
+
 /* ---- primitives run on the device, for known-answer / parity tests ------------------------------------ */
 /* n states of 16 canonical words, permuted in place on the GPU */
 int32_t b2s_poseidon2_permute(b2s_engine* e, uint32_t* host_states, size_t n_states);

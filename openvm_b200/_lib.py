@@ -65,6 +65,7 @@ SIGNATURES = {
     "b2s_pk_free": (None, [vp]),
     "b2s_commit_host": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint64, C.c_int32, C.c_int32, vp, C.POINTER(vp)]),
     "b2s_engine_set_pow_witnesses": (C.c_int32, [vp, C.c_uint32, C.c_uint32]),
+    "b2s_debug_quotient_ptx": (C.c_int32, [vp, C.c_size_t, C.c_uint32, C.c_uint32, C.POINTER(vp)]),
     "b2s_verify": (C.c_int32, [vp, vp, C.c_char_p, C.c_size_t]),
     "b2s_prove": (C.c_int32, [vp, vp, vp, C.c_size_t, C.POINTER(vp), C.POINTER(C.c_size_t)]),
     "b2s_poseidon2_permute": (C.c_int32, [vp, vp, C.c_size_t]),

@@ -265,6 +265,7 @@ void b2s_engine_free(b2s_engine* e) {
         e->collect_timers();
         free_twiddles(e);
         free_scales(e);
+        free_selectors(e);
     } catch (...) {
     }
     for (auto ev : e->event_pool) cudaEventDestroy(ev);
@@ -545,6 +546,26 @@ int32_t b2s_engine_set_pow_witnesses(b2s_engine* e, uint32_t logup_witness, uint
                    B2S_ERR_BAD_ARG, "pow witnesses must be canonical field elements or B2S_POW_SEARCH");
         e->pow_override[0] = logup_witness;
         e->pow_override[1] = fri_witness;
+    });
+}
+
+int32_t b2s_debug_quotient_ptx(const uint32_t* key_words, size_t n_words, uint32_t log_blowup, uint32_t air_index, char** ptx_out) {
+    if (!key_words || !ptx_out) return B2S_ERR_BAD_ARG;
+    *ptx_out = nullptr;
+    return guarded(nullptr, [&] {
+        b2s_pk* pk = pk_load(nullptr, key_words, n_words, true, log_blowup);
+        try {
+            B2_REQUIRE(air_index < pk->airs.size(), B2S_ERR_BAD_ARG, "air index out of range");
+            const std::string ptx = quotient_jit_ptx(pk->airs[air_index]);
+            char* buf = (char*)malloc(ptx.size() + 1);
+            if (!buf) fail(B2S_ERR_OOM, "ptx buffer allocation failed");
+            memcpy(buf, ptx.c_str(), ptx.size() + 1);
+            *ptx_out = buf;
+        } catch (...) {
+            pk_free(pk);
+            throw;
+        }
+        pk_free(pk);
     });
 }
 

@@ -65,6 +65,8 @@ struct b2s_engine {
     uint64_t launches[4] = {0, 0, 0, 0};  // lde, leaf, compress, other
     uint64_t permutations = 0;
     cudaStream_t copy_stream = nullptr;                     // host -> device staging of the streaming commit
+    std::map<uint64_t, uint32_t*> selector_cache;           // (log height, log quotient degree, blowup) -> 4 planes
+    size_t selector_cache_bytes = 0;
     uint32_t pow_override[2] = {0xFFFFFFFFu, 0xFFFFFFFFu};  // [logup, fri]; 0xFFFFFFFF = search for the minimum witness
     std::map<unsigned, b2::TwiddleSet*> twiddles;  // by log size
     std::map<uint64_t, b2::ScaleSet*> scales;      // by (logn, log_blowup, shift_in)
@@ -117,6 +119,10 @@ struct AirKeyDev {
     // symbolic constraints as loaded ({kind, a, b, c} per node), kept for the verifier's evaluation at zeta
     std::vector<uint4> nodes;
     std::vector<uint32_t> constraint_idx;
+    // JIT-compiled quotient kernels (qjit.cu): cudaKernel_t handles, empty when the interpreter is used
+    std::vector<void*> jit_kernels;
+    std::vector<std::string> jit_ptx;     // only while the key is being loaded
+    uint32_t jit_num_mats = 0;
     uint32_t total_cols() const {
         uint32_t t = width_prep + width_common;
         for (uint32_t w : cached_widths) t += w;
@@ -177,8 +183,16 @@ struct OpenDesc {
     uint32_t out_off;
 };
 void gather_rows(b2s_engine* e, const std::vector<OpenDesc>& descs, size_t total_words, uint32_t* h_out);
+// qjit.cu
+bool quotient_jit_enabled();
+size_t quotient_jit_prepare(AirKeyDev& a);
+void quotient_jit_compile(AirKeyDev& a, size_t k);
+std::string quotient_jit_ptx(const AirKeyDev& a);
+void quotient_jit_launch(b2s_engine* e, const AirKeyDev& a, const uint32_t* const* mats, const uint32_t* publics,
+                         const uint32_t* alpha_pows, const uint32_t* ef_consts, uint32_t* acc, uint32_t* out, unsigned n, unsigned lq);
+void free_selectors(b2s_engine* e);
 // prover.cu
-b2s_pk* pk_load(b2s_engine* e, const uint32_t* words, size_t n);
+b2s_pk* pk_load(b2s_engine* e, const uint32_t* words, size_t n, bool host_only = false, uint32_t log_blowup = 0);
 void pk_free(b2s_pk* pk);
 void verify(const b2s_engine* e, const b2s_pk* pk, const uint8_t* proof, size_t len);
 void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_airs, std::vector<uint8_t>& out);

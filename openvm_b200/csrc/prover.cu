@@ -27,7 +27,9 @@
 #include <array>
 #include <chrono>
 #include <deque>
+#include <atomic>
 #include <map>
+#include <thread>
 
 namespace b2 {
 
@@ -200,6 +202,7 @@ static void root_monty(b2s_engine* e, const b2s_pcs_data* d, uint32_t out[8]) {
 void pk_free(b2s_pk* pk) {
     if (!pk) return;
     b2s_engine* e = pk->eng;
+    if (!e) { delete pk; return; }
     for (auto& a : pk->airs) {
         if (a.prep_pcs) free_pcs(a.prep_pcs);
         if (a.prep_trace) b2s_matrix_free(a.prep_trace);
@@ -209,7 +212,9 @@ void pk_free(b2s_pk* pk) {
     delete pk;
 }
 
-b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n) {
+// host_only: parse and validate without touching a device (e may be null); used to inspect the generated quotient PTX
+b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n, bool host_only, uint32_t log_blowup) {
+    if (!host_only) log_blowup = e->params.log_blowup;
     size_t i = 0;
     auto rd = [&]() -> uint32_t {
         if (i >= n) fail(B2S_ERR_BAD_ARG, "key blob truncated");
@@ -218,7 +223,7 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n) {
     B2_REQUIRE(rd() == 0x4B503242u, B2S_ERR_BAD_ARG, "key blob: bad magic");
     B2_REQUIRE(rd() == 2, B2S_ERR_BAD_ARG, "key blob: unsupported version");
     b2s_pk* pk = new b2s_pk();
-    pk->eng = e;
+    pk->eng = host_only ? nullptr : e;
     try {
         for (int j = 0; j < 8; j++) {
             uint32_t v = rd();
@@ -238,13 +243,16 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n) {
             a.width_common = rd(); a.width_after = rd(); a.log_qd = rd(); a.num_pv = rd(); a.num_exposed = rd();
             B2_REQUIRE(a.num_exposed == (a.width_after ? 1u : 0u) && a.width_after < (1u << 20), B2S_ERR_BAD_ARG,
                        "key: after-challenge shape");
-            if (a.log_qd > e->params.log_blowup) fail(B2S_ERR_CONSTRAINT_DEGREE, "key: quotient degree exceeds the engine's blowup");
+            if (a.log_qd > log_blowup) fail(B2S_ERR_CONSTRAINT_DEGREE, "key: quotient degree exceeds the engine's blowup");
             if (a.width_prep) {
                 for (int j = 0; j < 8; j++) a.prep_commit[j] = Fp::from_canonical(rd()).v;
                 a.prep_log_height = rd();
-                B2_REQUIRE(a.prep_log_height + e->params.log_blowup <= TWO_ADICITY, B2S_ERR_SHAPE, "key: preprocessed height");
+                B2_REQUIRE(a.prep_log_height + log_blowup <= TWO_ADICITY, B2S_ERR_SHAPE, "key: preprocessed height");
                 const size_t cnt = (size_t)a.width_prep << a.prep_log_height;
                 B2_REQUIRE(i + cnt <= n, B2S_ERR_BAD_ARG, "key blob truncated (preprocessed trace)");
+                if (host_only) {
+                    i += cnt;
+                } else {
                 B2_REQUIRE(b2s_matrix_upload(e, w + i, (uint64_t)1 << a.prep_log_height, a.width_prep, B2S_LAYOUT_ROW_MAJOR,
                                              B2S_REPR_CANONICAL, &a.prep_trace) == 0,
                            B2S_ERR_INTERNAL, std::string("key: preprocessed upload failed: ") + e->last_error);
@@ -255,6 +263,7 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n) {
                 root_monty(e, a.prep_pcs, root);
                 B2_REQUIRE(memcmp(root, a.prep_commit, 32) == 0, B2S_ERR_BAD_ARG,
                            "key: preprocessed commitment does not match the committed trace");
+                }
             }
             const uint32_t nn = rd();
             B2_REQUIRE((size_t)nn * 4 <= n - i, B2S_ERR_BAD_ARG, "key blob truncated (nodes)");
@@ -292,7 +301,7 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n) {
             for (auto& nd : nodes) a.nodes.push_back(make_uint4(nd.kind, nd.a, nd.b, nd.c));
             a.constraint_idx = cidx;
             auto up = [&](const std::vector<uint4>& prog) -> uint4* {
-                if (prog.empty()) return nullptr;
+                if (prog.empty() || host_only) return nullptr;
                 uint4* d = (uint4*)e->dmalloc(prog.size() * sizeof(uint4));
                 B2_CUDA(cudaMemcpyAsync(d, prog.data(), prog.size() * sizeof(uint4), cudaMemcpyHostToDevice, e->stream));
                 return d;
@@ -309,7 +318,42 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n) {
             }
         }
         B2_REQUIRE(i == n, B2S_ERR_BAD_ARG, "key blob: trailing words");
+        if (host_only) return pk;
         B2_CUDA(cudaStreamSynchronize(e->stream));
+        // quotient kernels: straight-line PTX per AIR, compiled by the driver on a few host threads (qjit.cu)
+        if (quotient_jit_enabled()) {
+            const auto t_jit = std::chrono::steady_clock::now();
+            std::vector<std::pair<size_t, size_t>> work;  // (air, module)
+            for (size_t k = 0; k < pk->airs.size(); k++) {
+                const size_t nm = quotient_jit_prepare(pk->airs[k]);
+                for (size_t m = 0; m < nm; m++) work.push_back({k, m});
+            }
+            const unsigned nthreads = (unsigned)std::min<size_t>(work.size(), std::max(1u, std::min(16u, std::thread::hardware_concurrency())));
+            std::vector<std::string> errors(work.size());
+            std::atomic<size_t> next{0};
+            std::vector<std::thread> pool;
+            const int device = e->device;
+            for (unsigned t = 0; t < nthreads; t++)
+                pool.emplace_back([&, device] {
+                    cudaSetDevice(device);
+                    for (size_t w; (w = next.fetch_add(1)) < work.size();) {
+                        try {
+                            quotient_jit_compile(pk->airs[work[w].first], work[w].second);
+                        } catch (const StatusError& se) {
+                            errors[w] = se.msg;
+                        } catch (const std::exception& ex) {
+                            errors[w] = ex.what();
+                        }
+                    }
+                });
+            for (auto& th : pool) th.join();
+            for (size_t w = 0; w < work.size(); w++)
+                if (!errors[w].empty()) fail(B2S_ERR_INTERNAL, "air " + std::to_string(work[w].first) + ": " + errors[w]);
+            for (auto& a : pk->airs) { a.jit_ptx.clear(); a.jit_ptx.shrink_to_fit(); }
+            if (getenv("B2S_PROVE_TRACE"))
+                fprintf(stderr, "[b2s trace] quotient JIT: %zu kernels on %u threads in %.1f ms\n", work.size(), nthreads,
+                        std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_jit).count());
+        }
     } catch (...) {
         pk_free(pk);
         throw;
@@ -1041,7 +1085,26 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
                 qp.inv_zh[j] = fp_inv(zh).v;
                 wpow *= wq;
             }
-            launch_quotient(e, k.num_slots, k.num_slots_e, qp);
+            if (!k.jit_kernels.empty()) {
+                // straight-line kernels generated from the DAG at key load (qjit.cu); same inputs, same output layout
+                const uint32_t* mats[16];
+                uint32_t nm = 0;
+                if (k.width_prep) mats[nm++] = k.prep_pcs->mats[0]->d;
+                for (uint32_t p = 0; p < airs[i].n_cached; p++) mats[nm++] = airs[i].cached[p]->mats[0]->d;
+                if (k.width_common) {
+                    size_t pos = std::find(common_of.begin(), common_of.end(), i) - common_of.begin();
+                    mats[nm++] = common_pcs->mats[pos]->d;
+                }
+                if (k.width_after) {
+                    size_t pos = std::find(after_of.begin(), after_of.end(), i) - after_of.begin();
+                    mats[nm++] = after_pcs->mats[pos]->d;
+                }
+                B2_REQUIRE(nm == k.jit_num_mats, B2S_ERR_INTERNAL, "quotient JIT: matrix count mismatch");
+                uint32_t* accbuf = k.jit_kernels.size() > 1 ? scratch.words((size_t)4 << (n + lq)) : nullptr;
+                quotient_jit_launch(e, k, mats, d_pv, d_apow, d_efc, accbuf, qp.out, n, lq);
+            } else {
+                launch_quotient(e, k.num_slots, k.num_slots_e, qp);
+            }
             Fp sh = Fp::raw(M_GENERATOR);
             for (uint32_t j = 0; j < (1u << lq); j++) {
                 b2s_matrix v;

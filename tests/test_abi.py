@@ -57,3 +57,40 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle_binding" not in src and "liboracle" not in src and "oracle/" not in src, f
+
+
+def test_quotient_ptx_assembles_for_sm_100a(tmp_path):
+    """The quotient kernels are generated as PTX from the constraint DAG at key load (qjit.cu). Host-only check: the
+    text for a few AIRs (base-field only, LogUp / extension field, preprocessed + cached partitions, a multi-kernel
+    split) assembles with ptxas for sm_100a."""
+    import ctypes as C
+    import shutil
+    import subprocess
+    import numpy as np
+    from openvm_b200 import _lib, airs as A
+    ptxas = shutil.which("ptxas") or "/usr/local/cuda/bin/ptxas"
+    if not os.path.exists(ptxas):
+        pytest.skip("no ptxas")
+    lib = _lib.load()
+    a_parts = A.lookup_chain_air_parts(6, 64, seed=2)
+    a_parts.prep_commit = np.arange(8, dtype=np.uint32)   # host-only parse: the commitment is not checked
+    cases = [[A.fibonacci_air()], [A.segment_air(8)], [a_parts, A.multi_receiver_air([2, 3], 5)], [A.segment_air(64)]]
+    os.environ["B2S_QUOTIENT_JIT_LINES"] = "3000"
+    try:
+        for air_list in cases:
+            key = A.key_blob(air_list, log_up_pow_bits=1)
+            for i in range(len(air_list)):
+                out = C.c_void_p()
+                assert lib.b2s_debug_quotient_ptx(key.ctypes.data, key.size, 1, i, C.byref(out)) == 0
+                text = C.string_at(out.value).decode()
+                lib.b2s_free(out)
+                mods = [m for m in text.split("// ---- next module\n") if m.strip()]
+                assert mods and all(".entry qk(" in m for m in mods)
+                for j, m in enumerate(mods):
+                    f = tmp_path / f"q{i}_{j}.ptx"
+                    f.write_text(m)
+                    r = subprocess.run([ptxas, "-arch=sm_100a", "-O1", str(f), "-o", str(f) + ".cubin"], capture_output=True, text=True)
+                    assert r.returncode == 0, r.stderr[:2000]
+        assert len(mods) > 1   # the last case is split into several kernels
+    finally:
+        del os.environ["B2S_QUOTIENT_JIT_LINES"]
