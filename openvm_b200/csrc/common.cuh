@@ -95,6 +95,7 @@ struct b2s_pcs_data {
     // digest layers, level 0 = leaves; each layer is 8 word-planes of n nodes: word w of node i at [w*n + i]
     std::vector<uint32_t*> layers;
     std::vector<uint64_t> layer_nodes;
+    std::vector<const uint32_t*> col_ptrs;  // host copy of the column pointer table (source of an asynchronous upload)
 };
 
 namespace b2 {

@@ -180,14 +180,15 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
     const uint32_t** d_ptrs = (const uint32_t**)e->dmalloc(total_cols * sizeof(void*));
     std::map<uint64_t, const uint32_t**> group_dev;
     {
-        std::vector<const uint32_t*> flat;
+        // the host table lives in the PcsData: no stream round trip is needed before it may go out of scope
+        std::vector<const uint32_t*>& flat = d->col_ptrs;
+        flat.clear();
         flat.reserve(total_cols);
         for (auto& g : groups) {
             group_dev[g.first] = d_ptrs + flat.size();
             flat.insert(flat.end(), g.second.begin(), g.second.end());
         }
         B2_CUDA(cudaMemcpyAsync(d_ptrs, flat.data(), total_cols * sizeof(void*), cudaMemcpyHostToDevice, e->stream));
-        B2_CUDA(cudaStreamSynchronize(e->stream));  // flat is a stack-lifetime buffer
     }
     // leaves
     d->layers.clear();
