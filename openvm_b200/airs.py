@@ -168,7 +168,7 @@ def fibonacci_trace(n, a=0, b=1):
     return t, np.array([t[0, 0], t[0, 1], t[n - 1, 1]], dtype=np.uint32)
 
 
-def chain_air(width, with_prep=False, cached_width=0, height=None, seed=0):
+def chain_air(width, with_prep=False, cached_width=0, height=None, seed=0, degree=3):
     """Columns x_0..x_{W-1} of the common main: x_{j+2} = x_j * x_{j+1} + x_j (degree 2), a degree-3 booleanity
     style constraint x_0 * (x_1 * x_2 - x_3 + x_0) = 0 ... kept satisfiable by construction: instead we use
     y := x_j * x_{j+1} * x_{j+2} - x_{j+3}' terms only on columns defined that way. Layout:
@@ -177,14 +177,20 @@ def chain_air(width, with_prep=False, cached_width=0, height=None, seed=0):
       transition: next.x_0 = local.x_0 + 1 ; first row: x_0 = pv_0 ; last row: x_1 = pv_1
       preprocessed (optional, width 2): p_0 = row index, p_1 = seed-derived; constraint x_1 = p_0 * p_1 + pv_0
       cached main (optional): k columns, each = x_0 + column index (degree 1)
+      degree 5 (quotient degree 4, needs log_blowup >= 2): the same traces, the last-column constraint multiplied by
+      x_3 * x_4 and a second one (x_2 - x_0 * x_1 - x_0) * x_1 * x_3 * x_4
     """
-    assert width >= 5
+    assert width >= 5 and degree in (3, 5)
     d = Dag()
     x = [d.main(j, 0, 1 if cached_width else 0) for j in range(width)]
     nx0 = d.main(0, 1, 1 if cached_width else 0)
     for j in range(width - 3):
         d.assert_zero(x[j + 2] - (x[j] * x[j + 1] + x[j]))
-    d.assert_zero(x[width - 1] - x[0] * x[1] * x[2])
+    if degree == 3:
+        d.assert_zero(x[width - 1] - x[0] * x[1] * x[2])
+    else:
+        d.assert_zero((x[width - 1] - x[0] * x[1] * x[2]) * x[3] * x[4])
+        d.assert_zero((x[2] - x[0] * x[1] - x[0]) * x[1] * x[3] * x[4])
     d.assert_zero(d.is_transition() * (nx0 - x[0] - 1))
     d.assert_zero(d.is_first() * (x[0] - d.public(0)))
     d.assert_zero(d.is_last() * (x[1] - d.public(1)))
@@ -199,7 +205,8 @@ def chain_air(width, with_prep=False, cached_width=0, height=None, seed=0):
         d.assert_zero(d.is_transition() * (d.prep(0, 1) - d.prep(0) - 1))
     for k in range(cached_width):
         d.assert_zero(d.main(k, 0, 0) - x[0] - k)
-    return Air(d, width_common=width, num_pv=2, log_qd=1, cached_widths=[cached_width] if cached_width else [], prep=prep)
+    return Air(d, width_common=width, num_pv=2, log_qd=1 if degree == 3 else 2,
+               cached_widths=[cached_width] if cached_width else [], prep=prep)
 
 
 def chain_trace(air, height, seed=0):
@@ -284,15 +291,16 @@ def lookup_chain_air_parts(width, height, seed=0, bus=5, cached_width=2):
     return a.finalize_logup(1)
 
 
-def multi_receiver_air(field_lens, bus0, max_chunk=1):
-    """columns [m_0, fields_0.., m_1, fields_1.., ...]: interaction i receives its fields with multiplicity m_i on
-    bus0 + i."""
+def multi_receiver_air(field_lens, bus0, max_chunk=1, is_send=False, log_qd=1):
+    """columns [m_0, fields_0.., m_1, fields_1.., ...]: interaction i receives (or sends) its fields with multiplicity
+    m_i on bus0 + i. `max_chunk` interactions share one reciprocal-sum column: constraint degree 1 + max_chunk, so
+    three per chunk need quotient degree 4 (log_qd 2)."""
     d = Dag()
     col = 0
-    a = Air(d, width_common=sum(field_lens) + len(field_lens), num_pv=0, log_qd=1)
+    a = Air(d, width_common=sum(field_lens) + len(field_lens), num_pv=0, log_qd=log_qd)
     for i, ln in enumerate(field_lens):
         m = d.main(col)
-        a.add_interaction(bus0 + i, [d.main(col + 1 + j) for j in range(ln)], m, False)
+        a.add_interaction(bus0 + i, [d.main(col + 1 + j) for j in range(ln)], m, is_send)
         col += 1 + ln
     return a.finalize_logup(max_chunk)
 

@@ -251,3 +251,55 @@ def test_pow_witness_override(orc):
         assert gpu_prove(eng, key, [(0, [trace], pvs)], [air]) == proof
     finally:
         eng.close()
+
+
+# ---- quotient degree 4 at log_blowup 2 / 3 (the leaf-aggregation configuration) ------------------------
+@pytest.mark.parametrize("b,n", [(2, 64), (2, 1 << 12), (3, 256)])
+def test_quotient_degree4_chain_bytes(orc, b, n):
+    a = airs.chain_air(8, degree=5)
+    key = build_key(orc, [a], b)
+    parts, pv = airs.chain_trace(a, n, seed=11)
+    eng = make_engine(b, 4, 3)
+    try:
+        check_same(orc, eng, key, [(0, parts, pv)], [a], b, 4, 3)
+        bad = [m.copy() for m in parts]
+        bad[-1][9, 7] = (int(bad[-1][9, 7]) + 1) % P
+        check_same(orc, eng, key, [(0, bad, pv)], [a], b, 4, 3, expect="OodEvaluationMismatch")
+    finally:
+        eng.close()
+
+
+def test_quotient_degree_exceeds_blowup_is_refused(orc):
+    from openvm_b200 import B2StarkError
+    a = airs.chain_air(8, degree=5)
+    key = build_key(orc, [a], 1)
+    eng = make_engine(1, 4, 3)
+    try:
+        with pytest.raises(B2StarkError):
+            eng.device().transport_pk_to_device(key)
+    finally:
+        eng.close()
+
+
+def test_mixed_quotient_degrees_with_logup_bytes(orc):
+    """one proof over AIRs of quotient degree 1, 2 and 4, two of them with three interactions per LogUp chunk"""
+    from test_oracle_stark import multi_bus_traces
+    b, queries, pow_bits = 2, 5, 4
+    lens = [2, 1, 3, 2]
+    air_objs = [airs.fibonacci_air(), airs.chain_air(7), airs.chain_air(9, degree=5),
+                airs.multi_receiver_air(lens, 7, max_chunk=3, is_send=True, log_qd=2),
+                airs.multi_receiver_air(lens, 7, max_chunk=3, is_send=False, log_qd=2)]
+    key = airs.key_blob(air_objs, log_up_pow_bits=4)
+    t0, pv0 = airs.fibonacci_trace(128)
+    p1, pv1 = airs.chain_trace(air_objs[1], 1 << 9, seed=1)
+    p2, pv2 = airs.chain_trace(air_objs[2], 1 << 7, seed=2)
+    s, r = multi_bus_traces(lens, 1 << 8, seed=5)
+    inputs = [(0, [t0], pv0), (1, p1, pv1), (2, p2, pv2), (3, [s], NONE), (4, [r], NONE)]
+    eng = make_engine(b, queries, pow_bits)
+    try:
+        check_same(orc, eng, key, inputs, air_objs, b, queries, pow_bits)
+        r2 = r.copy(); r2[17, 0] += 1
+        check_same(orc, eng, key, inputs[:4] + [(4, [r2], NONE)], air_objs, b, queries, pow_bits,
+                   expect="NonZeroCumulativeSum")
+    finally:
+        eng.close()

@@ -176,3 +176,55 @@ def test_logup_prep_cached_rotated_fields(orc, n, b):
     bad = recv.copy(); bad[3, 6] = (int(bad[3, 6]) + 1) % P
     p2 = orc.stark_prove(key, [(0, parts, pv), (1, [bad], none)], b, 4, 3)
     assert "NonZeroCumulativeSum" in orc.stark_verify(key, p2, b, 4, 3)
+
+
+# ---- quotient degree 4 (constraint degree 5; three interactions per LogUp chunk) -- the leaf-aggregation shape -----------
+def multi_bus_traces(field_lens, n, seed=0):
+    """rows [m_0, fields_0.., m_1, ...] for multi_receiver_air as a sender, and the same rows in reverse order for the
+    receiver: every bus balances."""
+    rng = np.random.default_rng(seed)
+    w = sum(field_lens) + len(field_lens)
+    t = rng.integers(0, 60, size=(n, w)).astype(np.uint32)
+    col = 0
+    for ln in field_lens:
+        t[:, col] = rng.integers(0, 3, size=n)
+        col += 1 + ln
+    return t, t[::-1].copy()
+
+
+@pytest.mark.parametrize("b", [2, 3])
+def test_quotient_degree4_chain(orc, b):
+    a = airs.chain_air(8, degree=5)
+    assert a.log_qd == 2
+    key = build_key(orc, [a], b)
+    parts, pv = airs.chain_trace(a, 64, seed=11)
+    proof = orc.stark_prove(key, [(0, parts, pv)], b, 4, 3)
+    assert orc.stark_verify(key, proof, b, 4, 3) is None
+    bad = [m.copy() for m in parts]
+    bad[-1][9, 7] = (int(bad[-1][9, 7]) + 1) % P
+    p2 = orc.stark_prove(key, [(0, bad, pv)], b, 4, 3)
+    assert "OodEvaluationMismatch" in orc.stark_verify(key, p2, b, 4, 3)
+
+
+def test_quotient_degree_exceeds_blowup_is_refused(orc):
+    a = airs.chain_air(8, degree=5)
+    key = build_key(orc, [a], 1)
+    parts, pv = airs.chain_trace(a, 64, seed=11)
+    with pytest.raises(Exception):
+        orc.stark_prove(key, [(0, parts, pv)], 1, 4, 3)
+
+
+def test_logup_three_per_chunk_quotient_degree4(orc):
+    b = 2
+    lens = [2, 1, 3, 2]
+    snd = airs.multi_receiver_air(lens, 7, max_chunk=3, is_send=True, log_qd=2)
+    rcv = airs.multi_receiver_air(lens, 7, max_chunk=3, is_send=False, log_qd=2)
+    assert [len(c) for c in snd.chunks] == [3, 1]
+    key = airs.key_blob([snd, rcv], log_up_pow_bits=4)
+    s, r = multi_bus_traces(lens, 128, seed=5)
+    none = np.zeros(0, dtype=np.uint32)
+    proof = orc.stark_prove(key, [(0, [s], none), (1, [r], none)], b, 4, 3)
+    assert orc.stark_verify(key, proof, b, 4, 3) is None
+    r2 = r.copy(); r2[17, 0] += 1          # one more copy of a message than was sent
+    p2 = orc.stark_prove(key, [(0, [s], none), (1, [r2], none)], b, 4, 3)
+    assert "NonZeroCumulativeSum" in orc.stark_verify(key, p2, b, 4, 3)
