@@ -280,6 +280,14 @@ def segment_shapes(scale_log=0):
     return [(max(4, h + scale_log), w) for h, w in base]
 
 
+def leaf_shapes(scale_log=0):
+    """Shape replay of a leaf-aggregation proof (15 AIRs, heights up to 2^22, ~446 M main cells,
+    quotient degree up to 4, log_blowup 2): (log_height, main width, constraint degree) per AIR."""
+    base = [(22, 34, 3), (21, 48, 5), (21, 24, 3), (20, 48, 3), (20, 30, 5), (19, 40, 3), (19, 28, 3), (18, 36, 5),
+            (18, 20, 3), (17, 66, 3), (16, 200, 3), (15, 32, 3), (14, 16, 3), (12, 8, 3), (10, 8, 3)]
+    return [(max(4, h + scale_log), w, dg) for h, w, dg in base]
+
+
 def lookup_chain_air_parts(width, height, seed=0, bus=5, cached_width=2):
     """chain_air with a preprocessed trace and a cached partition whose interactions read every kind of column:
     send (x_0, x_1) once per row on `bus`; send (cached_0, prep_0, next x_0) with multiplicity prep_0 (the row index)
@@ -320,12 +328,12 @@ def lookup_chain_parts_receiver_trace(air, parts):
     return t[::-1].copy()
 
 
-def segment_air(width):
+def segment_air(width, degree=3):
     """One chip of the shape-replay segment: chain_air plus LogUp traffic shaped like an OpenVM chip's (BaseAlu:
     36 main columns and 20 extension-field permutation columns in crates/prof/data/metrics.example.json). Chunk c holds
     two interactions on bus c: send (x_j, x_{j+1}) of this row and receive the same pair of the NEXT row, so the bus
     balances over the cyclic trace while every row's reciprocal sum is non-trivial. Degree 3 -> quotient degree 2."""
-    a = chain_air(width)
+    a = chain_air(width, degree=degree)
     d = a.dag
     k = max(1, width // 2) if width <= 100 else width // 10
     for c in range(k):

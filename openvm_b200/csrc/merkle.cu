@@ -10,7 +10,7 @@
 //                     (coalesced: adjacent threads read adjacent rows of the same column), optionally fused with
 //                     the compress-and-inject step of the level the group joins the tree at; or a plain 2-to-1
 //                     compression of the previous digest layer
-//   tree_tail_kernel  all levels of <= 256 nodes in one launch
+//   tree_level_coop_kernel / tree_subtree_kernel  small levels, four lanes per permutation; up to nine levels per launch
 // Digest layers are stored as 8 word-planes (word w of node i at [w*n + i]) so both kernels read and
 // write fully coalesced.
 #include "common.cuh"
@@ -86,27 +86,138 @@ __global__ void __launch_bounds__(HASH_THREADS, HASH_MIN_BLOCKS)
     hash_node(cols, ncols, n, prev, out, mode, i);
 }
 
-// The top of the tree (levels of <= TAIL_NODES nodes) in one launch: one block walks the levels with a block
-// barrier in between, instead of one ~3 us launch per level.
-constexpr int TAIL_THREADS = 256;
-constexpr int TAIL_MAX_LEVELS = 12;
-struct TailParams {
-    const uint32_t* const* cols[TAIL_MAX_LEVELS];
-    uint32_t ncols[TAIL_MAX_LEVELS];
-    uint32_t* out[TAIL_MAX_LEVELS];
+// ---- four lanes per permutation --------------------------------------------------------------------------------------
+// Small levels (the top of every tree, every level of the FRI commit-phase trees) are bound by the LATENCY of one
+// permutation chain per thread (~8 us: 5.7 k dependent-ish instructions), not by throughput. Here four adjacent lanes
+// share one state, lane `sub` holding words 4*sub .. 4*sub+3: the S-box layer and the 4x4 blocks of the external layer
+// stay lane-local, the column sums of the external layer and the row sum of the internal layer are two xor-shuffles
+// each, the internal diagonal is one Montgomery product per word with per-lane constants. ~2 us per permutation.
+static __device__ uint32_t P2G_EXT[8][16] = B2_P2_EXT_ALL;
+static __device__ uint32_t P2G_DIAG[16] = B2_P2_DIAG;
+constexpr unsigned FULL_MASK = 0xFFFFFFFFu;
+
+B2_D Fp quad_sum(Fp v) {
+    v = v + Fp::raw(__shfl_xor_sync(FULL_MASK, v.v, 1));
+    return v + Fp::raw(__shfl_xor_sync(FULL_MASK, v.v, 2));
+}
+B2_D void poseidon2_permute4(Fp (&s)[4], const Fp (&diag)[4], uint32_t sub) {
+#pragma unroll 1
+    for (int r = 0; r < 9; r++) {
+        uint4 rc = make_uint4(0, 0, 0, 0);
+        if (r < 8) rc = __ldg(reinterpret_cast<const uint4*>(&P2G_EXT[r][4 * sub]));
+        mat4(s[0], s[1], s[2], s[3]);
+#pragma unroll
+        for (int k = 0; k < 4; k++) s[k] += quad_sum(s[k]);
+        if (r == 4) {
+#pragma unroll 1
+            for (int q = 0; q < 13; q++) {
+                const Fp x0 = sbox7_rc(s[0], P2C_PARTIAL[q]);
+                if (sub == 0) s[0] = x0;
+                const Fp sum = quad_sum((s[0] + s[1]) + (s[2] + s[3]));
+#pragma unroll
+                for (int k = 0; k < 4; k++) s[k] = s[k] * diag[k] + sum;
+            }
+        }
+        if (r < 8) {
+            s[0] = sbox7_rc(s[0], rc.x);
+            s[1] = sbox7_rc(s[1], rc.y);
+            s[2] = sbox7_rc(s[2], rc.z);
+            s[3] = sbox7_rc(s[3], rc.w);
+        }
+    }
+}
+// hash_node with four lanes per node; every lane of the warp must call it (idle quads pass store = false and a valid i)
+B2_D void hash_node4(const uint32_t* const* __restrict__ cols, uint32_t ncols, uint64_t n, const uint32_t* prev,
+                     uint32_t* out, int mode, uint64_t i, uint32_t sub, bool store) {
+    Fp s[4], keep[4], diag[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        s[k] = Fp::zero();
+        keep[k] = Fp::zero();
+        diag[k] = Fp::raw(P2G_DIAG[4 * sub + k]);
+    }
+    const uint32_t chunks = (ncols + 7) >> 3;
+    const uint32_t total = chunks + (mode == 0 ? 0u : (mode == 1 ? 2u : 1u));
+    const unsigned lane = threadIdx.x & 31u;
+#pragma unroll 1
+    for (uint32_t it = 0; it < total; it++) {
+        if (it < chunks) {
+            const uint32_t c = (it << 3) + 4 * sub;
+            if (sub < 2) {
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    if (c + k < ncols) s[k] = Fp::raw(__ldg(cols[c + k] + i));
+            }
+        } else if (it == chunks && mode != 0) {
+            const uint64_t np = 2 * n, node = 2 * i + (sub >> 1);
+            const uint32_t w0 = 4 * (sub & 1);
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                keep[k] = s[k];
+                s[k] = Fp::raw(__ldcg(prev + (uint64_t)(w0 + k) * np + node));
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const uint32_t v = __shfl_sync(FULL_MASK, keep[k].v, sub >= 2 ? lane - 2 : lane);
+                if (sub >= 2) s[k] = Fp::raw(v);
+            }
+        }
+        poseidon2_permute4(s, diag, sub);
+    }
+    if (store && sub < 2) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) out[(uint64_t)(4 * sub + k) * n + i] = s[k].v;
+    }
+}
+
+// one level of at most COOP_MAX_NODES nodes, four lanes per node (same modes as tree_level_kernel). Above ~2^13 nodes
+// the machine is full and the one-node-per-thread kernel wins (the four-lane form spends ~1.5 x the multiplies: every
+// lane runs the partial-round S-box and the diagonal is a generic product).
+constexpr uint64_t COOP_MAX_NODES = 1u << 13;
+constexpr int COOP_THREADS = 256;
+__global__ void __launch_bounds__(COOP_THREADS)
+    tree_level_coop_kernel(const uint32_t* const* __restrict__ cols, uint32_t ncols, uint64_t n,
+                           const uint32_t* __restrict__ prev, uint32_t* __restrict__ out, int mode) {
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t i = t >> 2;
+    hash_node4(cols, ncols, n, prev, out, mode, i < n ? i : n - 1, (uint32_t)(t & 3), i < n);
+}
+
+// Several consecutive levels in one launch: block b owns the sub-tree over nodes [b*W, (b+1)*W) of the first level
+// (W = min(n0, SUBTREE_NODES)) and walks it up to its single top node with a block barrier per level, four lanes per
+// node, instead of one launch (and one ~8 us latency-bound permutation wave) per level. With one block it is the top of
+// the tree; with n0 / W blocks it takes log2(W) + 1 levels off a mid-sized tree.
+constexpr int SUBTREE_NODES = 256;
+constexpr int SUBTREE_THREADS = 4 * SUBTREE_NODES;
+constexpr int SUBTREE_MAX_LEVELS = 9;
+constexpr uint64_t SUBTREE_MAX_FIRST = 1u << 14;  // one wave of blocks; above this the levels run one launch each
+struct SubtreeParams {
+    const uint32_t* const* cols[SUBTREE_MAX_LEVELS];
+    uint32_t ncols[SUBTREE_MAX_LEVELS];
+    uint32_t* out[SUBTREE_MAX_LEVELS];
     const uint32_t* prev0;
     uint64_t n0;        // nodes of the first level handled here
+    uint32_t w0;        // nodes of the first level per block
     uint32_t levels;
 };
-__global__ void __launch_bounds__(TAIL_THREADS, 1) tree_tail_kernel(TailParams p) {
+__global__ void __launch_bounds__(SUBTREE_THREADS, 1) tree_subtree_kernel(SubtreeParams p) {
     const uint32_t* prev = p.prev0;
     uint64_t n = p.n0;
+    uint32_t w = p.w0;
+    const uint32_t local = threadIdx.x >> 2, sub = threadIdx.x & 3;
 #pragma unroll 1
     for (uint32_t l = 0; l < p.levels; l++) {
-        if (threadIdx.x < n) hash_node(p.cols[l], p.ncols[l], n, prev, p.out[l], p.ncols[l] ? 1 : 2, threadIdx.x);
+        // whole warps drop out together (8 nodes per warp): the shuffles stay converged
+        if ((threadIdx.x >> 5) * 8 < w) {
+            const bool valid = local < w;
+            const uint64_t i = (uint64_t)blockIdx.x * w + (valid ? local : w - 1);
+            hash_node4(p.cols[l], p.ncols[l], n, prev, p.out[l], p.ncols[l] ? 1 : 2, i, sub, valid);
+        }
         __syncthreads();
         prev = p.out[l];
         n >>= 1;
+        w >>= 1;
     }
 }
 
@@ -160,6 +271,15 @@ void leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_t n
     e->permutations += n * ((ncols + 7) / 8);
 }
 
+// one tree level: throughput kernel (one node per thread) for big levels, latency kernel (four lanes per node) below
+static void launch_level(b2s_engine* e, const uint32_t* const* cols, uint32_t ncols, uint64_t n, const uint32_t* prev,
+                         uint32_t* out, int mode) {
+    if (n <= COOP_MAX_NODES)
+        tree_level_coop_kernel<<<grid_for(4 * n, COOP_THREADS), COOP_THREADS, 0, e->stream>>>(cols, ncols, n, prev, out, mode);
+    else
+        tree_level_kernel<<<grid_for(n, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(cols, ncols, n, prev, out, mode);
+}
+
 // Build the tree of d->mats (any heights). Fills d->layers. `leaf_layer` (optional): digest planes of the tallest height
 // group, already computed by the streaming sponge; the tree takes ownership of it.
 void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
@@ -200,8 +320,7 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
         StageScope sc(e, ST_LEAF);
         uint32_t* leaf = (uint32_t*)e->dmalloc(hmax * 32);
         uint32_t nc = (uint32_t)groups[hmax].size();
-        tree_level_kernel<<<grid_for(hmax, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(group_dev[hmax], nc, hmax,
-                                                                                          nullptr, leaf, 0);
+        launch_level(e, group_dev[hmax], nc, hmax, nullptr, leaf, 0);
         B2_CHECK_LAUNCH();
         e->launches[1]++;
         e->permutations += hmax * ((nc + 7) / 8);
@@ -211,15 +330,16 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
     uint64_t h = hmax;
     while (h > 1) {
         uint64_t nh = h / 2;
-        if (nh <= TAIL_THREADS) {
-            // all remaining levels in one launch
+        if (nh <= SUBTREE_MAX_FIRST) {
+            // log2(W) + 1 levels in one launch (all remaining ones when nh <= SUBTREE_NODES)
             StageScope sc(e, ST_COMPRESS);
-            TailParams tp{};
+            SubtreeParams tp{};
             tp.prev0 = d->layers.back();
             tp.n0 = nh;
+            tp.w0 = (uint32_t)std::min<uint64_t>(nh, SUBTREE_NODES);
             uint32_t l = 0;
-            for (uint64_t m = nh; m >= 1; m >>= 1, l++) {
-                B2_REQUIRE(l < TAIL_MAX_LEVELS, B2S_ERR_INTERNAL, "mmcs: tail too deep");
+            uint64_t m = nh;
+            for (uint32_t w = tp.w0; w >= 1; w >>= 1, m >>= 1, l++) {
                 auto it = groups.find(m);
                 tp.cols[l] = it != groups.end() ? group_dev[m] : nullptr;
                 tp.ncols[l] = it != groups.end() ? (uint32_t)it->second.size() : 0u;
@@ -227,28 +347,26 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
                 d->layers.push_back(tp.out[l]);
                 d->layer_nodes.push_back(m);
                 e->permutations += m * (tp.ncols[l] ? (tp.ncols[l] + 7) / 8 + 2 : 1);
-                if (m == 1) { l++; break; }
             }
             tp.levels = l;
-            tree_tail_kernel<<<1, TAIL_THREADS, 0, e->stream>>>(tp);
+            tree_subtree_kernel<<<(unsigned)(nh / tp.w0), SUBTREE_THREADS, 0, e->stream>>>(tp);
             B2_CHECK_LAUNCH();
             e->launches[2]++;
-            break;
+            h = nh / tp.w0;   // nodes of the last level written
+            continue;
         }
         uint32_t* next = (uint32_t*)e->dmalloc(nh * 32);
         auto it = groups.find(nh);
         if (it != groups.end()) {
             StageScope sc(e, ST_LEAF);
             uint32_t nc = (uint32_t)it->second.size();
-            tree_level_kernel<<<grid_for(nh, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(group_dev[nh], nc, nh,
-                                                                                            d->layers.back(), next, 1);
+            launch_level(e, group_dev[nh], nc, nh, d->layers.back(), next, 1);
             B2_CHECK_LAUNCH();
             e->launches[1]++;
             e->permutations += nh * ((nc + 7) / 8 + 2);
         } else {
             StageScope sc(e, ST_COMPRESS);
-            tree_level_kernel<<<grid_for(nh, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(nullptr, 0, nh,
-                                                                                            d->layers.back(), next, 2);
+            launch_level(e, nullptr, 0, nh, d->layers.back(), next, 2);
             B2_CHECK_LAUNCH();
             e->launches[2]++;
             e->permutations += nh;

@@ -835,8 +835,9 @@ static Fp grind_device(b2s_engine* e, Scratch& scratch, HostChallenger& ch, unsi
     pp.in_ptr = (uint32_t)ch.in_ptr;
     pp.bits = bits;
     uint32_t found = 0xFFFFFFFFu;
-    const uint32_t batch = 1u << 20;
-    for (uint64_t base = 0; base < P && found == 0xFFFFFFFFu; base += batch) {
+    // first batch: 4 x the expected witness (found with probability 1 - e^-4); later batches double
+    uint32_t batch = std::min(1u << 22, std::max(1u << 14, 4u << bits));
+    for (uint64_t base = 0; base < P && found == 0xFFFFFFFFu; base += batch, batch = std::min(1u << 22, batch * 2)) {
         pp.base = (uint32_t)base;
         B2_CUDA(cudaMemsetAsync(d_res, 0xFF, 4, e->stream));
         pow_grind_kernel<<<batch / 128, 128, 0, e->stream>>>(pp, batch, d_res);
@@ -856,10 +857,13 @@ static Fp grind_device(b2s_engine* e, Scratch& scratch, HostChallenger& ch, unsi
 struct HostTrace {
     b2s_engine* e;
     bool on;
+    int level;   // B2S_PROVE_TRACE=2 adds marks inside the FRI commit phase
     std::chrono::steady_clock::time_point t0, last;
-    explicit HostTrace(b2s_engine* e_) : e(e_), on(getenv("B2S_PROVE_TRACE") != nullptr) { t0 = last = std::chrono::steady_clock::now(); }
-    void mark(const char* what) {
-        if (!on) return;
+    explicit HostTrace(b2s_engine* e_) : e(e_), on(getenv("B2S_PROVE_TRACE") != nullptr), level(on ? atoi(getenv("B2S_PROVE_TRACE")) : 0) {
+        t0 = last = std::chrono::steady_clock::now();
+    }
+    void mark(const char* what, int min_level = 1) {
+        if (!on || level < min_level) return;
         auto a = std::chrono::steady_clock::now();
         cudaStreamSynchronize(e->stream);
         auto b = std::chrono::steady_clock::now();
@@ -1279,9 +1283,11 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
         t->owns.push_back(true);
         scratch.pcs.push_back(t);
         mmcs_build(e, t);
+        trace.mark("  fri layer: tree enqueued", 2);
         fri_trees.push_back(t);
         std::array<uint32_t, 8> root;
         root_monty(e, t, root.data());
+        trace.mark("  fri layer: root on host", 2);
         fri_commits.push_back(root);
         ch.observe_digest(root.data());
         const Fp4 beta = ch.sample_ext();
@@ -1292,6 +1298,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
         B2_CHECK_LAUNCH();
         e->launches[3]++;
         folded = next;
+        trace.mark("  fri layer: fold", 2);
     }
     trace.mark("fri commit phase");
     // final polynomial: log_final_poly_len = 0, the constant (two_adic_pcs.rs:52-58)

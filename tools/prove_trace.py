@@ -1,6 +1,6 @@
 """Host/device timeline of one shape-replay segment proof (B2S_PROVE_TRACE marks from prover.cu)."""
 import os, sys, time
-os.environ["B2S_PROVE_TRACE"] = "1"
+os.environ.setdefault("B2S_PROVE_TRACE", "1")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from openvm_b200 import B2Engine, FriParameters, AirProvingContext, airs as A
 
