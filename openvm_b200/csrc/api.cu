@@ -265,6 +265,7 @@ void b2s_engine_free(b2s_engine* e) {
         e->collect_timers();
         free_twiddles(e);
         free_scales(e);
+        if (e->tile_ctr) e->dfree(e->tile_ctr, 256);
         free_selectors(e);
     } catch (...) {
     }

@@ -70,6 +70,7 @@ struct b2s_engine {
     uint32_t pow_override[2] = {0xFFFFFFFFu, 0xFFFFFFFFu};  // [logup, fri]; 0xFFFFFFFF = search for the minimum witness
     std::map<unsigned, b2::TwiddleSet*> twiddles;  // by log size
     std::map<uint64_t, b2::ScaleSet*> scales;      // by (logn, log_blowup, shift_in)
+    unsigned* tile_ctr = nullptr;                  // work counter of the persistent leaf-hash kernel (merkle.cu)
 
     void* dmalloc(size_t bytes);
     void dfree(void* p, size_t bytes);

@@ -14,7 +14,7 @@
 // Digest layers are stored as 8 word-planes (word w of node i at [w*n + i]) so both kernels read and
 // write fully coalesced.
 #include "common.cuh"
-#include "poseidon2.cuh"
+#include "poseidon2_f64.cuh"
 
 namespace b2 {
 
@@ -259,13 +259,152 @@ __global__ void __launch_bounds__(HASH_THREADS, HASH_MIN_BLOCKS)
     }
 }
 
+// ---- integer and FP64 pipes side by side ---------------------------------------------------------------------------
+// Tall leaf levels (the bulk of every commit) run as a persistent kernel whose warps take tiles of 32 adjacent rows from
+// an atomic counter. MIX_INT_WARPS of the 8 warps of a block hash their rows with the integer permutation, the others
+// with the FP64 one (poseidon2_f64.cuh): the fmaheavy pipe (IMAD) and the FP64 pipe (DFMA) work at the same time, and a
+// tile's digest words do not depend on which code path produced them (both are exact arithmetic mod p). Which tile goes
+// to which path is decided by whoever is free, so the faster path simply takes more tiles.
+constexpr int MIX_THREADS = 256;
+constexpr int MIX_INT_WARPS = 4;
+constexpr uint64_t MIX_MIN_ROWS = 1u << 14;
+
+struct ColTable {     // columns through a pointer table (any mix of matrices of one height)
+    const uint32_t* const* cols;
+    B2_D uint32_t ld(uint32_t c, uint64_t i) const { return __ldg(cols[c] + i); }
+};
+struct ColStrided {   // columns of one matrix
+    const uint32_t* base;
+    uint64_t stride;
+    B2_D uint32_t ld(uint32_t c, uint64_t i) const { return __ldg(base + (uint64_t)c * stride + i); }
+};
+
+// sponge over columns [0, ncols) of row i. state_in: 16 word-planes to resume from (or null: zero state);
+// state_out: 16 word-planes to suspend to (or null: write the 8 digest planes to out)
+template <class Cols>
+B2_D void sponge_row_int(const Cols& src, uint32_t ncols, uint64_t n, uint64_t i, const uint32_t* state_in,
+                         uint32_t* state_out, uint32_t* out) {
+    Fp s[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) s[k] = state_in ? Fp::raw(state_in[(uint64_t)k * n + i]) : Fp::zero();
+    const uint32_t chunks = (ncols + 7) >> 3;
+    uint32_t nxt[8];
+    auto fetch = [&](uint32_t chunk) {
+        const uint32_t c = chunk << 3;
+#pragma unroll
+        for (int k = 0; k < 8; k++) nxt[k] = (c + k < ncols) ? src.ld(c + k, i) : 0u;
+    };
+    if (chunks) fetch(0);
+#pragma unroll 1
+    for (uint32_t it = 0; it < chunks; it++) {
+        const uint32_t c = it << 3;
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+            if (c + k < ncols) s[k] = Fp::raw(nxt[k]);
+        if (it + 1 < chunks) fetch(it + 1);
+        poseidon2_permute(s);
+    }
+    if (state_out) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) state_out[(uint64_t)k * n + i] = s[k].v;
+    } else {
+#pragma unroll
+        for (int w = 0; w < 8; w++) out[(uint64_t)w * n + i] = s[w].v;
+    }
+}
+template <class Cols>
+B2_D void sponge_row_f64(const Cols& src, uint32_t ncols, uint64_t n, uint64_t i, const uint32_t* state_in,
+                         uint32_t* state_out, uint32_t* out) {
+    double s[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) s[k] = state_in ? f64_from_monty(state_in[(uint64_t)k * n + i]) : 0.0;
+    const uint32_t chunks = (ncols + 7) >> 3;
+    uint32_t nxt[8];
+    auto fetch = [&](uint32_t chunk) {
+        const uint32_t c = chunk << 3;
+#pragma unroll
+        for (int k = 0; k < 8; k++) nxt[k] = (c + k < ncols) ? src.ld(c + k, i) : 0u;
+    };
+    if (chunks) fetch(0);
+#pragma unroll 1
+    for (uint32_t it = 0; it < chunks; it++) {
+        const uint32_t c = it << 3;
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+            if (c + k < ncols) s[k] = f64_from_monty(nxt[k]);
+        if (it + 1 < chunks) fetch(it + 1);
+        poseidon2_permute_f64(s);   // words stay within 17.5 p between permutations, no reduction needed
+    }
+    if (state_out) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) state_out[(uint64_t)k * n + i] = f64_to_monty(s[k]);
+    } else {
+#pragma unroll
+        for (int w = 0; w < 8; w++) out[(uint64_t)w * n + i] = f64_to_monty(s[w]);
+    }
+}
+// n is a multiple of 32 (power of two >= MIX_MIN_ROWS). ctr: one word, zeroed on the stream before the launch.
+// 3 blocks of 8 warps per SM (80 registers): measured against 4 x 8 warps at 64 registers, 8 x 4 warps, and an
+// all-integer plus an all-FP64 kernel side by side on two streams -- all end on the same plateau (236-239 ms for the
+// 2^25 x 256 leaf level, 259 ms integer only), which is the issue rate of the two code paths together, not a pipe.
+template <class Cols>
+__global__ void __launch_bounds__(MIX_THREADS, 3) leaf_mixed_kernel(Cols src, uint32_t ncols, uint64_t n, const uint32_t* state_in,
+                                                                    uint32_t* state_out, uint32_t* out, unsigned* ctr, int int_warps) {
+    const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned tiles = (unsigned)(n >> 5);
+    const bool int_path = (int)warp < int_warps;
+    for (;;) {
+        unsigned t = 0;
+        if (lane == 0) t = atomicAdd(ctr, 1u);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t >= tiles) break;
+        const uint64_t i = ((uint64_t)t << 5) + lane;
+        if (int_path) sponge_row_int(src, ncols, n, i, state_in, state_out, out);
+        else sponge_row_f64(src, ncols, n, i, state_in, state_out, out);
+    }
+}
+
+// B2S_HASH_F64: number of the 8 warps per block left on the integer path (default MIX_INT_WARPS; 8 = all integer
+// through the persistent kernel; "off" = the one-row-per-thread integer kernels)
+static int mixed_int_warps() {
+    static int v = [] {
+        const char* env = getenv("B2S_HASH_F64");
+        if (!env) return MIX_INT_WARPS;
+        if (!strcmp(env, "off")) return -1;
+        const int k = atoi(env);
+        return k < 0 ? 0 : (k > 8 ? 8 : k);
+    }();
+    return v;
+}
+template <class Cols>
+static void launch_mixed(b2s_engine* e, Cols src, uint32_t ncols, uint64_t n, const uint32_t* state_in, uint32_t* state_out,
+                         uint32_t* out) {
+    static int blocks_per_sm = 0, sms = 0;
+    if (!blocks_per_sm) {
+        B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, leaf_mixed_kernel<Cols>, MIX_THREADS, 0));
+        int dev = 0;
+        B2_CUDA(cudaGetDevice(&dev));
+        B2_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        if (blocks_per_sm < 1) blocks_per_sm = 1;
+    }
+    if (!e->tile_ctr) e->tile_ctr = (unsigned*)e->dmalloc(256);
+    B2_CUDA(cudaMemsetAsync(e->tile_ctr, 0, 4, e->stream));
+    const uint64_t want = (n >> 5) / (MIX_THREADS / 32) + 1;  // no more blocks than tiles / warps
+    const unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)sms * blocks_per_sm, want);
+    leaf_mixed_kernel<Cols><<<grid, MIX_THREADS, 0, e->stream>>>(src, ncols, n, state_in, state_out, out, e->tile_ctr,
+                                                                 mixed_int_warps());
+}
+
 static inline unsigned grid_for(uint64_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
 
 void leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_t n, uint32_t* state, uint32_t* out, bool first,
                  bool last) {
     StageScope sc(e, ST_LEAF);
-    leaf_absorb_kernel<<<grid_for(n, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(base, ncols, n, state, out, first ? 1 : 0,
-                                                                                   last ? 1 : 0);
+    if (n >= MIX_MIN_ROWS && mixed_int_warps() >= 0)
+        launch_mixed(e, ColStrided{base, n}, ncols, n, first ? nullptr : state, last ? nullptr : state, out);
+    else
+        leaf_absorb_kernel<<<grid_for(n, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(base, ncols, n, state, out, first ? 1 : 0,
+                                                                                       last ? 1 : 0);
     B2_CHECK_LAUNCH();
     e->launches[1]++;
     e->permutations += n * ((ncols + 7) / 8);
@@ -274,7 +413,9 @@ void leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_t n
 // one tree level: throughput kernel (one node per thread) for big levels, latency kernel (four lanes per node) below
 static void launch_level(b2s_engine* e, const uint32_t* const* cols, uint32_t ncols, uint64_t n, const uint32_t* prev,
                          uint32_t* out, int mode) {
-    if (n <= COOP_MAX_NODES)
+    if (mode == 0 && n >= MIX_MIN_ROWS && mixed_int_warps() >= 0)
+        launch_mixed(e, ColTable{cols}, ncols, n, nullptr, nullptr, out);
+    else if (n <= COOP_MAX_NODES)
         tree_level_coop_kernel<<<grid_for(4 * n, COOP_THREADS), COOP_THREADS, 0, e->stream>>>(cols, ncols, n, prev, out, mode);
     else
         tree_level_kernel<<<grid_for(n, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(cols, ncols, n, prev, out, mode);
