@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(HASH_THREADS, HASH_MIN_BLOCKS)
 // to which path is decided by whoever is free, so the faster path simply takes more tiles.
 constexpr int MIX_THREADS = 256;
 constexpr int MIX_INT_WARPS = 4;
-constexpr uint64_t MIX_MIN_ROWS = 1u << 14;
+constexpr uint64_t MIX_MIN_ROWS = 1u << 19;  // >= 4 tiles per resident warp; below, a level is bound by the slower (FP64) path's latency
 
 struct ColTable {     // columns through a pointer table (any mix of matrices of one height)
     const uint32_t* const* cols;
@@ -281,14 +281,22 @@ struct ColStrided {   // columns of one matrix
 
 // sponge over columns [0, ncols) of row i. state_in: 16 word-planes to resume from (or null: zero state);
 // state_out: 16 word-planes to suspend to (or null: write the 8 digest planes to out)
-template <class Cols>
+// One node: sponge over columns [0, ncols) of row i, then (PREV) the compressions that join the level below:
+//   node = compress(compress(prev[2i], prev[2i+1]), rowhash)   or, with ncols == 0, the inner compression alone.
+// state_in: 16 word-planes to resume from (or null: zero state); state_out: 16 word-planes to suspend to (or null: write
+// the 8 digest planes to out). As in hash_node, every permutation of a node runs through ONE call site inside a rolled
+// loop: with three call sites per code path the kernel's ~60 KB of permutation bodies miss the instruction cache
+// (measured: the leaf-aggregation shape's leaf stage 210 -> 237 ms).
+template <bool PREV, class Cols>
 B2_D void sponge_row_int(const Cols& src, uint32_t ncols, uint64_t n, uint64_t i, const uint32_t* state_in,
-                         uint32_t* state_out, uint32_t* out) {
+                         uint32_t* state_out, uint32_t* out, const uint32_t* prev) {
     Fp s[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) s[k] = state_in ? Fp::raw(state_in[(uint64_t)k * n + i]) : Fp::zero();
     const uint32_t chunks = (ncols + 7) >> 3;
+    const uint32_t total = chunks + (PREV ? (ncols ? 2u : 1u) : 0u);
     uint32_t nxt[8];
+    Fp keep[PREV ? 8 : 1];
     auto fetch = [&](uint32_t chunk) {
         const uint32_t c = chunk << 3;
 #pragma unroll
@@ -296,12 +304,26 @@ B2_D void sponge_row_int(const Cols& src, uint32_t ncols, uint64_t n, uint64_t i
     };
     if (chunks) fetch(0);
 #pragma unroll 1
-    for (uint32_t it = 0; it < chunks; it++) {
-        const uint32_t c = it << 3;
+    for (uint32_t it = 0; it < total; it++) {
+        if (!PREV || it < chunks) {
+            const uint32_t c = it << 3;
 #pragma unroll
-        for (int k = 0; k < 8; k++)
-            if (c + k < ncols) s[k] = Fp::raw(nxt[k]);
-        if (it + 1 < chunks) fetch(it + 1);
+            for (int k = 0; k < 8; k++)
+                if (c + k < ncols) s[k] = Fp::raw(nxt[k]);
+            if (it + 1 < chunks) fetch(it + 1);
+        } else if (it == chunks) {
+            const uint64_t np = 2 * n;
+#pragma unroll
+            for (int w = 0; w < 8; w++) {
+                keep[w] = s[w];
+                const uint2 lr = __ldcg(reinterpret_cast<const uint2*>(prev + (uint64_t)w * np + 2 * i));
+                s[w] = Fp::raw(lr.x);
+                s[8 + w] = Fp::raw(lr.y);
+            }
+        } else {
+#pragma unroll
+            for (int w = 0; w < 8; w++) s[8 + w] = keep[w];
+        }
         poseidon2_permute(s);
     }
     if (state_out) {
@@ -312,14 +334,16 @@ B2_D void sponge_row_int(const Cols& src, uint32_t ncols, uint64_t n, uint64_t i
         for (int w = 0; w < 8; w++) out[(uint64_t)w * n + i] = s[w].v;
     }
 }
-template <class Cols>
+template <bool PREV, class Cols>
 B2_D void sponge_row_f64(const Cols& src, uint32_t ncols, uint64_t n, uint64_t i, const uint32_t* state_in,
-                         uint32_t* state_out, uint32_t* out) {
+                         uint32_t* state_out, uint32_t* out, const uint32_t* prev) {
     double s[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) s[k] = state_in ? f64_from_monty(state_in[(uint64_t)k * n + i]) : 0.0;
     const uint32_t chunks = (ncols + 7) >> 3;
+    const uint32_t total = chunks + (PREV ? (ncols ? 2u : 1u) : 0u);
     uint32_t nxt[8];
+    double keep[PREV ? 8 : 1];
     auto fetch = [&](uint32_t chunk) {
         const uint32_t c = chunk << 3;
 #pragma unroll
@@ -327,12 +351,26 @@ B2_D void sponge_row_f64(const Cols& src, uint32_t ncols, uint64_t n, uint64_t i
     };
     if (chunks) fetch(0);
 #pragma unroll 1
-    for (uint32_t it = 0; it < chunks; it++) {
-        const uint32_t c = it << 3;
+    for (uint32_t it = 0; it < total; it++) {
+        if (!PREV || it < chunks) {
+            const uint32_t c = it << 3;
 #pragma unroll
-        for (int k = 0; k < 8; k++)
-            if (c + k < ncols) s[k] = f64_from_monty(nxt[k]);
-        if (it + 1 < chunks) fetch(it + 1);
+            for (int k = 0; k < 8; k++)
+                if (c + k < ncols) s[k] = f64_from_monty(nxt[k]);
+            if (it + 1 < chunks) fetch(it + 1);
+        } else if (it == chunks) {
+            const uint64_t np = 2 * n;
+#pragma unroll
+            for (int w = 0; w < 8; w++) {
+                keep[w] = s[w];
+                const uint2 lr = __ldcg(reinterpret_cast<const uint2*>(prev + (uint64_t)w * np + 2 * i));
+                s[w] = f64_from_monty(lr.x);
+                s[8 + w] = f64_from_monty(lr.y);
+            }
+        } else {
+#pragma unroll
+            for (int w = 0; w < 8; w++) s[8 + w] = keep[w];
+        }
         poseidon2_permute_f64(s);   // words stay within 17.5 p between permutations, no reduction needed
     }
     if (state_out) {
@@ -347,25 +385,37 @@ B2_D void sponge_row_f64(const Cols& src, uint32_t ncols, uint64_t n, uint64_t i
 // 3 blocks of 8 warps per SM (80 registers): measured against 4 x 8 warps at 64 registers, 8 x 4 warps, and an
 // all-integer plus an all-FP64 kernel side by side on two streams -- all end on the same plateau (236-239 ms for the
 // 2^25 x 256 leaf level, 259 ms integer only), which is the issue rate of the two code paths together, not a pipe.
-template <class Cols>
+template <class Cols, bool PREV>
 __global__ void __launch_bounds__(MIX_THREADS, 3) leaf_mixed_kernel(Cols src, uint32_t ncols, uint64_t n, const uint32_t* state_in,
-                                                                    uint32_t* state_out, uint32_t* out, unsigned* ctr, int int_warps) {
+                                                                    uint32_t* state_out, uint32_t* out, const uint32_t* prev, unsigned* ctr,
+                                                                    int int_warps) {
     const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const unsigned tiles = (unsigned)(n >> 5);
     const bool int_path = (int)warp < int_warps;
-    for (;;) {
-        unsigned t = 0;
-        if (lane == 0) t = atomicAdd(ctr, 1u);
-        t = __shfl_sync(0xffffffffu, t, 0);
-        if (t >= tiles) break;
+    // the next tile is claimed before the current one is hashed: the counter's round trip (~1 us) hides behind the
+    // permutations even on levels with one or two of them per row
+    unsigned t = 0;
+    if (lane == 0) t = atomicAdd(ctr, 1u);
+    t = __shfl_sync(0xffffffffu, t, 0);
+    while (t < tiles) {
+        unsigned nxt_t = 0;
+        if (lane == 0) nxt_t = atomicAdd(ctr, 1u);
         const uint64_t i = ((uint64_t)t << 5) + lane;
-        if (int_path) sponge_row_int(src, ncols, n, i, state_in, state_out, out);
-        else sponge_row_f64(src, ncols, n, i, state_in, state_out, out);
+        if (int_path) sponge_row_int<PREV>(src, ncols, n, i, state_in, state_out, out, prev);
+        else sponge_row_f64<PREV>(src, ncols, n, i, state_in, state_out, out, prev);
+        t = __shfl_sync(0xffffffffu, nxt_t, 0);
     }
 }
 
 // B2S_HASH_F64: number of the 8 warps per block left on the integer path (default MIX_INT_WARPS; 8 = all integer
 // through the persistent kernel; "off" = the one-row-per-thread integer kernels)
+static uint64_t mixed_min_rows() {  // B2S_HASH_MIN_LOG: log2 of the smallest level hashed by the two-pipe kernel
+    static uint64_t v = [] {
+        const char* env = getenv("B2S_HASH_MIN_LOG");
+        return env ? (uint64_t)1 << atoi(env) : MIX_MIN_ROWS;
+    }();
+    return v;
+}
 static int mixed_int_warps() {
     static int v = [] {
         const char* env = getenv("B2S_HASH_F64");
@@ -376,12 +426,12 @@ static int mixed_int_warps() {
     }();
     return v;
 }
-template <class Cols>
-static void launch_mixed(b2s_engine* e, Cols src, uint32_t ncols, uint64_t n, const uint32_t* state_in, uint32_t* state_out,
-                         uint32_t* out) {
+template <class Cols, bool PREV>
+static void launch_mixed_as(b2s_engine* e, Cols src, uint32_t ncols, uint64_t n, const uint32_t* state_in, uint32_t* state_out,
+                            uint32_t* out, const uint32_t* prev) {
     static int blocks_per_sm = 0, sms = 0;
     if (!blocks_per_sm) {
-        B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, leaf_mixed_kernel<Cols>, MIX_THREADS, 0));
+        B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, leaf_mixed_kernel<Cols, PREV>, MIX_THREADS, 0));
         int dev = 0;
         B2_CUDA(cudaGetDevice(&dev));
         B2_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -391,8 +441,14 @@ static void launch_mixed(b2s_engine* e, Cols src, uint32_t ncols, uint64_t n, co
     B2_CUDA(cudaMemsetAsync(e->tile_ctr, 0, 4, e->stream));
     const uint64_t want = (n >> 5) / (MIX_THREADS / 32) + 1;  // no more blocks than tiles / warps
     const unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)sms * blocks_per_sm, want);
-    leaf_mixed_kernel<Cols><<<grid, MIX_THREADS, 0, e->stream>>>(src, ncols, n, state_in, state_out, out, e->tile_ctr,
-                                                                 mixed_int_warps());
+    leaf_mixed_kernel<Cols, PREV><<<grid, MIX_THREADS, 0, e->stream>>>(src, ncols, n, state_in, state_out, out, prev, e->tile_ctr,
+                                                                       mixed_int_warps());
+}
+template <class Cols>
+static void launch_mixed(b2s_engine* e, Cols src, uint32_t ncols, uint64_t n, const uint32_t* state_in, uint32_t* state_out,
+                         uint32_t* out, const uint32_t* prev = nullptr) {
+    if (prev) launch_mixed_as<Cols, true>(e, src, ncols, n, state_in, state_out, out, prev);
+    else launch_mixed_as<Cols, false>(e, src, ncols, n, state_in, state_out, out, prev);
 }
 
 static inline unsigned grid_for(uint64_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
@@ -400,7 +456,7 @@ static inline unsigned grid_for(uint64_t n, int threads) { return (unsigned)((n 
 void leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_t n, uint32_t* state, uint32_t* out, bool first,
                  bool last) {
     StageScope sc(e, ST_LEAF);
-    if (n >= MIX_MIN_ROWS && mixed_int_warps() >= 0)
+    if (n >= mixed_min_rows() && mixed_int_warps() >= 0)
         launch_mixed(e, ColStrided{base, n}, ncols, n, first ? nullptr : state, last ? nullptr : state, out);
     else
         leaf_absorb_kernel<<<grid_for(n, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(base, ncols, n, state, out, first ? 1 : 0,
@@ -413,8 +469,8 @@ void leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_t n
 // one tree level: throughput kernel (one node per thread) for big levels, latency kernel (four lanes per node) below
 static void launch_level(b2s_engine* e, const uint32_t* const* cols, uint32_t ncols, uint64_t n, const uint32_t* prev,
                          uint32_t* out, int mode) {
-    if (mode == 0 && n >= MIX_MIN_ROWS && mixed_int_warps() >= 0)
-        launch_mixed(e, ColTable{cols}, ncols, n, nullptr, nullptr, out);
+    if (n >= mixed_min_rows() && mixed_int_warps() >= 0)
+        launch_mixed(e, ColTable{cols}, ncols, n, nullptr, nullptr, out, mode == 0 ? nullptr : prev);
     else if (n <= COOP_MAX_NODES)
         tree_level_coop_kernel<<<grid_for(4 * n, COOP_THREADS), COOP_THREADS, 0, e->stream>>>(cols, ncols, n, prev, out, mode);
     else

@@ -132,30 +132,32 @@ rng = np.random.default_rng(77)
 e = B2Engine.new(FriParameters(log_blowup=1), 0)
 dev = e.device()
 out = []
-for h, w in {shapes!r}:
-    m = rng.integers(0, 2013265921, size=(h, w), dtype=np.uint64).astype(np.uint32)
-    root, pcs = dev.commit([dev.transport_matrix_to_device(m)])
+for group in {shapes!r}:
+    ms = [rng.integers(0, 2013265921, size=(h, w), dtype=np.uint64).astype(np.uint32) for h, w in group]
+    root, pcs = dev.commit([dev.transport_matrix_to_device(m) for m in ms])
     out.append(" ".join(str(int(x)) for x in root))
 e.close()
 print("|".join(out))
 """
 
 
-@pytest.mark.parametrize("knob", ["0", "8", "off"])
+@pytest.mark.parametrize("knob", ["0", "4", "8", "off"])
 def test_leaf_hash_code_paths_agree(orc, knob):
     """The tall leaf level is hashed by a persistent kernel whose warps run either the integer or the FP64 Poseidon2
-    (merkle.cu, poseidon2_f64.cuh), whichever is free. Every single path -- all FP64 (B2S_HASH_F64=0), all integer (8),
-    the one-row-per-thread integer kernel (off) -- must give the oracle's root, on widths that end in a partial chunk."""
+    (merkle.cu, poseidon2_f64.cuh), whichever is free. Every path -- all FP64 (B2S_HASH_F64=0), the shipped 4 + 4 mix,
+    all integer (8), the one-row-per-thread integer kernel (off) -- must give the oracle's root, on widths that end in a
+    partial chunk and on trees with compress-and-inject levels."""
     import os, subprocess, sys
-    shapes = [(1 << 13, 19), (1 << 14, 8), (1 << 13, 1), (1 << 15, 70)]
+    # the last group joins shorter matrices below the leaves (compress-and-inject levels) and has plain compress levels
+    shapes = [[(1 << 13, 19)], [(1 << 14, 8)], [(1 << 13, 1)], [(1 << 15, 70)], [(1 << 16, 9), (1 << 14, 13), (1 << 13, 3)]]
     root_dir = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    env = dict(os.environ, B2S_HASH_F64=knob)
+    env = dict(os.environ, B2S_HASH_F64=knob, B2S_HASH_MIN_LOG="12")  # the product switches at 2^19 rows
     r = subprocess.run([sys.executable, "-c", _LEAF_PATH_SCRIPT.format(root=root_dir, shapes=shapes)], env=env,
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     got = [[int(x) for x in part.split()] for part in r.stdout.strip().splitlines()[-1].split("|")]
     rng2 = np.random.default_rng(77)
-    for (h, w), g in zip(shapes, got):
-        m = rng2.integers(0, P, size=(h, w), dtype=np.uint64).astype(np.uint32)
-        want_root = orc.commit([m], 1)
-        assert g == [int(x) for x in want_root], (knob, h, w)
+    for group, g in zip(shapes, got):
+        ms = [rng2.integers(0, P, size=(h, w), dtype=np.uint64).astype(np.uint32) for h, w in group]
+        want_root = orc.commit(ms, 1)
+        assert g == [int(x) for x in want_root], (knob, group)
