@@ -412,11 +412,11 @@ def main():
         lde_ms_step = met["lde_ms"] / steps
         perms = permutations(log_h, width, b)
         roofline = {
-            "kernel": "tree_level_kernel (Poseidon2 leaf sponge; integer-multiply bound: ncu fmaheavy 91 % busy, dram 1.7 %, profiles/r1e_ncu_hash_summary.md; reported against HBM as the contract asks)",
+            "kernel": "leaf_mixed_kernel (Poseidon2 leaf sponge on the integer-multiply and FP64 pipes side by side; ncu: fmaheavy 78 % + fp64 46 % busy, issue 0.71/cycle, dispatch-bound, dram 1.8 %, profiles/r1g_fp64_pipe.md; reported against HBM as the contract asks)",
             "bound": "hbm", "achieved": leaf_bytes / (leaf_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
             "frac": leaf_bytes / (leaf_ms * 1e-3) / 1e9 / peak,
-            # dram__bytes_read.sum + dram__bytes_write.sum of this launch, ncu --set full capture profiles/r1e_ncu_hash_summary.md
-            "traffic": 35.490e9 if (log_h, width, b) == (24, 256, 1) else None, "peak_source": peak_src,
+            # dram__bytes_read.sum + dram__bytes_write.sum of this launch, ncu --set full capture profiles/r1g_fp64_pipe.md
+            "traffic": 35.508e9 if (log_h, width, b) == (24, 256, 1) else None, "peak_source": peak_src,
             "ms_per_launch": leaf_ms, "share_of_step": met["leaf_hash_ms"] / steps / ms_step,
         }
         roofline_lde = {
