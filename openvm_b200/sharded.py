@@ -1,0 +1,160 @@
+"""One commitment across the GPUs of a node (SURVEY.md 8e "if a single proof must span GPUs", 8f-4).
+
+Segments are independent proofs and normally go one per GPU (scheduler.py). This module is for the other case: ONE trace
+too tall to wait for on a single GPU. The reference has no such path (TraceCommitter::commit runs on one device,
+crates/vm/src/arch/vm.rs:735); the result here is bit-identical to `B2Device.commit` of the whole trace on one GPU.
+
+Plan for G ranks, trace N x W, blowup 2^b (R = 2^b N / G rows per rank afterwards):
+  1. every rank holds a COLUMN shard of the trace (N x W_g): the NTT is per column, so the coset LDE needs no exchange
+     (b2s_coset_lde on the shard);
+  2. the leaf sponge runs along a row, so the LDE is re-sharded by ROWS: rank g receives rows [g R, (g+1) R) of every
+     column -- one all-to-all over NVLink / NVSwitch (torch.distributed all_to_all_single on the NCCL backend; the send
+     buffer is the column shard regrouped by destination, a single strided copy);
+  3. rows are stored bit-reversed, so a contiguous block of R = 2^k rows is exactly one sub-tree of the Merkle tree:
+     rank g hashes its rows and builds that sub-tree (b2s_mmcs_commit on the adopted row shard);
+  4. the G sub-roots are all-gathered (32 bytes each) and the top log2(G) levels are compressed on every rank.
+Openings: the rank owning the row answers with the row and its sub-tree path; the top-level siblings come from the
+gathered sub-roots (`ShardedPcsData.open_batch`).
+
+All device work is queued on torch's current stream (the engine is switched to it), so the collective and the kernels
+are ordered without host synchronisation.
+"""
+import numpy as np
+
+from .engine import B2Engine, DeviceMatrix  # noqa: F401  (types for callers)
+
+
+def column_shards(width, world_size):
+    """Column ranges [lo, hi) per rank: contiguous, sizes differing by at most one (the order of columns in a row is
+    the order of absorption into the leaf sponge, so shards must be contiguous and in rank order)."""
+    if world_size < 1 or width < world_size:
+        raise ValueError("need at least one column per rank")
+    base, extra = divmod(width, world_size)
+    out, lo = [], 0
+    for g in range(world_size):
+        hi = lo + base + (1 if g < extra else 0)
+        out.append((lo, hi))
+        lo = hi
+    return out
+
+
+def combine_subroots(subroots, compress):
+    """Top of the tree over G = 2^k sub-roots (in rank order). `compress(left8, right8) -> 8 words` is the 2-to-1
+    Poseidon2 compression. Returns (root, levels) with levels[0] = the sub-roots, levels[-1] = [root]."""
+    g = len(subroots)
+    if g & (g - 1):
+        raise ValueError("world size must be a power of two")
+    levels = [[np.asarray(r, dtype=np.uint32) for r in subroots]]
+    while len(levels[-1]) > 1:
+        cur = levels[-1]
+        levels.append([compress(cur[2 * i], cur[2 * i + 1]) for i in range(len(cur) // 2)])
+    return levels[-1][0], levels
+
+
+def top_path(levels, rank):
+    """Sibling digests above sub-tree `rank`, bottom-up."""
+    path, i = [], rank
+    for lvl in levels[:-1]:
+        path.append(lvl[i ^ 1])
+        i >>= 1
+    return path
+
+
+def reshard_rows(lde_t, width, group=None):
+    """Column shard -> row shard. `lde_t`: this rank's LDE columns as one flat int32 tensor ([column][row], rows =
+    full LDE height), on the device of the process group's backend. Returns the (width, rows / G) tensor holding rows
+    [g R, (g+1) R) of ALL columns ([column][row], i.e. a column-major R x width matrix). The send buffer is the shard
+    regrouped [column][dest][row] -> [dest][column][row] (one strided copy); ragged column shards go through the
+    split sizes of all_to_all_single."""
+    import torch
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    shards = column_shards(width, world)
+    w_local = shards[rank][1] - shards[rank][0]
+    rows = lde_t.numel() // w_local
+    r = rows // world
+    send = lde_t.view(w_local, world, r).permute(1, 0, 2).contiguous().view(world * w_local, r)
+    recv = torch.empty((width, r), dtype=lde_t.dtype, device=lde_t.device)
+    dist.all_to_all_single(recv, send, output_split_sizes=[hi - lo for lo, hi in shards],
+                           input_split_sizes=[w_local] * world, group=group)
+    return recv
+
+
+class _DevBuf:
+    """A device pointer as a CUDA-array-interface object (torch.as_tensor shares the memory)."""
+
+    def __init__(self, ptr, nwords):
+        self.__cuda_array_interface__ = {"shape": (int(nwords),), "typestr": "<i4", "data": (int(ptr), False), "version": 2}
+
+
+class ShardedPcsData:
+    def __init__(self, rank, world, log_height, width, local_pcs, levels, keep):
+        self.rank, self.world = rank, world
+        self.log_height, self.width = log_height, width   # of the whole LDE
+        self.local = local_pcs                             # PcsData of this rank's row block (a sub-tree)
+        self.levels = levels
+        self._keep = keep
+
+    def owner(self, index):
+        return index >> (self.log_height - (self.world.bit_length() - 1))
+
+    def open_batch(self, index):
+        """On the owning rank: (row, path) exactly as PcsData.open_batch of the single-GPU commitment; None elsewhere."""
+        if self.owner(index) != self.rank:
+            return None
+        rows_per_rank = 1 << (self.log_height - (self.world.bit_length() - 1))
+        row, path = self.local.open_batch(index & (rows_per_rank - 1))
+        top = top_path(self.levels, self.rank)
+        if top:
+            path = np.concatenate([np.asarray(path, dtype=np.uint32).reshape(-1, 8), np.stack(top)])
+        return row, path
+
+
+def sharded_commit(engine, local_columns, width, log_blowup, group=None):
+    """Commit the N x `width` trace whose columns [lo_g, hi_g) = column_shards(width, G)[g] live on rank g as the
+    DeviceMatrix `local_columns` (N x W_g, column-major). Returns (root as 8 canonical words, ShardedPcsData); every rank
+    gets the same root, equal to B2Device.commit([whole trace]) on one GPU."""
+    import torch
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    dev = engine.device()
+    cuda_dev = torch.device("cuda", torch.cuda.current_device())
+    cur = torch.cuda.current_stream().cuda_stream
+    if engine.stream != cur:
+        engine.set_stream(cur)
+    shards = column_shards(width, world)
+    w_local = shards[rank][1] - shards[rank][0]
+    if local_columns.width != w_local:
+        raise ValueError(f"rank {rank} must hold {w_local} columns, has {local_columns.width}")
+    n = local_columns.height
+    rows = n << log_blowup
+    if rows % world or (world & (world - 1)):
+        raise ValueError("world size must be a power of two dividing the LDE height")
+    r = rows // world
+
+    # 1. coset LDE of the column shard
+    lde = dev.coset_lde(local_columns, log_blowup)
+    lde_t = torch.as_tensor(_DevBuf(lde.device_ptr, w_local * rows), device=cuda_dev)
+    # 2. regroup by destination and exchange
+    recv = reshard_rows(lde_t, width, group)
+    lde.free()
+    del lde_t
+    # 3. this rank's sub-tree over its R rows of all columns
+    block = dev.adopt_device_matrix(recv.data_ptr(), r, width)
+    subroot, local_pcs = dev.mmcs_commit([block])
+    # 4. top levels from the gathered sub-roots
+    mine = torch.from_numpy(subroot.astype(np.int64)).to(cuda_dev)
+    allroots = torch.empty((world, 8), dtype=torch.int64, device=cuda_dev)
+    dist.all_gather_into_tensor(allroots, mine, group=group)
+    subroots = allroots.cpu().numpy().astype(np.uint32)
+
+    def compress(left, right):
+        return dev.poseidon2_permute(np.concatenate([left, right]))[0, :8].copy()
+
+    root, levels = combine_subroots(list(subroots), compress)
+    log_height = rows.bit_length() - 1
+    return root, ShardedPcsData(rank, world, log_height, width, local_pcs, levels, keep=(recv, block))

@@ -1,0 +1,73 @@
+"""GPU parity of the sharded commitment (openvm_b200/sharded.py): two ranks over NCCL produce the root, the rows and
+the opening paths of the single-GPU b2s_commit of the same trace. Needs two GPUs; skipped on a one-GPU box."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+P = 2013265921
+
+
+def _worker(rank, world, port, q, height, width, b):
+    try:
+        import torch.distributed as dist
+        from openvm_b200 import B2Engine, FriParameters, sharded
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+        eng = B2Engine.new(FriParameters(log_blowup=b), rank)
+        dev = eng.device()
+        trace = np.random.default_rng(9).integers(0, P, size=(height, width), dtype=np.uint64).astype(np.uint32)
+        lo, hi = sharded.column_shards(width, world)[rank]
+        local = dev.transport_matrix_to_device(np.ascontiguousarray(trace[:, lo:hi]))
+        root, spcs = sharded.sharded_commit(eng, local, width, b)
+        torch.cuda.synchronize()
+        rows = height << b
+        indices = [0, 1, rows // 2 - 1, rows // 2, rows - 1, 12345 % rows]
+        opened = {i: spcs.open_batch(i) for i in indices}
+        out = {"rank": rank, "root": [int(x) for x in root],
+               "opened": {i: (v[0][0].tolist(), np.asarray(v[1]).tolist()) for i, v in opened.items() if v is not None}}
+        if rank == 0:
+            want_root, pcs = dev.commit([dev.transport_matrix_to_device(trace)])
+            out["want_root"] = [int(x) for x in want_root]
+            out["want_opened"] = {}
+            for i in indices:
+                r_, p_ = pcs.open_batch(i)
+                out["want_opened"][i] = (r_[0].tolist(), np.asarray(p_).tolist())
+        dist.barrier()
+        q.put(out)
+        eng.close()
+        dist.destroy_process_group()
+    except Exception as ex:  # surface the failure in the parent
+        import traceback
+        q.put({"rank": rank, "error": traceback.format_exc() + repr(ex)})
+
+
+@pytest.mark.parametrize("height,width,b", [(1 << 12, 19, 1), (1 << 18, 64, 1), (1 << 14, 9, 2)])
+def test_sharded_commit_two_gpus(height, width, b):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q, height, width, b)) for r in range(2)]
+    for p in procs: p.start()
+    res = [q.get(timeout=600) for _ in range(2)]
+    for p in procs: p.join(timeout=120)
+    for r in res:
+        assert "error" not in r, r.get("error")
+    res.sort(key=lambda r: r["rank"])
+    want = res[0]
+    for r in res:
+        assert r["root"] == want["want_root"]
+    seen = 0
+    for r in res:
+        for i, (row, path) in r["opened"].items():
+            wrow, wpath = want["want_opened"][i]
+            assert row == wrow and path == wpath, (r["rank"], i)
+            seen += 1
+    assert seen == len(want["want_opened"])      # every index was answered by exactly one rank
