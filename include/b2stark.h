@@ -136,6 +136,26 @@ int32_t b2s_coset_lde(b2s_engine* e, const b2s_matrix* in, uint32_t log_blowup, 
 int32_t b2s_mmcs_commit(b2s_engine* e, const b2s_matrix* const* mats, size_t n_mats, uint32_t root8[8],
                         b2s_pcs_data** out);
 
+/* ---- one commitment across the GPUs of a node (no reference counterpart: TraceCommitter::commit runs on one device,
+ * crates/vm/src/arch/vm.rs:735; host side: openvm_b200/sharded.py) ---------------------------
+ * Every rank (one process per GPU) holds a COLUMN shard of the trace and, after the exchange, a ROW block of the LDE
+ * of all columns, which is one sub-tree of the Merkle tree (rows are stored bit-reversed). The exchange is fused into
+ * the LDE: the last NTT pass stores every output row straight into the buffer of the rank that will hash it, over
+ * NVLink peer mappings -- no staging buffer, no separate collective.
+ *   b2s_shared_alloc   device buffer that other processes can map (cudaMalloc + cudaIpcGetMemHandle, 64-byte handle)
+ *   b2s_shared_open    maps a peer's buffer from its handle (cudaIpcOpenMemHandle); b2s_shared_close unmaps it
+ *   b2s_coset_lde_scatter  coset LDE of this rank's columns [col0, col0 + in->width) of a trace of `total_width` columns;
+ *                      rank g's buffer peer_bufs[g] (this rank's own allocation at its own index) receives LDE rows
+ *                      [g R, (g+1) R), R = (height << log_blowup) / n_peers, as a column-major R x total_width matrix.
+ * The caller orders the ranks (a barrier after synchronising the stream) before anyone reads its buffer. */
+#define B2S_MAX_PEERS 16
+int32_t b2s_shared_alloc(b2s_engine* e, uint64_t bytes, void** device_ptr, uint8_t handle64[64]);
+int32_t b2s_shared_free(b2s_engine* e, void* device_ptr);
+int32_t b2s_shared_open(b2s_engine* e, const uint8_t handle64[64], void** device_ptr);
+int32_t b2s_shared_close(b2s_engine* e, void* device_ptr);
+int32_t b2s_coset_lde_scatter(b2s_engine* e, const b2s_matrix* in, uint32_t log_blowup, uint32_t shift_in,
+                              void* const* peer_bufs, uint32_t n_peers, uint64_t total_width, uint64_t col0);
+
 size_t b2s_pcs_num_matrices(const b2s_pcs_data* d);
 uint32_t b2s_pcs_log_max_height(const b2s_pcs_data* d);
 /* borrowed view of the i-th retained (LDE) matrix, valid while `d` lives */

@@ -55,6 +55,11 @@ SIGNATURES = {
     "b2s_commit": (C.c_int32, [vp, C.POINTER(vp), C.c_size_t, u32p, C.POINTER(vp)]),
     "b2s_coset_lde": (C.c_int32, [vp, vp, C.c_uint32, C.c_uint32, C.POINTER(vp)]),
     "b2s_mmcs_commit": (C.c_int32, [vp, C.POINTER(vp), C.c_size_t, u32p, C.POINTER(vp)]),
+    "b2s_shared_alloc": (C.c_int32, [vp, C.c_uint64, C.POINTER(vp), C.c_char_p]),
+    "b2s_shared_free": (C.c_int32, [vp, vp]),
+    "b2s_shared_open": (C.c_int32, [vp, C.c_char_p, C.POINTER(vp)]),
+    "b2s_shared_close": (C.c_int32, [vp, vp]),
+    "b2s_coset_lde_scatter": (C.c_int32, [vp, vp, C.c_uint32, C.c_uint32, C.POINTER(vp), C.c_uint32, C.c_uint64, C.c_uint64]),
     "b2s_pcs_num_matrices": (C.c_size_t, [vp]),
     "b2s_pcs_log_max_height": (C.c_uint32, [vp]),
     "b2s_pcs_matrix": (vp, [vp, C.c_size_t]),

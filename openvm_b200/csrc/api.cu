@@ -440,6 +440,71 @@ int32_t b2s_coset_lde(b2s_engine* e, const b2s_matrix* in, uint32_t log_blowup, 
     });
 }
 
+int32_t b2s_shared_alloc(b2s_engine* e, uint64_t bytes, void** device_ptr, uint8_t handle64[64]) {
+    if (!e || !device_ptr || !handle64 || !bytes) return B2S_ERR_BAD_ARG;
+    *device_ptr = nullptr;
+    return guarded(e, [&] {
+        static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
+        void* p = nullptr;
+        B2_CUDA(cudaMalloc(&p, bytes));   // not from the stream-ordered pool: pool memory cannot be exported
+        cudaIpcMemHandle_t h;
+        cudaError_t err = cudaIpcGetMemHandle(&h, p);
+        if (err != cudaSuccess) {
+            cudaFree(p);
+            B2_CUDA(err);
+        }
+        memcpy(handle64, &h, 64);
+        *device_ptr = p;
+    });
+}
+int32_t b2s_shared_free(b2s_engine* e, void* device_ptr) {
+    if (!e) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] {
+        B2_CUDA(cudaStreamSynchronize(e->stream));
+        B2_CUDA(cudaFree(device_ptr));
+    });
+}
+int32_t b2s_shared_open(b2s_engine* e, const uint8_t handle64[64], void** device_ptr) {
+    if (!e || !device_ptr || !handle64) return B2S_ERR_BAD_ARG;
+    *device_ptr = nullptr;
+    return guarded(e, [&] {
+        cudaIpcMemHandle_t h;
+        memcpy(&h, handle64, 64);
+        B2_CUDA(cudaIpcOpenMemHandle(device_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    });
+}
+int32_t b2s_shared_close(b2s_engine* e, void* device_ptr) {
+    if (!e) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] {
+        B2_CUDA(cudaStreamSynchronize(e->stream));
+        B2_CUDA(cudaIpcCloseMemHandle(device_ptr));
+    });
+}
+int32_t b2s_coset_lde_scatter(b2s_engine* e, const b2s_matrix* in, uint32_t log_blowup, uint32_t shift_in,
+                              void* const* peer_bufs, uint32_t n_peers, uint64_t total_width, uint64_t col0) {
+    if (!e || !in || !peer_bufs) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] {
+        B2_REQUIRE(is_pow2(in->height), B2S_ERR_SHAPE, "lde: height must be a power of two");
+        B2_REQUIRE(shift_in > 0 && shift_in < P, B2S_ERR_BAD_ARG, "lde: shift must be a non-zero canonical element");
+        B2_REQUIRE(n_peers >= 1 && n_peers <= B2_MAX_PEERS && is_pow2(n_peers), B2S_ERR_BAD_ARG,
+                   "lde scatter: the number of peers must be a power of two, at most 16");
+        B2_REQUIRE(col0 + in->width <= total_width, B2S_ERR_SHAPE, "lde scatter: column shard outside the trace");
+        const uint64_t rows = in->height << log_blowup;
+        B2_REQUIRE(rows / n_peers >= 4, B2S_ERR_SHAPE, "lde scatter: fewer than 4 rows per peer");
+        PeerScatter ps{};
+        ps.n_peers = n_peers;
+        ps.log_rows = log2_exact(rows / n_peers);
+        ps.col0 = col0;
+        for (uint32_t i = 0; i < n_peers; i++) {
+            B2_REQUIRE(peer_bufs[i] != nullptr, B2S_ERR_BAD_ARG, "lde scatter: null peer buffer");
+            ps.peer[i] = (uint32_t*)peer_bufs[i];
+        }
+        StageScope sc(e, ST_LDE);
+        lde_columns(e, in->d, in->height, log2_exact(in->height), in->width, log_blowup, Fp::from_canonical(shift_in), nullptr, 0,
+                    &ps);
+    });
+}
+
 static void root_to_host(b2s_engine* e, b2s_pcs_data* d, uint32_t root8[8]) {
     uint32_t raw[8];
     B2_CUDA(cudaMemcpyAsync(raw, d->layers.back(), 32, cudaMemcpyDeviceToHost, e->stream));

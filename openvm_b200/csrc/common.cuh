@@ -159,8 +159,16 @@ struct StageScope {
 
 // ---- kernels' host entry points (defined in the .cu files) ---------------------------------------------
 // ntt.cu
+#define B2_MAX_PEERS 16
+// row-sharded LDE output over peer memory (sharded commitment): see PassParams in ntt.cu
+struct PeerScatter {
+    uint32_t* peer[B2_MAX_PEERS];   // per rank: column-major (2^log_rows) x total_width buffer, mapped into this process
+    uint32_t n_peers;
+    uint32_t log_rows;               // rows per rank
+    uint64_t col0;                   // global index of the first column of this shard
+};
 void lde_columns(b2s_engine* e, const uint32_t* in, uint64_t in_col_stride, unsigned logn, uint64_t width,
-                 unsigned log_blowup, Fp shift_in, uint32_t* out, uint64_t out_col_stride);
+                 unsigned log_blowup, Fp shift_in, uint32_t* out, uint64_t out_col_stride, const PeerScatter* ps = nullptr);
 void free_twiddles(b2s_engine* e);
 void free_scales(b2s_engine* e);
 // merkle.cu

@@ -189,6 +189,13 @@ struct PassParams {
     uint32_t in_block;        // 1: the input is offset by the coset block as well (in-place passes on the LDE)
     uint32_t scale;           // != 0: multiply loaded words by this (1/N; first forward pass)
     uint32_t reverse_load;    // contiguous pass with D == log_len: word p of the run is stored at slot bitrev_D(p)
+    // Row-sharded output over peer memory (last pass of a sharded commitment, openvm_b200/sharded.py): LDE row `row` of
+    // launch column `col` is stored at peer_out[row >> peer_log_rows] + (peer_col0 + col) * 2^peer_log_rows + (row mod
+    // 2^peer_log_rows) -- the buffer of the rank that will hash that row, written over NVLink by this kernel's own stores.
+    uint32_t peer_n;          // 0: plain output
+    uint32_t peer_log_rows;
+    uint64_t peer_col0;
+    uint32_t* peer_out[B2_MAX_PEERS];
 };
 
 template <int D, int U, bool GATHER>
@@ -474,7 +481,14 @@ __global__ void __launch_bounds__(K2Cfg<D>::THREADS) ntt_contig_kernel(PassParam
         if (g >= total_runs) break;
         uint32_t col, rho;
         locate(rs, col, rho);
-        uint32_t* dst = p.out + (uint64_t)col * p.out_col_stride + blk_off + ((uint64_t)rho << D) + w;
+        uint32_t* dst;
+        if (p.peer_n) {
+            const uint64_t row = blk_off + ((uint64_t)rho << D) + w;   // 4 words never straddle two peers' row blocks
+            dst = p.peer_out[row >> p.peer_log_rows] + ((p.peer_col0 + col) << p.peer_log_rows) +
+                  (row & (((uint64_t)1 << p.peer_log_rows) - 1));
+        } else {
+            dst = p.out + (uint64_t)col * p.out_col_stride + blk_off + ((uint64_t)rho << D) + w;
+        }
         const uint32_t* xs = x + rs * C::PITCH + phys(w);  // w % 4 == 0: the four words share one group of 32
         if constexpr (V == 4) *reinterpret_cast<uint4*>(dst) = make_uint4(xs[0], xs[1], xs[2], xs[3]);
         else dst[0] = xs[0];
@@ -619,11 +633,12 @@ static Plan make_plan(unsigned n) {
 // LDE of `width` columns: in = evaluations over shift_in*H_N, natural order (column stride in_col_stride);
 // out = evaluations over GENERATOR*H_{N*2^b}, bit-reversed order (column stride out_col_stride >= N*2^b).
 void lde_columns(b2s_engine* e, const uint32_t* in, uint64_t in_col_stride, unsigned logn, uint64_t width,
-                 unsigned log_blowup, Fp shift_in, uint32_t* out, uint64_t out_col_stride) {
+                 unsigned log_blowup, Fp shift_in, uint32_t* out, uint64_t out_col_stride, const PeerScatter* ps) {
     B2_REQUIRE(logn + log_blowup <= TWO_ADICITY, B2S_ERR_SHAPE, "lde: log height + log blowup exceeds two-adicity 27");
     if (width == 0) return;
     const uint64_t N = (uint64_t)1 << logn;
     const uint32_t B = 1u << log_blowup;
+    B2_REQUIRE(!ps || logn >= 2, B2S_ERR_SHAPE, "lde: a row-sharded output needs at least 4 rows");
     if (logn == 0) {
         for (uint64_t c0 = 0; c0 < width; c0 += 1u << 20) {
             uint32_t g = (uint32_t)std::min<uint64_t>(width - c0, 1u << 20);
@@ -647,11 +662,21 @@ void lde_columns(b2s_engine* e, const uint32_t* in, uint64_t in_col_stride, unsi
     if (G > width) G = width;
     if (G > 65535) G = 65535;
     uint32_t* coef = (uint32_t*)e->dmalloc(G * N * 4);
+    // row-sharded output: the passes before the last work in a group-sized scratch, the last one stores to the peers
+    uint32_t* scratch = ps ? (uint32_t*)e->dmalloc(G * N * B * 4) : nullptr;
+    if (ps) out_col_stride = N * B;
 
     for (uint64_t c0 = 0; c0 < width; c0 += G) {
         const uint32_t g = (uint32_t)std::min<uint64_t>(G, width - c0);
         const uint32_t* gin = in + c0 * in_col_stride;
-        uint32_t* gout = out + c0 * out_col_stride;
+        uint32_t* gout = ps ? scratch : out + c0 * out_col_stride;
+        auto to_peers = [&](PassParams& q) {
+            if (!ps) return;
+            q.peer_n = ps->n_peers;
+            q.peer_log_rows = ps->log_rows;
+            q.peer_col0 = ps->col0 + c0;
+            for (uint32_t i = 0; i < ps->n_peers; i++) q.peer_out[i] = ps->peer[i];
+        };
         // ---------------- inverse: evaluations (natural) -> coefficients at bit-reversed slots, unscaled
         PassParams p{};
         p.width = g;
@@ -681,6 +706,7 @@ void lde_columns(b2s_engine* e, const uint32_t* in, uint64_t in_col_stride, unsi
         if (pl.strided.empty()) {
             p.t0 = 0;
             p.reverse_load = 1;
+            to_peers(p);
             launch_contig(e, pl.contig, p, B);
         } else {
             p.t0 = 0;
@@ -693,9 +719,11 @@ void lde_columns(b2s_engine* e, const uint32_t* in, uint64_t in_col_stride, unsi
                 t0 += pl.strided[i];
             }
             p.t0 = t0;
+            to_peers(p);
             launch_contig(e, pl.contig, p, B);
         }
     }
+    if (scratch) e->dfree(scratch, G * N * B * 4);
     e->dfree(coef, G * N * 4);
 }
 

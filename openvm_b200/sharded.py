@@ -18,7 +18,15 @@ gathered sub-roots (`ShardedPcsData.open_batch`).
 
 All device work is queued on torch's current stream (the engine is switched to it), so the collective and the kernels
 are ordered without host synchronisation.
+
+`ShardedCommitter` is the fused form of steps 1-2 (the one to use): the rows never pass through a send buffer or a
+collective. Each rank allocates its row-block buffer once, the ranks exchange CUDA IPC handles and map each other's
+buffers, and the LAST NTT PASS of the LDE stores every output row straight into the buffer of the rank that will hash
+it, over NVLink (b2s_coset_lde_scatter: ntt_contig_kernel with a peer table). What is left of the exchange is two barriers.
+`sharded_commit` (NCCL all-to-all) is kept as the baseline it is measured against.
 """
+import ctypes as C
+
 import numpy as np
 
 from .engine import B2Engine, DeviceMatrix  # noqa: F401  (types for callers)
@@ -158,3 +166,88 @@ def sharded_commit(engine, local_columns, width, log_blowup, group=None):
     root, levels = combine_subroots(list(subroots), compress)
     log_height = rows.bit_length() - 1
     return root, ShardedPcsData(rank, world, log_height, width, local_pcs, levels, keep=(recv, block))
+
+
+class ShardedCommitter:
+    """Fused sharded commitment for traces of one shape (height x width, log_blowup), reusable across commits.
+
+    The row-block buffers are allocated once (cudaMalloc, exported with CUDA IPC, mapped by every peer). `commit`
+    returns a ShardedPcsData whose sub-tree BORROWS this rank's buffer: it is valid until the next `commit` on the same
+    committer (use two committers to keep two commitments alive)."""
+
+    def __init__(self, engine, height, width, log_blowup, group=None):
+        import torch.distributed as dist
+        self.engine, self.group = engine, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.height, self.width, self.b = height, width, log_blowup
+        self.rows = height << log_blowup
+        if self.world & (self.world - 1) or self.world > 16 or self.rows // self.world < 4:
+            raise ValueError("world size must be a power of two (<= 16) with at least 4 LDE rows per rank")
+        self.r = self.rows // self.world
+        self.shards = column_shards(width, self.world)
+        e = engine
+        ptr, handle = C.c_void_p(), C.create_string_buffer(64)
+        e._check(e._lib.b2s_shared_alloc(e._h, self.r * width * 4, C.byref(ptr), handle))
+        self._own = ptr.value
+        handles = [None] * self.world
+        dist.all_gather_object(handles, handle.raw, group=group)
+        self._peers = []
+        for g, h in enumerate(handles):
+            if g == self.rank:
+                self._peers.append(self._own)
+            else:
+                q = C.c_void_p()
+                e._check(e._lib.b2s_shared_open(e._h, h, C.byref(q)))
+                self._peers.append(q.value)
+        self._peer_arr = (C.c_void_p * self.world)(*self._peers)
+        self._block = engine.device().adopt_device_matrix(self._own, self.r, width)
+
+    def commit(self, local_columns):
+        """local_columns: this rank's DeviceMatrix of columns column_shards(width, G)[rank] (height x W_g)."""
+        import torch
+        import torch.distributed as dist
+        e, dev = self.engine, self.engine.device()
+        lo, hi = self.shards[self.rank]
+        if local_columns.width != hi - lo or local_columns.height != self.height:
+            raise ValueError(f"rank {self.rank} must hold a {self.height} x {hi - lo} column shard")
+        cur = torch.cuda.current_stream().cuda_stream
+        if e.stream != cur:
+            e.set_stream(cur)
+        # nobody may still be hashing the previous contents of a buffer we are about to overwrite
+        torch.cuda.current_stream().synchronize()
+        dist.barrier(group=self.group)
+        # 1 + 2. coset LDE whose last pass writes each row into its owner's buffer over NVLink
+        e._check(e._lib.b2s_coset_lde_scatter(e._h, local_columns._h, self.b, 1, self._peer_arr, self.world, self.width, lo))
+        torch.cuda.current_stream().synchronize()
+        dist.barrier(group=self.group)          # every peer's rows have landed
+        # 3. this rank's sub-tree
+        subroot, local_pcs = dev.mmcs_commit([self._block])
+        # 4. top levels
+        cuda_dev = torch.device("cuda", torch.cuda.current_device())
+        mine = torch.from_numpy(subroot.astype(np.int64)).to(cuda_dev)
+        allroots = torch.empty((self.world, 8), dtype=torch.int64, device=cuda_dev)
+        dist.all_gather_into_tensor(allroots, mine, group=self.group)
+        subroots = allroots.cpu().numpy().astype(np.uint32)
+
+        def compress(left, right):
+            return dev.poseidon2_permute(np.concatenate([left, right]))[0, :8].copy()
+
+        root, levels = combine_subroots(list(subroots), compress)
+        return root, ShardedPcsData(self.rank, self.world, self.rows.bit_length() - 1, self.width, local_pcs, levels,
+                                    keep=(self,))
+
+    def close(self):
+        import torch
+        import torch.distributed as dist
+        e = self.engine
+        if self._own is None:
+            return
+        torch.cuda.synchronize()
+        dist.barrier(group=self.group)          # no peer is still writing into a buffer that is about to go away
+        for g, q in enumerate(self._peers):
+            if g != self.rank:
+                e._check(e._lib.b2s_shared_close(e._h, q))
+        dist.barrier(group=self.group)
+        self._block.free()
+        e._check(e._lib.b2s_shared_free(e._h, self._own))
+        self._own = None

@@ -1,5 +1,6 @@
-"""GPU parity of the sharded commitment (openvm_b200/sharded.py): two ranks over NCCL produce the root, the rows and
-the opening paths of the single-GPU b2s_commit of the same trace. Needs two GPUs; skipped on a one-GPU box."""
+"""GPU parity of the sharded commitment (openvm_b200/sharded.py): two ranks produce the root, the rows and the opening
+paths of the single-GPU b2s_commit of the same trace -- through the NCCL all-to-all baseline and through the fused form
+(last NTT pass storing into the peers' buffers over NVLink). Needs two GPUs; skipped on a one-GPU box."""
 import os
 import socket
 
@@ -12,7 +13,7 @@ pytestmark = pytest.mark.gpu
 P = 2013265921
 
 
-def _worker(rank, world, port, q, height, width, b):
+def _worker(rank, world, port, q, height, width, b, fused):
     try:
         import torch.distributed as dist
         from openvm_b200 import B2Engine, FriParameters, sharded
@@ -24,7 +25,13 @@ def _worker(rank, world, port, q, height, width, b):
         trace = np.random.default_rng(9).integers(0, P, size=(height, width), dtype=np.uint64).astype(np.uint32)
         lo, hi = sharded.column_shards(width, world)[rank]
         local = dev.transport_matrix_to_device(np.ascontiguousarray(trace[:, lo:hi]))
-        root, spcs = sharded.sharded_commit(eng, local, width, b)
+        if fused:
+            committer = sharded.ShardedCommitter(eng, height, width, b)
+            root0, _ = committer.commit(local)          # a second commit on the same buffers must give the same tree
+            root, spcs = committer.commit(local)
+            assert [int(x) for x in root0] == [int(x) for x in root]
+        else:
+            root, spcs = sharded.sharded_commit(eng, local, width, b)
         torch.cuda.synchronize()
         rows = height << b
         indices = [0, 1, rows // 2 - 1, rows // 2, rows - 1, 12345 % rows]
@@ -40,6 +47,9 @@ def _worker(rank, world, port, q, height, width, b):
                 out["want_opened"][i] = (r_[0].tolist(), np.asarray(p_).tolist())
         dist.barrier()
         q.put(out)
+        if fused:
+            del spcs
+            committer.close()
         eng.close()
         dist.destroy_process_group()
     except Exception as ex:  # surface the failure in the parent
@@ -47,14 +57,15 @@ def _worker(rank, world, port, q, height, width, b):
         q.put({"rank": rank, "error": traceback.format_exc() + repr(ex)})
 
 
-@pytest.mark.parametrize("height,width,b", [(1 << 12, 19, 1), (1 << 18, 64, 1), (1 << 14, 9, 2)])
-def test_sharded_commit_two_gpus(height, width, b):
+@pytest.mark.parametrize("fused", [False, True], ids=["nccl_all_to_all", "fused_peer_stores"])
+@pytest.mark.parametrize("height,width,b", [(1 << 12, 19, 1), (1 << 18, 64, 1), (1 << 14, 9, 2), (4, 2, 1)])
+def test_sharded_commit_two_gpus(height, width, b, fused):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, q, height, width, b)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q, height, width, b, fused)) for r in range(2)]
     for p in procs: p.start()
     res = [q.get(timeout=600) for _ in range(2)]
     for p in procs: p.join(timeout=120)
