@@ -157,6 +157,9 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-proof", action="store_true")
+    ap.add_argument("--sharded", action="store_true",
+                    help="N > 1 only: also time ONE commitment of the same trace sharded across the N GPUs (strong scaling; "
+                         "openvm_b200/sharded.py, last NTT pass storing into the peers' buffers over NVLink)")
     ap.add_argument("--proof-scale-log", type=int, default=0, help="log2 scale of the shape-replay segment heights")
     ap.add_argument("--proof-engines", type=int, default=3,
                     help="engines proving concurrently on each GPU for the segments/s figure (one host thread each)")
@@ -402,6 +405,38 @@ def main():
                                    "sample": f"same segment with heights scaled by 2^-5 ({scells} main cells), oracle prover"}
             seg["main_cells_per_s"] = cells * seg["segments_per_s"]
 
+    # ---- opt-in: one commitment of the workload's trace across all ranks (strong scaling)
+    sharded_leg = None
+    if args.sharded and world > 1 and world & (world - 1) == 0:
+        from openvm_b200 import sharded
+        trace.free()
+        seng = B2Engine.new(FriParameters.standard_with_100_bits_conjectured_security(b), local_rank)
+        sdev = seng.device()
+        lo, hi = sharded.column_shards(width, world)[rank]
+        shard = sdev.alloc_matrix(H, hi - lo)
+        sdev.fill_synthetic(shard, 0xB200000000000001 + rank)
+        committer = sharded.ShardedCommitter(seng, H, width, b)
+        for _ in range(2):
+            sroot, spcs = committer.commit(shard)
+            del spcs
+        barrier()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        for _ in range(args.steps):
+            sroot, spcs = committer.commit(shard)
+            del spcs
+        s1.record()
+        barrier()
+        t = torch.tensor([s0.elapsed_time(s1) / args.steps], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        sms = float(t.item())
+        sharded_leg = {"what": "ONE commitment of the workload's trace, columns sharded over the ranks, rows exchanged by the last "
+                               "NTT pass storing into the peers' buffers over NVLink (no NCCL on the data path)",
+                       "scaling": "strong", "ms_per_commit": sms, "value": a_bytes / (sms * 1e-3) / 1e9, "unit": UNIT,
+                       "speedup_vs_one_gpu_step": ms_step / sms}
+        committer.close()
+        seng.close()
+
     if rank == 0:
         peak, peak_src = measured_peaks()
         steps = args.steps
@@ -453,6 +488,7 @@ def main():
                        "l2": "inputs (16 GiB trace, 32 GiB LDE) are far larger than the 126 MB L2; no flush needed",
                        "fri": {"log_blowup": b}},
             "roofline": roofline, "roofline_lde": roofline_lde, "int_pipe": int_pipe, "cpu_baseline": cpu,
+            "sharded_commit": sharded_leg,
             "e2e": e2e, "segment_proof": seg, "gpu_launches": int(launches), "clocks": clocks,
             "stage_ms_per_step": {"main_trace_commit_time_ms": met["commit_total_ms"] / steps,
                                   "lde_ms": lde_ms_step, "leaf_hash_ms": met["leaf_hash_ms"] / steps,
