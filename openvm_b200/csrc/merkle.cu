@@ -412,7 +412,9 @@ __global__ void __launch_bounds__(MIX_THREADS, 3) leaf_mixed_kernel(Cols src, ui
 static uint64_t mixed_min_rows() {  // B2S_HASH_MIN_LOG: log2 of the smallest level hashed by the two-pipe kernel
     static uint64_t v = [] {
         const char* env = getenv("B2S_HASH_MIN_LOG");
-        return env ? (uint64_t)1 << atoi(env) : MIX_MIN_ROWS;
+        if (!env) return MIX_MIN_ROWS;
+        const int l = atoi(env);
+        return (uint64_t)1 << (l < 5 ? 5 : (l > 40 ? 40 : l));   // a tile is 32 rows
     }();
     return v;
 }

@@ -15,6 +15,7 @@
 //   the 3-operation reduction dred where they would outgrow the product's domain.
 #pragma once
 #include "poseidon2.cuh"
+#include "field_f64.cuh"
 
 namespace b2 {
 
@@ -24,7 +25,6 @@ struct P2F64Tables {
     double diag[16];       // canonical internal diagonal
     double diag_over_p[16];
 };
-constexpr uint32_t C_RINV = c_inv(R_MOD_P);  // 2^-32 mod p: Montgomery word -> canonical value
 constexpr P2F64Tables make_p2_f64_tables() {
     P2F64Tables t{};
     constexpr uint32_t ext[8][16] = B2_P2_EXT_ALL;
@@ -43,31 +43,6 @@ constexpr P2F64Tables make_p2_f64_tables() {
 #if defined(__CUDACC__)
 static __constant__ P2F64Tables P2D = make_p2_f64_tables();
 
-constexpr double D_P = 2013265921.0;
-constexpr double D_INVP = 1.0 / 2013265921.0;
-constexpr double D_MAGIC = 6755399441055744.0;     // 1.5 * 2^52: x + MAGIC - MAGIC = round to nearest integer, |x| < 2^51
-constexpr double D_P_HIGH = 2013265920.0;          // p - 1 = 15 * 2^27: q * (p - 1) is exact for |q| < 2^49
-constexpr double D_2_52 = 4503599627370496.0;
-constexpr double D_RINV = (double)C_RINV;
-constexpr double D_RINV_OVER_P = (double)C_RINV / 2013265921.0;
-constexpr double D_R = (double)R_MOD_P;
-constexpr double D_R_OVER_P = (double)R_MOD_P / 2013265921.0;
-
-B2_D double dmod(double a, double b) {
-    const double h = a * b;
-    const double l = fma(a, b, -h);
-    const double q = fma(h, D_INVP, D_MAGIC) - D_MAGIC;
-    return fma(-q, D_P, h) + l;
-}
-// x * c mod p for a constant c < p with c_over_p = c / p;  |x| < 2^40
-B2_D double dmodc(double x, double c, double c_over_p) {
-    const double q = fma(x, c_over_p, D_MAGIC) - D_MAGIC;
-    return fma(x, c, -(q * D_P_HIGH)) - q;
-}
-B2_D double dred(double x) {  // |x| < 2^51 -> |r| <= p/2 + 1
-    const double q = fma(x, D_INVP, D_MAGIC) - D_MAGIC;
-    return fma(-q, D_P, x);
-}
 B2_D double dsbox(double x, double rc) {  // |x| < 2^40.5 -> |r| <= p/2 + 1
     const double y = x + rc;
     const double y2 = dmod(y, y), y3 = dmod(y2, y), y4 = dmod(y2, y2);
@@ -135,16 +110,6 @@ B2_D void poseidon2_permute_f64(double (&s)[16]) {
             for (int i = 0; i < 16; i++) s[i] = dsbox(s[i], P2D.ext[r][i]);
         }
     }
-}
-// Montgomery word of the integer code path <-> canonical double
-B2_D double f64_from_monty(uint32_t m) {
-    const double x = __hiloint2double(0x43300000, (int)m) - D_2_52;   // exact u32 -> double without a conversion instruction
-    return dmodc(x, D_RINV, D_RINV_OVER_P);
-}
-B2_D uint32_t f64_to_monty(double x) {  // |x| < 2^40
-    const double r = dmodc(x, D_R, D_R_OVER_P);
-    const double t = (r < 0.0 ? r + D_P : r) + D_2_52;
-    return (uint32_t)__double2loint(t);
 }
 #endif  // __CUDACC__
 

@@ -15,7 +15,7 @@
 //                         domain (= the first N*qd rows of the bit-reversed LDE), folds with alpha, divides by Z_H
 //   bary_weights_kernel   x_i / (z - x_i) for the N points of LDE block 0, once per (height, point)
 //   bary_dot_kernel       per column sum_i p(x_i) * weight_i  -> p(z)          (block per column x split)
-//   reduced_open_kernel   ro_h[row] += alpha^o * (sum_t alpha^t p_t(z) - sum_t alpha^t p_t(x)) / (z - x)
+//   reduced_open_height_kernel   ro_h[row] = sum over the matrices of height h of alpha^o * (sum_t alpha^t p_t(z) - sum_t alpha^t p_t(x)) / (z - x)
 //   fri_pack / fri_fold   commit-phase leaves (2 EF = 8 words per row) and the arity-2 fold with beta^2 roll-in
 //   pow_grind_kernel      parallel search for the minimum proof-of-work witness
 //   gather_rows_kernel    all query openings (rows and Merkle siblings) of all rounds in one launch
@@ -635,35 +635,48 @@ __global__ void __launch_bounds__(DOT_THREADS) bary_dot_kernel(const uint32_t* _
 }
 
 // ---- reduced openings ------------------------------------------------------------------------------------------------
-struct ReducedParams {
-    const uint32_t* mat;        // LDE matrix, column-major, height 2^h
-    uint32_t width, h;
-    const uint32_t* alpha_pows; // [>= width][4]
-    uint32_t* ro;               // 4 planes of 2^h
-    uint32_t npoints;
-    Fp4 z[2], cz[2], coef[2];   // point, sum_t alpha^t p_t(z), alpha^offset
-    uint32_t wh;                // generator of order 2^h
-};
-__global__ void __launch_bounds__(128) reduced_open_kernel(ReducedParams p) {
+// All matrices of one LDE height in one launch. Every matrix of height 2^h is opened at zeta and, for trace matrices, at
+// zeta * g_N (quotient chunks: zeta only), so the two inverses 1 / (z_j - x) -- an exponentiation for x and two extension
+// inversions, ~250 products, more than the column sums of a narrow matrix -- are paid once per row instead of once per
+// row and matrix, and ro is written once instead of read-modify-written per matrix (the segment proof had 40 launches).
+// Descriptor of matrix m (RO_DESC_WORDS words): pointer lo/hi, width, npoints, cz[2][4], coef[2][4].
+constexpr uint32_t RO_DESC_WORDS = 20;
+__global__ void __launch_bounds__(128) reduced_open_height_kernel(const uint32_t* __restrict__ descs, uint32_t nmats, uint32_t h,
+                                                                  const uint32_t* __restrict__ alpha_pows,
+                                                                  uint32_t* __restrict__ ro, Fp4 z0, Fp4 z1, uint32_t two_points,
+                                                                  uint32_t wh) {
     const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t H = 1u << p.h;
+    const uint32_t H = 1u << h;
     if (row >= H) return;
-    Fp4 inner = Fp4::zero();
-    for (uint32_t t = 0; t < p.width; t++) {
-        const Fp v = Fp::raw(__ldg(p.mat + (uint64_t)t * H + row));
-        const uint4 ap = __ldg(reinterpret_cast<const uint4*>(p.alpha_pows) + t);
-        inner.c[0] += v * Fp::raw(ap.x); inner.c[1] += v * Fp::raw(ap.y);
-        inner.c[2] += v * Fp::raw(ap.z); inner.c[3] += v * Fp::raw(ap.w);
-    }
-    const uint32_t e = p.h ? (__brev(row) >> (32 - p.h)) : 0u;
-    const Fp x = Fp::raw(M_GENERATOR) * fp_pow(Fp::raw(p.wh), e);
+    const uint32_t e = h ? (__brev(row) >> (32 - h)) : 0u;
+    const Fp x = Fp::raw(M_GENERATOR) * fp_pow(Fp::raw(wh), e);
+    const Fp4 inv0 = fp4_inv(z0 - x);
+    Fp4 inv1 = Fp4::zero();
+    if (two_points) inv1 = fp4_inv(z1 - x);
     Fp4 acc = Fp4::zero();
-    for (uint32_t j = 0; j < p.npoints; j++) acc += p.coef[j] * ((p.cz[j] - inner) * fp4_inv(p.z[j] - x));
-#pragma unroll
-    for (int c = 0; c < 4; c++) {
-        uint32_t* dst = p.ro + (uint64_t)c * H + row;
-        *dst = (Fp::raw(*dst) + acc.c[c]).v;
+#pragma unroll 1
+    for (uint32_t m = 0; m < nmats; m++) {
+        const uint32_t* __restrict__ d = descs + (uint64_t)m * RO_DESC_WORDS;
+        const uint32_t* __restrict__ mat = reinterpret_cast<const uint32_t*>(((uint64_t)__ldg(d + 1) << 32) | __ldg(d));
+        const uint32_t width = __ldg(d + 2), npoints = __ldg(d + 3);
+        Fp4 inner = Fp4::zero();
+        for (uint32_t t = 0; t < width; t++) {
+            const Fp v = Fp::raw(__ldg(mat + (uint64_t)t * H + row));
+            const uint4 ap = __ldg(reinterpret_cast<const uint4*>(alpha_pows) + t);
+            inner.c[0] += v * Fp::raw(ap.x); inner.c[1] += v * Fp::raw(ap.y);
+            inner.c[2] += v * Fp::raw(ap.z); inner.c[3] += v * Fp::raw(ap.w);
+        }
+        const Fp4 cz0(Fp::raw(__ldg(d + 4)), Fp::raw(__ldg(d + 5)), Fp::raw(__ldg(d + 6)), Fp::raw(__ldg(d + 7)));
+        const Fp4 cf0(Fp::raw(__ldg(d + 12)), Fp::raw(__ldg(d + 13)), Fp::raw(__ldg(d + 14)), Fp::raw(__ldg(d + 15)));
+        acc += cf0 * ((cz0 - inner) * inv0);
+        if (npoints > 1) {
+            const Fp4 cz1(Fp::raw(__ldg(d + 8)), Fp::raw(__ldg(d + 9)), Fp::raw(__ldg(d + 10)), Fp::raw(__ldg(d + 11)));
+            const Fp4 cf1(Fp::raw(__ldg(d + 16)), Fp::raw(__ldg(d + 17)), Fp::raw(__ldg(d + 18)), Fp::raw(__ldg(d + 19)));
+            acc += cf1 * ((cz1 - inner) * inv1);
+        }
     }
+#pragma unroll
+    for (int c = 0; c < 4; c++) ro[(uint64_t)c * H + row] = acc.c[c].v;
 }
 
 // ---- FRI commit phase ------------------------------------------------------------------------------------------------
@@ -1229,33 +1242,56 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     {
         uint64_t max_w = 1;
         for (auto& r : rounds) for (auto& m : r.mats) max_w = std::max<uint64_t>(max_w, m.lde->width);
-        uint32_t* d_apow = scratch.words((max_w + 1) * 4);
-        upload_ef_powers(e, d_apow, fri_alpha, max_w + 1);
+        // alpha^t for t up to the widest matrix; the host copy lives in the scratch until the proof is done
+        std::vector<uint32_t> apw((max_w + 1) * 4);
+        {
+            Fp4 pw = Fp4::one();
+            for (uint64_t t = 0; t <= max_w; t++) {
+                for (int c = 0; c < 4; c++) apw[4 * t + c] = pw.c[c].v;
+                pw = pw * fri_alpha;
+            }
+        }
+        const uint32_t* d_apow = scratch.upload(std::move(apw));
         std::map<unsigned, Fp4> alpha_pow;
+        struct HeightBatch { std::vector<uint32_t> descs; uint32_t nmats = 0; Fp4 z[2]; uint32_t npoints = 0; };
+        std::map<unsigned, HeightBatch> batches;
         for (auto& r : rounds)
             for (auto& m : r.mats) {
                 const unsigned h = m.log_n + b;
                 if (!ro.count(h)) {
                     ro[h] = scratch.words((size_t)4 << h);
-                    B2_CUDA(cudaMemsetAsync(ro[h], 0, (size_t)16 << h, e->stream));
                     alpha_pow[h] = Fp4::one();
                 }
-                ReducedParams rp{};
-                rp.mat = m.lde->d; rp.width = (uint32_t)m.lde->width; rp.h = h;
-                rp.alpha_pows = d_apow; rp.ro = ro[h]; rp.npoints = (uint32_t)m.points.size();
-                rp.wh = two_adic_generator(h).v;
+                HeightBatch& hb = batches[h];
+                B2_REQUIRE(m.points.size() >= 1 && m.points.size() <= 2, B2S_ERR_INTERNAL, "prove: a matrix is opened at 1 or 2 points");
+                for (size_t j = 0; j < m.points.size(); j++) {
+                    if (hb.npoints <= j) { hb.z[j] = m.points[j]; hb.npoints = (uint32_t)j + 1; }
+                    B2_REQUIRE(hb.z[j] == m.points[j], B2S_ERR_INTERNAL, "prove: matrices of one height share their opening points");
+                }
+                const uint64_t mp = (uint64_t)(uintptr_t)m.lde->d;
+                uint32_t d[RO_DESC_WORDS] = {(uint32_t)mp, (uint32_t)(mp >> 32), (uint32_t)m.lde->width, (uint32_t)m.points.size()};
                 Fp4 aw = Fp4::one();
                 for (uint64_t t = 0; t < m.lde->width; t++) aw = aw * fri_alpha;
                 for (size_t j = 0; j < m.points.size(); j++) {
                     Fp4 cz = Fp4::zero(), ap = Fp4::one();
                     for (auto& v : m.values[j]) { cz += v * ap; ap = ap * fri_alpha; }
-                    rp.z[j] = m.points[j]; rp.cz[j] = cz; rp.coef[j] = alpha_pow[h];
+                    for (int c = 0; c < 4; c++) { d[4 + 4 * j + c] = cz.c[c].v; d[12 + 4 * j + c] = alpha_pow[h].c[c].v; }
                     alpha_pow[h] = alpha_pow[h] * aw;
                 }
-                reduced_open_kernel<<<((1u << h) + 127) / 128, 128, 0, e->stream>>>(rp);
-                B2_CHECK_LAUNCH();
-                e->launches[3]++;
+                hb.descs.insert(hb.descs.end(), d, d + RO_DESC_WORDS);
+                hb.nmats++;
             }
+        for (auto& kv : batches) {
+            const unsigned h = kv.first;
+            HeightBatch& hb = kv.second;
+            const uint32_t nm = hb.nmats;
+            const uint32_t* d_descs = scratch.upload(std::move(hb.descs));
+            reduced_open_height_kernel<<<((1u << h) + 127) / 128, 128, 0, e->stream>>>(
+                d_descs, nm, h, d_apow, ro[h], hb.z[0], hb.npoints > 1 ? hb.z[1] : Fp4::zero(), hb.npoints > 1 ? 1u : 0u,
+                two_adic_generator(h).v);
+            B2_CHECK_LAUNCH();
+            e->launches[3]++;
+        }
     }
 
     trace.mark("reduced openings");

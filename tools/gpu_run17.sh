@@ -1,0 +1,11 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest17.log 2>&1; echo pytest rc=$?; tail -3 gpurun_out/pytest17.log
+B2S_PROVE_TRACE=1 timeout 600 python tools/leaf_shape.py 0 3 2>&1 | grep -E "proof 2|reduced|ood values|accepted" | tail -5
+timeout 600 python tools/keccak_shape.py 2>&1 | tail -2
+timeout 600 python bench.py --log-height 12 --steps 3 --warmup 1 --no-cpu --no-e2e > gpurun_out/b17.json 2>/dev/null
+python - <<PY
+import json
+d=json.loads(open('gpurun_out/b17.json').read().strip().splitlines()[-1])
+print('segment', d['segment_proof']['device_ms_per_proof'], d['segment_proof']['segments_per_s'], d['segment_proof']['stage_ms'])
+PY
