@@ -167,6 +167,17 @@ B2_HD Fp4 fp4_inv(const Fp4& a) {
     return prod * fp_inv(n.c[0]);
 }
 
+// two inverses for one base-field inversion (the exponentiation is most of fp4_inv)
+B2_HD void fp4_inv_pair(const Fp4& a, const Fp4& b, Fp4& ia, Fp4& ib) {
+    Fp4 a1 = fp4_frobenius(a), a2 = fp4_frobenius(a1), a3 = fp4_frobenius(a2);
+    Fp4 b1 = fp4_frobenius(b), b2 = fp4_frobenius(b1), b3 = fp4_frobenius(b2);
+    const Fp4 pa = a1 * a2 * a3, pb = b1 * b2 * b3;
+    const Fp na = (a * pa).c[0], nb = (b * pb).c[0];
+    const Fp t = fp_inv(na * nb);
+    ia = pa * (nb * t);
+    ib = pb * (na * t);
+}
+
 B2_HD uint32_t bitrev32(uint32_t x, unsigned bits) {
 #if defined(__CUDA_ARCH__)
     return bits ? (__brev(x) >> (32 - bits)) : 0u;

@@ -639,6 +639,8 @@ __global__ void __launch_bounds__(DOT_THREADS) bary_dot_kernel(const uint32_t* _
 // zeta * g_N (quotient chunks: zeta only), so the two inverses 1 / (z_j - x) -- an exponentiation for x and two extension
 // inversions, ~250 products, more than the column sums of a narrow matrix -- are paid once per row instead of once per
 // row and matrix, and ro is written once instead of read-modify-written per matrix (the segment proof had 40 launches).
+// The kernel is bound by its products (leaf-aggregation shape: ~27 G for the per-row part, ~24 G for the column sums, ~10 G
+// per (matrix, row)): batching the loads or moving the column sums to FP64 dot products did not change its 20 ms.
 // Descriptor of matrix m (RO_DESC_WORDS words): pointer lo/hi, width, npoints, cz[2][4], coef[2][4].
 constexpr uint32_t RO_DESC_WORDS = 20;
 __global__ void __launch_bounds__(128) reduced_open_height_kernel(const uint32_t* __restrict__ descs, uint32_t nmats, uint32_t h,
@@ -650,10 +652,11 @@ __global__ void __launch_bounds__(128) reduced_open_height_kernel(const uint32_t
     if (row >= H) return;
     const uint32_t e = h ? (__brev(row) >> (32 - h)) : 0u;
     const Fp x = Fp::raw(M_GENERATOR) * fp_pow(Fp::raw(wh), e);
-    const Fp4 inv0 = fp4_inv(z0 - x);
-    Fp4 inv1 = Fp4::zero();
-    if (two_points) inv1 = fp4_inv(z1 - x);
-    Fp4 acc = Fp4::zero();
+    Fp4 inv0, inv1 = Fp4::zero();
+    if (two_points) fp4_inv_pair(z0 - x, z1 - x, inv0, inv1);
+    else inv0 = fp4_inv(z0 - x);
+    // per point: sum over the matrices of alpha^o (cz - inner); the division by (z_j - x) is applied once at the end
+    Fp4 acc0 = Fp4::zero(), acc1 = Fp4::zero();
 #pragma unroll 1
     for (uint32_t m = 0; m < nmats; m++) {
         const uint32_t* __restrict__ d = descs + (uint64_t)m * RO_DESC_WORDS;
@@ -668,13 +671,15 @@ __global__ void __launch_bounds__(128) reduced_open_height_kernel(const uint32_t
         }
         const Fp4 cz0(Fp::raw(__ldg(d + 4)), Fp::raw(__ldg(d + 5)), Fp::raw(__ldg(d + 6)), Fp::raw(__ldg(d + 7)));
         const Fp4 cf0(Fp::raw(__ldg(d + 12)), Fp::raw(__ldg(d + 13)), Fp::raw(__ldg(d + 14)), Fp::raw(__ldg(d + 15)));
-        acc += cf0 * ((cz0 - inner) * inv0);
+        acc0 += cf0 * (cz0 - inner);
         if (npoints > 1) {
             const Fp4 cz1(Fp::raw(__ldg(d + 8)), Fp::raw(__ldg(d + 9)), Fp::raw(__ldg(d + 10)), Fp::raw(__ldg(d + 11)));
             const Fp4 cf1(Fp::raw(__ldg(d + 16)), Fp::raw(__ldg(d + 17)), Fp::raw(__ldg(d + 18)), Fp::raw(__ldg(d + 19)));
-            acc += cf1 * ((cz1 - inner) * inv1);
+            acc1 += cf1 * (cz1 - inner);
         }
     }
+    Fp4 acc = acc0 * inv0;
+    if (two_points) acc += acc1 * inv1;
 #pragma unroll
     for (int c = 0; c < 4; c++) ro[(uint64_t)c * H + row] = acc.c[c].v;
 }
