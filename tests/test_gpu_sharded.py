@@ -82,3 +82,59 @@ def test_sharded_commit_two_gpus(height, width, b, fused):
             assert row == wrow and path == wpath, (r["rank"], i)
             seen += 1
     assert seen == len(want["want_opened"])      # every index was answered by exactly one rank
+
+
+@pytest.mark.parametrize("height,width,b,peers", [(1 << 10, 7, 1, 1), (1 << 12, 19, 1, 4), (1 << 15, 5, 2, 8), (1 << 14, 33, 1, 2), (4, 3, 1, 2)])
+def test_lde_scatter_layout_one_gpu(engine, engine_b2, height, width, b, peers):
+    """b2s_coset_lde_scatter on ONE GPU: the "peers" are buffers of this process (b2s_shared_alloc), so the row-block layout
+    the last NTT pass writes -- rank g gets LDE rows [g R, (g+1) R) of every column, column-major R x total_width, columns at
+    their global index -- is checked against b2s_coset_lde without a second GPU. Two column shards are scattered one after
+    the other, as two ranks would."""
+    import ctypes as C
+    e = engine if b == 1 else engine_b2
+    dev = e.device()
+    rng = np.random.default_rng(21)
+    trace = rng.integers(0, P, size=(height, width), dtype=np.uint64).astype(np.uint32)
+    want = dev.coset_lde(dev.transport_matrix_to_device(trace), b).to_host()       # (rows, width) canonical
+    rows = height << b
+    r = rows // peers
+    bufs = []
+    for _ in range(peers):
+        ptr, handle = C.c_void_p(), C.create_string_buffer(64)
+        e._check(e._lib.b2s_shared_alloc(e._h, r * width * 4, C.byref(ptr), handle))
+        bufs.append(ptr.value)
+    try:
+        arr = (C.c_void_p * peers)(*bufs)
+        split = max(1, width // 3)
+        for lo, hi in ((0, split), (split, width)):
+            if hi > lo:
+                shard = dev.transport_matrix_to_device(np.ascontiguousarray(trace[:, lo:hi]))
+                e._check(e._lib.b2s_coset_lde_scatter(e._h, shard._h, b, 1, arr, peers, width, lo))
+        e.synchronize()
+        for g in range(peers):
+            block = dev.adopt_device_matrix(bufs[g], r, width).to_host()
+            assert np.array_equal(block, want[g * r:(g + 1) * r]), g
+    finally:
+        e.synchronize()
+        for pbuf in bufs:
+            e._check(e._lib.b2s_shared_free(e._h, pbuf))
+
+
+def test_lde_scatter_rejects_bad_arguments(engine):
+    import ctypes as C
+    from openvm_b200 import B2StarkError
+    e = engine
+    dev = e.device()
+    m = dev.transport_matrix_to_device(np.ones((8, 2), dtype=np.uint32))
+    ptr, handle = C.c_void_p(), C.create_string_buffer(64)
+    e._check(e._lib.b2s_shared_alloc(e._h, 4096, C.byref(ptr), handle))
+    try:
+        one = (C.c_void_p * 3)(ptr.value, ptr.value, ptr.value)
+        with pytest.raises(B2StarkError):   # three peers: not a power of two
+            e._check(e._lib.b2s_coset_lde_scatter(e._h, m._h, 1, 1, one, 3, 2, 0))
+        with pytest.raises(B2StarkError):   # shard outside the trace
+            e._check(e._lib.b2s_coset_lde_scatter(e._h, m._h, 1, 1, one, 1, 2, 1))
+        with pytest.raises(B2StarkError):   # fewer than 4 rows per peer
+            e._check(e._lib.b2s_coset_lde_scatter(e._h, m._h, 1, 1, (C.c_void_p * 8)(*([ptr.value] * 8)), 8, 2, 0))
+    finally:
+        e._check(e._lib.b2s_shared_free(e._h, ptr.value))
