@@ -470,6 +470,13 @@ def main():
             "poseidon2_perm_per_s_register_peak": perm_peak,
             "modmul_per_s_peak": nthreads * 4096 * 8 / (mms * 1e-3),
         }
+        # the bound that explains the time (profiles/r1j_dispatch_probe.md): S-box products of the hashing
+        # (564 per permutation) and butterflies of the LDE (one product each) against the measured product rate
+        int_pipe["hash_products_per_s"] = int_pipe["poseidon2_perm_per_s"] * 564
+        int_pipe["hash_frac_of_modmul_peak"] = int_pipe["hash_products_per_s"] / int_pipe["modmul_per_s_peak"]
+        butterflies = (1 + (1 << b)) * 0.5 * H * log_h * width
+        int_pipe["lde_butterflies_per_s"] = butterflies / (lde_ms_step * 1e-3)
+        int_pipe["lde_frac_of_modmul_peak"] = int_pipe["lde_butterflies_per_s"] / int_pipe["modmul_per_s_peak"]
         cpu = None
         if not args.no_cpu:
             os.sched_setaffinity(0, all_cpus)
