@@ -431,18 +431,20 @@ static int mixed_int_warps() {
 template <class Cols, bool PREV>
 static void launch_mixed_as(b2s_engine* e, Cols src, uint32_t ncols, uint64_t n, const uint32_t* state_in, uint32_t* state_out,
                             uint32_t* out, const uint32_t* prev) {
-    static int blocks_per_sm = 0, sms = 0;
-    if (!blocks_per_sm) {
-        B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, leaf_mixed_kernel<Cols, PREV>, MIX_THREADS, 0));
-        int dev = 0;
-        B2_CUDA(cudaGetDevice(&dev));
-        B2_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        if (blocks_per_sm < 1) blocks_per_sm = 1;
-    }
+    // resident blocks of the whole chip, computed once (thread-safe: engines on several host threads share this)
+    static const unsigned resident = [] {
+        int per_sm = 0, dev = 0, sms = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, leaf_mixed_kernel<Cols, PREV>, MIX_THREADS, 0) != cudaSuccess ||
+            cudaGetDevice(&dev) != cudaSuccess ||
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+            return 0u;
+        return (unsigned)(sms * (per_sm < 1 ? 1 : per_sm));
+    }();
+    B2_REQUIRE(resident > 0, B2S_ERR_INTERNAL, "leaf hash: occupancy query failed");
     if (!e->tile_ctr) e->tile_ctr = (unsigned*)e->dmalloc(256);
     B2_CUDA(cudaMemsetAsync(e->tile_ctr, 0, 4, e->stream));
     const uint64_t want = (n >> 5) / (MIX_THREADS / 32) + 1;  // no more blocks than tiles / warps
-    const unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)sms * blocks_per_sm, want);
+    const unsigned grid = (unsigned)std::min<uint64_t>(resident, want);
     leaf_mixed_kernel<Cols, PREV><<<grid, MIX_THREADS, 0, e->stream>>>(src, ncols, n, state_in, state_out, out, prev, e->tile_ctr,
                                                                        mixed_int_warps());
 }
