@@ -232,6 +232,14 @@ int32_t b2s_engine_set_pow_witnesses(b2s_engine* e, uint32_t logup_witness, uint
  * (InvalidProofShape, InvalidOpeningArgument, InvalidPowWitness, NonZeroCumulativeSum, OodEvaluationMismatch ...). */
 int32_t b2s_verify(b2s_engine* e, const b2s_pk* pk, const uint8_t* proof_bytes, size_t proof_len);
 
+/* Proof -> hint stream of the recursive verifier: what the next aggregation layer feeds its verifier program
+ * (`proof.write()` of `Hintable for Proof<BabyBearPoseidon2Config>`, extensions/native/recursion/src/hints.rs:272-316,
+ * fri/hints.rs:22-163; consumed at crates/sdk/src/prover/agg.rs:307-321). Host-only; `e` may be NULL (then no message
+ * is kept for b2s_last_error). Output, released with b2s_free: n_vectors, then per vector its length and its canonical
+ * words. Fails with B2S_ERR_VERIFY_FAILED (InvalidProofShape) on bytes that do not decode. */
+int32_t b2s_proof_hint_stream(b2s_engine* e, const uint8_t* proof_bytes, size_t proof_len, uint32_t** words,
+                              size_t* n_words);
+
 /* The quotient kernels of an AIR are generated as PTX from its constraint DAG when the key is loaded and compiled by
  * the driver (openvm_b200/csrc/qjit.cu; B2S_QUOTIENT_JIT=0 selects the interpreter instead). This entry point returns
  * that PTX text for AIR `air_index` of a key blob without touching a device (release with b2s_free): tests assemble

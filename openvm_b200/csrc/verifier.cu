@@ -495,4 +495,106 @@ void verify(const b2s_engine* e, const b2s_pk* pk, const uint8_t* bytes, size_t 
     }
 }
 
+// ---- proof -> hint stream of the recursive verifier -------------------------------------------------------------------
+// The next aggregation layer reads a proof through `hint` instructions; the stream is what `Hintable::write` produces
+// for Proof<BabyBearPoseidon2Config> (extensions/native/recursion/src/hints.rs:272-316 and the impls it calls:
+// hints.rs:71-266,318-444, fri/hints.rs:22-163; used by crates/sdk/src/prover/agg.rs:307-321): a sequence of vectors of
+// field elements. Layout rules followed here, in the reference's words:
+//   usize / Val            one vector of one word                      (hints.rs:71-94)
+//   Challenge              four vectors of one word                    (hints.rs:97-112)
+//   Vec<usize>, Vec<Val>   ONE vector with all words, no length        (hints.rs:156-198)
+//   Vec<Challenge>         [len], then one vector of 4 len words       (hints.rs:200-216)
+//   Vec<T> otherwise       [len], then every element's own stream      (hints.rs:134-154)
+//   digest                 eight vectors of one word                   (fri/hints.rs:22-36)
+//   opening proof          [number of digests], then one flat vector   (fri/hints.rs:157-162)
+//   batch opening          [total words], one flat vector of the opened rows, then its opening proof (fri/hints.rs:124-150)
+// Output: n_vectors, then per vector its length and its canonical words.
+namespace {
+struct HintWriter {
+    std::vector<uint32_t> out;
+    uint32_t vectors = 0;
+    HintWriter() { out.push_back(0); }
+    void one(uint32_t x) { out.push_back(1); out.push_back(x); vectors++; }
+    void begin(size_t n) { out.push_back((uint32_t)n); vectors++; }
+    void f(Fp x) { one(x.to_canonical()); }
+    void ef(const Fp4& e) { for (int c = 0; c < 4; c++) f(e.c[c]); }
+    void digest(const Digest& d) { for (int i = 0; i < 8; i++) f(d[i]); }
+    void digests(const std::vector<Digest>& v) { one((uint32_t)v.size()); for (auto& d : v) digest(d); }
+    void efs(const std::vector<Fp4>& v) {
+        one((uint32_t)v.size());
+        begin(4 * v.size());
+        for (auto& e : v) for (int c = 0; c < 4; c++) out.push_back(e.c[c].to_canonical());
+    }
+    void opening_proof(const std::vector<Digest>& v) {
+        one((uint32_t)v.size());
+        begin(8 * v.size());
+        for (auto& d : v) for (int i = 0; i < 8; i++) out.push_back(d[i].to_canonical());
+    }
+    void adj(const AdjacentOpened& a) { efs(a.local); efs(a.next); }
+    void adjs(const std::vector<AdjacentOpened>& v) { one((uint32_t)v.size()); for (auto& a : v) adj(a); }
+};
+}  // namespace
+
+std::vector<uint32_t> proof_hint_stream(const uint8_t* bytes, size_t len) {
+    const DecodedProof p = decode(bytes, len);
+    HintWriter w;
+    // Commitments (hints.rs:417-444)
+    w.digests(p.main_commits);
+    w.digests(p.after_commits);
+    w.digest(p.quotient_commit);
+    // OpeningProof = FriProof, then OpenedValues (hints.rs:344-366)
+    w.digests(p.fri_commits);                                   // fri/hints.rs:101-122
+    w.one((uint32_t)p.queries.size());
+    for (auto& q : p.queries) {                                  // fri/hints.rs:64-88
+        w.one((uint32_t)q.input_proof.size());
+        for (auto& b : q.input_proof) {
+            size_t total = 0;
+            for (auto& row : b.opened_values) total += row.size();
+            w.one((uint32_t)total);
+            w.begin(total);
+            for (auto& row : b.opened_values) for (Fp x : row) w.out.push_back(x.to_canonical());
+            w.opening_proof(b.opening_proof);
+        }
+        w.one((uint32_t)q.commit_phase_openings.size());
+        for (auto& s : q.commit_phase_openings) {                // fri/hints.rs:38-60
+            w.ef(s.sibling_value);
+            w.opening_proof(s.opening_proof);
+        }
+    }
+    w.efs(p.final_poly);
+    w.f(p.pow_witness);
+    // OpenedValues: preprocessed, main, QUOTIENT, after_challenge (hints.rs:368-398; not the wire order)
+    w.adjs(p.opened_prep);
+    w.one((uint32_t)p.opened_main.size());
+    for (auto& part : p.opened_main) w.adjs(part);
+    w.one((uint32_t)p.opened_quotient.size());
+    for (auto& air : p.opened_quotient) {
+        w.one((uint32_t)air.size());
+        for (auto& chunk : air) w.efs(chunk);
+    }
+    w.one((uint32_t)p.opened_after.size());
+    for (auto& ph : p.opened_after) w.adjs(ph);
+    // per_air (hints.rs:318-342): air_id, log2(degree), exposed values, public values as one vector
+    w.one((uint32_t)p.per_air.size());
+    for (auto& a : p.per_air) {
+        if (a.degree == 0 || (a.degree & (a.degree - 1))) reject("InvalidProofShape: degree is not a power of two");
+        w.one(a.air_id);
+        w.one(log2_exact(a.degree));
+        w.one((uint32_t)a.exposed.size());
+        for (auto& v : a.exposed) w.efs(v);
+        w.begin(a.public_values.size());
+        for (Fp x : a.public_values) w.out.push_back(x.to_canonical());
+    }
+    // air_perm_by_height: indices stably sorted by descending degree, one vector (hints.rs:302-305)
+    std::vector<uint32_t> perm(p.per_air.size());
+    for (size_t i = 0; i < perm.size(); i++) perm[i] = (uint32_t)i;
+    std::stable_sort(perm.begin(), perm.end(), [&](uint32_t x, uint32_t y) { return p.per_air[x].degree > p.per_air[y].degree; });
+    w.begin(perm.size());
+    for (uint32_t i : perm) w.out.push_back(i);
+    // logup proof-of-work witness, 0 when the proof has no challenge phase (hints.rs:306-312)
+    w.one(p.has_logup_witness ? p.logup_witness.to_canonical() : 0u);
+    w.out[0] = w.vectors;
+    return w.out;
+}
+
 }  // namespace b2

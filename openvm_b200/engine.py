@@ -360,6 +360,20 @@ class B2Engine:
             raise VerificationError((self._lib.b2s_last_error(self._h) or b"").decode())
         self._check(st)
 
+    def proof_hint_stream(self, proof):
+        """`proof.write()` of the recursive verifier's Hintable (extensions/native/recursion/src/hints.rs:272-316): the list
+        of field-element vectors the next aggregation layer hints to its verifier program (crates/sdk/src/prover/agg.rs:307-321)."""
+        words, n = C.POINTER(C.c_uint32)(), C.c_size_t()
+        self._check(self._lib.b2s_proof_hint_stream(self._h, bytes(proof), len(proof), C.byref(words), C.byref(n)))
+        flat = np.ctypeslib.as_array(words, shape=(n.value,)).copy()
+        self._lib.b2s_free(words)
+        out, i = [], 1
+        for _ in range(int(flat[0])):
+            ln = int(flat[i])
+            out.append(flat[i + 1:i + 1 + ln].copy())
+            i += 1 + ln
+        return out
+
     def set_pow_witnesses(self, logup_witness=None, fri_witness=None):
         """Replay aid: use the given proof-of-work witnesses instead of searching for the minimum ones."""
         s = 0xFFFFFFFF

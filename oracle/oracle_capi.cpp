@@ -143,6 +143,7 @@ void orc_fill_synthetic(uint32_t* out, uint64_t height, uint64_t width, uint64_t
 
 // ---- STARK prove / verify (oracle/stark.hpp, oracle/stark_verify.hpp) -------------------------------------
 #include "stark_verify.hpp"
+#include "hints.hpp"
 static std::string g_orc_error;
 extern "C" {
 const char* orc_last_error() { return g_orc_error.c_str(); }
@@ -209,4 +210,24 @@ void orc_challenger_run(const uint32_t* obs, size_t n_obs, uint32_t* samples, si
     for (size_t i = 0; i < n_obs; i++) ch.observe(F(obs[i]));
     for (size_t i = 0; i < n_samples; i++) samples[i] = ch.sample().v;
 }
+// proof bytes -> hint stream (oracle/hints.hpp), flattened as n_vectors, then per vector its length and words
+int orc_proof_hint_stream(const uint8_t* proof, size_t len, uint32_t** words_out, size_t* n_out) {
+    try {
+        const Stream st = hint_stream(decode_proof(proof, len));
+        std::vector<uint32_t> flat;
+        flat.push_back((uint32_t)st.size());
+        for (auto& v : st) {
+            flat.push_back((uint32_t)v.size());
+            flat.insert(flat.end(), v.begin(), v.end());
+        }
+        *words_out = (uint32_t*)malloc(flat.size() * 4 + 4);
+        memcpy(*words_out, flat.data(), flat.size() * 4);
+        *n_out = flat.size();
+        return 0;
+    } catch (const std::exception& ex) {
+        g_orc_error = ex.what();
+        return -1;
+    }
+}
+
 }

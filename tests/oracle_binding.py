@@ -172,6 +172,18 @@ class Oracle:
         rc = self.lib.orc_stark_verify(key.ctypes.data, key.size, buf, len(proof), log_blowup, num_queries, pow_bits)
         return None if rc == 0 else self.lib.orc_last_error().decode()
 
+    def proof_hint_stream(self, proof):
+        """Proof bytes -> list of vectors (lists of canonical words): oracle/hints.hpp."""
+        buf = (C.c_uint8 * len(proof)).from_buffer_copy(proof)
+        words, n = C.POINTER(C.c_uint32)(), C.c_size_t()
+        self.lib.orc_proof_hint_stream.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.POINTER(C.c_uint32)), C.POINTER(C.c_size_t)]
+        rc = self.lib.orc_proof_hint_stream(buf, len(proof), C.byref(words), C.byref(n))
+        if rc != 0:
+            raise ValueError(self.lib.orc_last_error().decode())
+        flat = np.ctypeslib.as_array(words, shape=(n.value,)).copy()
+        self.lib.orc_free(words)
+        return unflatten_stream(flat)
+
     def challenger_run(self, observed, n_samples):
         obs = np.ascontiguousarray(observed, dtype=np.uint32)
         out = np.zeros(n_samples, dtype=np.uint32)
@@ -193,3 +205,15 @@ def load():
         build()
         _oracle = Oracle(C.CDLL(LIB))
     return _oracle
+
+
+def unflatten_stream(flat):
+    """n_vectors, then per vector its length and words -> list of lists"""
+    flat = [int(x) for x in flat]
+    out, i = [], 1
+    for _ in range(flat[0]):
+        ln = flat[i]
+        out.append(flat[i + 1:i + 1 + ln])
+        i += 1 + ln
+    assert i == len(flat)
+    return out

@@ -124,6 +124,8 @@ def check_same(orc, eng, key, inputs, air_objs, b, queries, pow_bits, expect=Non
     else:
         assert expect in res and expect in mine
     assert proof == orc.stark_prove(key, inputs, b, queries, pow_bits)
+    # what the next aggregation layer would be fed: the hint stream of the device-made proof (hints.rs:272-316)
+    assert [list(map(int, v)) for v in eng.proof_hint_stream(proof)] == orc.proof_hint_stream(proof)
     return proof
 
 
