@@ -18,12 +18,18 @@ FLAGS = [
 
 
 def sources():
-    return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cu"))
+    return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cu") or f.endswith(".cpp"))
+
+
+def flags_for(src):
+    if src.endswith(".cpp"):   # host-only translation units (AVX2 transcript hashing): the host compiler through nvcc
+        return ["-O3", "-std=c++17", "-Xcompiler", "-fPIC,-mavx2"]
+    return FLAGS
 
 
 def deps():
     out = sources()
-    out += [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")]
+    out += [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh") or f.endswith(".hpp")]
     out.append(os.path.join(HERE, "..", "include", "b2stark.h"))
     return out
 
@@ -42,8 +48,8 @@ def build(force=False, verbose=False):
     objs = []
     procs = []
     for src in sources():
-        obj = os.path.join(LIB_DIR, os.path.basename(src)[:-3] + ".o")
-        cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+        obj = os.path.join(LIB_DIR, os.path.splitext(os.path.basename(src))[0] + ".o")
+        cmd = [NVCC] + flags_for(src) + (["-Xptxas", "-v"] if verbose and src.endswith(".cu") else []) + ["-c", src, "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
         objs.append(obj)
     failed = False

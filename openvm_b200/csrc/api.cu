@@ -32,6 +32,18 @@ void b2s_engine::dfree(void* p, size_t bytes) {
     cudaFreeAsync(p, stream);
     mem_in_use -= bytes;
 }
+void* b2s_engine::host_pinned(size_t bytes) {
+    if (bytes > pinned_bytes) {
+        B2_CUDA(cudaStreamSynchronize(stream));   // nothing may still be landing in the old buffer
+        if (pinned) B2_CUDA(cudaFreeHost(pinned));
+        pinned = nullptr;
+        pinned_bytes = 0;
+        const size_t want = std::max<size_t>(bytes + bytes / 2, (size_t)1 << 20);
+        B2_CUDA(cudaMallocHost(&pinned, want));
+        pinned_bytes = want;
+    }
+    return pinned;
+}
 cudaEvent_t b2s_engine::get_event() {
     if (!event_pool.empty()) {
         cudaEvent_t ev = event_pool.back();
@@ -266,6 +278,7 @@ void b2s_engine_free(b2s_engine* e) {
         free_twiddles(e);
         free_scales(e);
         if (e->tile_ctr) e->dfree(e->tile_ctr, 256);
+        if (e->pinned) cudaFreeHost(e->pinned);
         free_selectors(e);
     } catch (...) {
     }

@@ -72,6 +72,9 @@ struct b2s_engine {
     std::map<uint64_t, b2::ScaleSet*> scales;      // by (logn, log_blowup, shift_in)
     unsigned* tile_ctr = nullptr;                  // work counter of the persistent leaf-hash kernel (merkle.cu)
 
+    void* pinned = nullptr;                        // grow-only pinned host buffer for small asynchronous read-backs
+    size_t pinned_bytes = 0;
+    void* host_pinned(size_t bytes);
     void* dmalloc(size_t bytes);
     void dfree(void* p, size_t bytes);
     cudaEvent_t get_event();

@@ -8,6 +8,11 @@
 #pragma once
 #include "field.cuh"
 #include "poseidon2_constants.cuh"
+#include <cstdlib>
+
+// host_poseidon2_avx2.cpp: the same permutation eight lanes at a time
+extern "C" int b2_host_has_avx2();
+extern "C" void b2_poseidon2_permute_avx2(uint32_t* state16);
 
 namespace b2 {
 
@@ -31,6 +36,15 @@ struct HostPoseidon2 {
         for (int i = 0; i < 16; i++) s[i] += sums[i & 3];
     }
     void permute(Fp* s) const {
+        static const bool avx2 = b2_host_has_avx2() != 0 && !getenv("B2S_HOST_SCALAR");
+        if (avx2) {
+            static_assert(sizeof(Fp) == 4, "Fp is one Montgomery word");
+            b2_poseidon2_permute_avx2(reinterpret_cast<uint32_t*>(s));
+            return;
+        }
+        permute_scalar(s);
+    }
+    void permute_scalar(Fp* s) const {
         external(s);
         for (int r = 0; r < 4; r++) {
             for (int i = 0; i < 16; i++) s[i] = sbox(s[i] + Fp::raw(ext[r][i]));

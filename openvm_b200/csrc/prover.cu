@@ -634,6 +634,21 @@ __global__ void __launch_bounds__(DOT_THREADS) bary_dot_kernel(const uint32_t* _
     if (threadIdx.x < 4) partial[((uint64_t)col * splits + split) * 4 + threadIdx.x] = sm[threadIdx.x][0];
 }
 
+// p(z) for every column of one (matrix, point): sums the splits' partial dot products and applies the barycentric factor
+// ((z/g)^N - 1) / N, so that the host receives finished values (it only hashes them into the transcript)
+__global__ void bary_finish_kernel(const uint32_t* __restrict__ partial, uint32_t width, uint32_t splits, Fp4 scale,
+                                   uint32_t* __restrict__ vals) {
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= width) return;
+    Fp4 s = Fp4::zero();
+    for (uint32_t sp = 0; sp < splits; sp++) {
+        const uint4 q = *reinterpret_cast<const uint4*>(partial + ((uint64_t)c * splits + sp) * 4);
+        s.c[0] += Fp::raw(q.x); s.c[1] += Fp::raw(q.y); s.c[2] += Fp::raw(q.z); s.c[3] += Fp::raw(q.w);
+    }
+    s = s * scale;
+    *reinterpret_cast<uint4*>(vals + (uint64_t)c * 4) = make_uint4(s.c[0].v, s.c[1].v, s.c[2].v, s.c[3].v);
+}
+
 // ---- reduced openings ------------------------------------------------------------------------------------------------
 // All matrices of one LDE height in one launch. Every matrix of height 2^h is opened at zeta and, for trace matrices, at
 // zeta * g_N (quotient chunks: zeta only), so the two inverses 1 / (z_j - x) -- an exponentiation for x and two extension
@@ -1193,51 +1208,56 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             }
             return slot[which];
         };
-        struct Job { size_t r, m, p; uint32_t splits; size_t off; };
+        struct Job { size_t r, m, p; uint32_t splits; size_t off, voff; cudaEvent_t done; };
         std::vector<Job> jobs;
-        size_t partial_words = 0;
+        size_t partial_words = 0, val_words = 0;
         for (size_t r = 0; r < rounds.size(); r++)
             for (size_t m = 0; m < rounds[r].mats.size(); m++)
                 for (size_t p = 0; p < rounds[r].mats[m].points.size(); p++) {
                     const RoundMat& rm = rounds[r].mats[m];
                     uint32_t splits = (uint32_t)std::min<uint64_t>(64, std::max<uint64_t>(1, ((uint64_t)1 << rm.log_n) / 4096));
-                    jobs.push_back(Job{r, m, p, splits, partial_words});
+                    jobs.push_back(Job{r, m, p, splits, partial_words, val_words, nullptr});
                     partial_words += (size_t)rm.lde->width * splits * 4;
+                    val_words += (size_t)rm.lde->width * 4;
                 }
         uint32_t* d_partial = scratch.words(partial_words);
-        for (auto& j : jobs) {
-            const RoundMat& rm = rounds[j.r].mats[j.m];
-            uint32_t* w = get_weights(rm.log_n, (int)j.p, rm.points[j.p]);
-            bary_dot_kernel<<<dim3((unsigned)rm.lde->width, j.splits), DOT_THREADS, 0, e->stream>>>(rm.lde->d, rm.lde->height, w,
-                                                                                                    rm.log_n, d_partial + j.off);
-            B2_CHECK_LAUNCH();
-            e->launches[3]++;
-        }
-        std::vector<uint32_t> partial(partial_words);
-        B2_CUDA(cudaMemcpyAsync(partial.data(), d_partial, partial_words * 4, cudaMemcpyDeviceToHost, e->stream));
-        B2_CUDA(cudaStreamSynchronize(e->stream));
+        uint32_t* d_vals = scratch.words(val_words);
+        // The values come back one (matrix, point) at a time into pinned memory, each behind its own event, in the order
+        // the transcript observes them (round -> matrix -> point -> column, two_adic_pcs.rs:63-95): the host hashes the
+        // values of one matrix while the device is still evaluating the next ones.
+        uint32_t* h_vals = (uint32_t*)e->host_pinned(val_words * 4);
         const Fp ginv = fp_inv(Fp::raw(M_GENERATOR));
         for (auto& j : jobs) {
-            RoundMat& rm = rounds[j.r].mats[j.m];
+            const RoundMat& rm = rounds[j.r].mats[j.m];
+            const uint32_t width = (uint32_t)rm.lde->width;
+            uint32_t* w = get_weights(rm.log_n, (int)j.p, rm.points[j.p]);
+            bary_dot_kernel<<<dim3(width, j.splits), DOT_THREADS, 0, e->stream>>>(rm.lde->d, rm.lde->height, w, rm.log_n,
+                                                                                  d_partial + j.off);
+            B2_CHECK_LAUNCH();
             const Fp ninv = fp_inv(Fp::from_canonical((uint32_t)(((uint64_t)1 << rm.log_n) % P)));
             const Fp4 scale = (fp4_pow2k(rm.points[j.p] * ginv, rm.log_n) - Fp::one()) * ninv;
+            bary_finish_kernel<<<(width + 127) / 128, 128, 0, e->stream>>>(d_partial + j.off, width, j.splits, scale, d_vals + j.voff);
+            B2_CHECK_LAUNCH();
+            e->launches[3] += 2;
+            B2_CUDA(cudaMemcpyAsync(h_vals + j.voff, d_vals + j.voff, (size_t)width * 16, cudaMemcpyDeviceToHost, e->stream));
+            j.done = e->get_event();
+            B2_CUDA(cudaEventRecord(j.done, e->stream));
+        }
+        trace.mark("ood values enqueued");
+        for (auto& j : jobs) {
+            RoundMat& rm = rounds[j.r].mats[j.m];
+            B2_CUDA(cudaEventSynchronize(j.done));
+            e->event_pool.push_back(j.done);
             std::vector<Fp4> vals(rm.lde->width);
+            const uint32_t* src = h_vals + j.voff;
             for (uint64_t c = 0; c < rm.lde->width; c++) {
-                Fp4 s = Fp4::zero();
-                for (uint32_t sp = 0; sp < j.splits; sp++)
-                    for (int k = 0; k < 4; k++) s.c[k] += Fp::raw(partial[j.off + (c * j.splits + sp) * 4 + k]);
-                vals[c] = s * scale;
+                vals[c] = Fp4(Fp::raw(src[4 * c]), Fp::raw(src[4 * c + 1]), Fp::raw(src[4 * c + 2]), Fp::raw(src[4 * c + 3]));
+                ch.observe_ext(vals[c]);
             }
             if (rm.values.size() <= j.p) rm.values.resize(j.p + 1);
             rm.values[j.p] = std::move(vals);
         }
     }
-    trace.mark("ood values");
-    // observed round -> matrix -> point -> column (two_adic_pcs.rs:63-95)
-    for (auto& r : rounds)
-        for (auto& m : r.mats)
-            for (auto& pt : m.values)
-                for (auto& v : pt) ch.observe_ext(v);
     const Fp4 fri_alpha = ch.sample_ext();
 
     trace.mark("observe opened values");
