@@ -80,6 +80,15 @@ int32_t b2s_engine_new(const b2s_fri_params* params, int32_t cuda_device, b2s_en
 void b2s_engine_free(b2s_engine* e);
 /* engine.fri_params()           crates/sdk/src/prover/app.rs:139 */
 int32_t b2s_engine_fri_params(const b2s_engine* e, b2s_fri_params* out);
+/* The hash of the configuration: BabyBearPoseidon2Config (default; digests are 8 BabyBear words) or
+ * BabyBearPoseidon2RootConfig (crates/continuations/src/lib.rs:17, crates/sdk/src/prover/root.rs): Poseidon2 over the
+ * BN254 scalar field, width 3, leaves hashed with the multi-field sponge of
+ * extensions/native/recursion/src/outer_poseidon2.rs:26-63; a digest is ONE scalar, returned as 8 little-endian 32-bit
+ * limbs of its canonical value in the same root8 / proof slots. Affects commitments made after the call. */
+#define B2S_HASH_POSEIDON2_BABYBEAR 0
+#define B2S_HASH_POSEIDON2_BN254 1
+int32_t b2s_engine_set_hash(b2s_engine* e, int32_t kind);
+int32_t b2s_engine_hash(const b2s_engine* e);
 /* message for the last non-zero status returned on this engine (or globally when e == NULL) */
 const char* b2s_last_error(const b2s_engine* e);
 /* the CUDA stream all work of this engine is ordered on (cudaStream_t as void*); set lets a caller that
@@ -252,6 +261,11 @@ int32_t b2s_debug_quotient_ptx(const uint32_t* key_words, size_t n_words, uint32
 int32_t b2s_poseidon2_permute(b2s_engine* e, uint32_t* host_states, size_t n_states);
 /* integer-pipe micro-benchmark: `iters` dependent Montgomery multiplications per thread on
  * `threads` threads; returns device ms (the measured modmul/s is the IMAD "peak" of DESIGN.md) */
+/* Poseidon2-BN254 width 3 on n states of 3 x 8 canonical limbs, in place
+ * (extensions/native/compiler/src/constraints/halo2/poseidon2_perm.rs:52-82) */
+int32_t b2s_poseidon2_bn254_permute(b2s_engine* e, uint32_t* host_states, size_t n_states);
+/* the same on the host cores (no device, no engine): the transcript and the verifier of the root configuration use it */
+int32_t b2s_host_poseidon2_bn254_permute(uint32_t* states, size_t n_states);
 int32_t b2s_bench_modmul(b2s_engine* e, uint64_t threads, uint32_t iters, int32_t ilp, double* ms_out);
 /* Poseidon2 permutations/s with state in registers and no memory traffic */
 int32_t b2s_bench_poseidon2(b2s_engine* e, uint64_t threads, uint32_t iters, double* ms_out);

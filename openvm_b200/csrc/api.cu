@@ -1,6 +1,7 @@
 // C ABI of libb2stark.so (include/b2stark.h). Every entry point converts internal failures into status codes;
 // there is no CPU fallback behind any of them.
 #include "common.cuh"
+#include "bn254.cuh"
 
 #include <mutex>
 
@@ -144,8 +145,10 @@ b2s_pcs_data* commit_host_streamed(b2s_engine* e, const uint32_t* host, uint64_t
     const unsigned logn = log2_exact(N);
     B2_REQUIRE(logn + lb <= TWO_ADICITY, B2S_ERR_SHAPE, "commit: trace too tall for this blowup");
     const uint64_t M = N << lb;
-    uint64_t G = (((uint64_t)1 << 27) / N) & ~(uint64_t)7;
-    if (G < 8) G = 8;
+    const uint64_t gq = e->hash_kind ? 16 : 8;          // columns per sponge block: a group ends on a block boundary
+    const size_t state_bytes = e->hash_kind ? 96 : 64;  // sponge state of one row between groups
+    uint64_t G = (((uint64_t)1 << 27) / N) & ~(gq - 1);
+    if (G < gq) G = gq;
     if (G > W) G = W;
     const uint64_t ngroups = (W + G - 1) / G;
     const bool row_major = layout == B2S_LAYOUT_ROW_MAJOR;
@@ -161,7 +164,7 @@ b2s_pcs_data* commit_host_streamed(b2s_engine* e, const uint32_t* host, uint64_t
             e->event_pool.push_back(copied[k]);
             e->event_pool.push_back(consumed[k]);
         }
-        if (state) e->dfree(state, M * 64);
+        if (state) e->dfree(state, M * state_bytes);
     };
     try {
         b2s_matrix* lde = new_matrix(e, M, W);
@@ -171,7 +174,7 @@ b2s_pcs_data* commit_host_streamed(b2s_engine* e, const uint32_t* host, uint64_t
             stage[k] = (uint32_t*)e->dmalloc(G * N * 4);
             if (row_major) raw[k] = (uint32_t*)e->dmalloc(G * N * 4);
         }
-        if (ngroups > 1) state = (uint32_t*)e->dmalloc(M * 64);
+        if (ngroups > 1) state = (uint32_t*)e->dmalloc(M * state_bytes);
         leaf = (uint32_t*)e->dmalloc(M * 32);
         // the buffers come from the stream-ordered allocator of e->stream: order the copy stream behind them
         B2_CUDA(cudaEventRecord(consumed[0], e->stream));
@@ -522,7 +525,7 @@ static void root_to_host(b2s_engine* e, b2s_pcs_data* d, uint32_t root8[8]) {
     uint32_t raw[8];
     B2_CUDA(cudaMemcpyAsync(raw, d->layers.back(), 32, cudaMemcpyDeviceToHost, e->stream));
     B2_CUDA(cudaStreamSynchronize(e->stream));
-    for (int i = 0; i < 8; i++) root8[i] = Fp::raw(raw[i]).to_canonical();
+    for (int i = 0; i < 8; i++) root8[i] = e->hash_kind ? raw[i] : Fp::raw(raw[i]).to_canonical();
 }
 
 int32_t b2s_mmcs_commit(b2s_engine* e, const b2s_matrix* const* mats, size_t n_mats, uint32_t root8[8],
@@ -585,6 +588,7 @@ int32_t b2s_prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size
     *proof_len = 0;
     return guarded(e, [&] {
         std::vector<uint8_t> bytes;
+        B2_REQUIRE(e->hash_kind == 0, B2S_ERR_BAD_ARG, "prove: the BN254 hash covers commitments and openings only");
         prove(e, pk, airs, n_airs, bytes);
         uint8_t* buf = (uint8_t*)malloc(bytes.size() ? bytes.size() : 1);
         if (!buf) fail(B2S_ERR_OOM, "proof buffer allocation failed");
@@ -608,7 +612,7 @@ int32_t b2s_commit_host(b2s_engine* e, const uint32_t* host, uint64_t height, ui
                 uint32_t r[8];
                 B2_CUDA(cudaMemcpyAsync(r, d->layers.back(), 32, cudaMemcpyDeviceToHost, e->stream));
                 B2_CUDA(cudaStreamSynchronize(e->stream));
-                for (int k = 0; k < 8; k++) root8[k] = Fp::raw(r[k]).to_canonical();
+                for (int k = 0; k < 8; k++) root8[k] = e->hash_kind ? r[k] : Fp::raw(r[k]).to_canonical();
             } catch (...) {
                 free_pcs(d);
                 throw;
@@ -652,6 +656,7 @@ int32_t b2s_verify(b2s_engine* e, const b2s_pk* pk, const uint8_t* proof_bytes, 
     if (!e || !pk || !proof_bytes) return B2S_ERR_BAD_ARG;
     return guarded(e, [&] {
         B2_REQUIRE(pk->eng == e, B2S_ERR_BAD_ARG, "verify: key was loaded on a different engine");
+        B2_REQUIRE(e->hash_kind == 0, B2S_ERR_BAD_ARG, "verify: the BN254 hash covers commitments and openings only");
         verify(e, pk, proof_bytes, proof_len);
     });
 }
@@ -703,6 +708,49 @@ int32_t b2s_poseidon2_permute(b2s_engine* e, uint32_t* host_states, size_t n_sta
         B2_CUDA(cudaStreamSynchronize(e->stream));
         e->dfree(d, bytes);
     });
+}
+
+int32_t b2s_engine_set_hash(b2s_engine* e, int32_t kind) {
+    if (!e) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] {
+        B2_REQUIRE(kind == B2S_HASH_POSEIDON2_BABYBEAR || kind == B2S_HASH_POSEIDON2_BN254, B2S_ERR_BAD_ARG, "unknown hash kind");
+        e->hash_kind = kind;
+    });
+}
+int32_t b2s_engine_hash(const b2s_engine* e) { return e ? e->hash_kind : B2S_ERR_BAD_ARG; }
+
+int32_t b2s_poseidon2_bn254_permute(b2s_engine* e, uint32_t* host_states, size_t n_states) {
+    if (!e || (!host_states && n_states)) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] {
+        if (!n_states) return;
+        size_t bytes = n_states * 96;
+        uint32_t* d = (uint32_t*)e->dmalloc(bytes);
+        B2_CUDA(cudaMemcpyAsync(d, host_states, bytes, cudaMemcpyHostToDevice, e->stream));
+        bn_permute_states(e, d, n_states);
+        B2_CUDA(cudaMemcpyAsync(host_states, d, bytes, cudaMemcpyDeviceToHost, e->stream));
+        B2_CUDA(cudaStreamSynchronize(e->stream));
+        e->dfree(d, bytes);
+    });
+}
+
+// the same permutation on the host (the verifier and the transcript of the root configuration hash on the CPU)
+int32_t b2s_host_poseidon2_bn254_permute(uint32_t* states, size_t n_states) {
+    if (!states && n_states) return B2S_ERR_BAD_ARG;
+    for (size_t i = 0; i < n_states; i++) {
+        Fr s[3];
+        for (int k = 0; k < 3; k++) {
+            uint32_t w[8];
+            for (int j = 0; j < 8; j++) w[j] = states[24 * i + 8 * k + j];
+            s[k] = fr_from_words(w);
+        }
+        poseidon2_bn254_permute(s);
+        for (int k = 0; k < 3; k++) {
+            uint32_t w[8];
+            fr_to_words(s[k], w);
+            for (int j = 0; j < 8; j++) states[24 * i + 8 * k + j] = w[j];
+        }
+    }
+    return B2S_OK;
 }
 
 int32_t b2s_bench_modmul(b2s_engine* e, uint64_t threads, uint32_t iters, int32_t ilp, double* ms_out) {

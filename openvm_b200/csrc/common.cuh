@@ -71,6 +71,7 @@ struct b2s_engine {
     std::map<unsigned, b2::TwiddleSet*> twiddles;  // by log size
     std::map<uint64_t, b2::ScaleSet*> scales;      // by (logn, log_blowup, shift_in)
     unsigned* tile_ctr = nullptr;                  // work counter of the persistent leaf-hash kernel (merkle.cu)
+    int hash_kind = 0;                             // B2S_HASH_*: 0 Poseidon2-BabyBear-16 digests of 8 words, 1 Poseidon2-BN254-3 (root config)
 
     void* pinned = nullptr;                        // grow-only pinned host buffer for small asynchronous read-backs
     size_t pinned_bytes = 0;
@@ -176,6 +177,13 @@ void free_twiddles(b2s_engine* e);
 void free_scales(b2s_engine* e);
 // merkle.cu
 void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer = nullptr);
+// merkle_bn254.cu: the root configuration's hash (one BN254 scalar per digest, canonical limbs in the same 8 planes)
+void bn_launch_level(b2s_engine* e, const uint32_t* const* cols, uint32_t ncols, uint64_t n, const uint32_t* prev, uint32_t* out,
+                     int mode);
+void bn_leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_t n, uint32_t* state, uint32_t* out, bool first,
+                    bool last);
+void bn_permute_states(b2s_engine* e, uint32_t* d_states, uint64_t n);
+
 void leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_t n, uint32_t* state, uint32_t* out, bool first,
                  bool last);
 void poseidon2_permute_states(b2s_engine* e, uint32_t* d_states, size_t n);
@@ -192,9 +200,11 @@ struct OpenDesc {
     const uint32_t* base;  // column 0 of a matrix, or plane 0 of a digest layer
     uint64_t stride;       // height (matrix) or node count (layer)
     uint64_t row;
-    uint32_t count;        // width or 8
+    uint32_t count;        // width or 8; OPEN_RAW set: words are copied as they are (BN254 digest limbs), not Montgomery -> canonical
     uint32_t out_off;
 };
+constexpr uint32_t OPEN_RAW = 0x80000000u;
+inline uint32_t digest_words_desc(const b2s_engine* e) { return e->hash_kind ? (8u | OPEN_RAW) : 8u; }
 void gather_rows(b2s_engine* e, const std::vector<OpenDesc>& descs, size_t total_words, uint32_t* h_out);
 // qjit.cu
 bool quotient_jit_enabled();

@@ -460,6 +460,13 @@ static inline unsigned grid_for(uint64_t n, int threads) { return (unsigned)((n 
 void leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_t n, uint32_t* state, uint32_t* out, bool first,
                  bool last) {
     StageScope sc(e, ST_LEAF);
+    if (e->hash_kind) {
+        bn_leaf_absorb(e, base, ncols, n, state, out, first, last);
+        B2_CHECK_LAUNCH();
+        e->launches[1]++;
+        e->permutations += n * ((ncols + 15) / 16);
+        return;
+    }
     if (n >= mixed_min_rows() && mixed_int_warps() >= 0)
         launch_mixed(e, ColStrided{base, n}, ncols, n, first ? nullptr : state, last ? nullptr : state, out);
     else
@@ -473,7 +480,9 @@ void leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_t n
 // one tree level: throughput kernel (one node per thread) for big levels, latency kernel (four lanes per node) below
 static void launch_level(b2s_engine* e, const uint32_t* const* cols, uint32_t ncols, uint64_t n, const uint32_t* prev,
                          uint32_t* out, int mode) {
-    if (n >= mixed_min_rows() && mixed_int_warps() >= 0)
+    if (e->hash_kind)
+        bn_launch_level(e, cols, ncols, n, prev, out, mode);
+    else if (n >= mixed_min_rows() && mixed_int_warps() >= 0)
         launch_mixed(e, ColTable{cols}, ncols, n, nullptr, nullptr, out, mode == 0 ? nullptr : prev);
     else if (n <= COOP_MAX_NODES)
         tree_level_coop_kernel<<<grid_for(4 * n, COOP_THREADS), COOP_THREADS, 0, e->stream>>>(cols, ncols, n, prev, out, mode);
@@ -531,7 +540,7 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
     uint64_t h = hmax;
     while (h > 1) {
         uint64_t nh = h / 2;
-        if (nh <= SUBTREE_MAX_FIRST) {
+        if (!e->hash_kind && nh <= SUBTREE_MAX_FIRST) {
             // log2(W) + 1 levels in one launch (all remaining ones when nh <= SUBTREE_NODES)
             StageScope sc(e, ST_COMPRESS);
             SubtreeParams tp{};

@@ -131,8 +131,12 @@ __global__ void gather_kernel(const OpenDesc* descs, uint32_t ndesc, uint32_t* o
     uint32_t di = blockIdx.x;
     if (di >= ndesc) return;
     OpenDesc d = descs[di];
-    for (uint32_t c = threadIdx.x; c < d.count; c += blockDim.x)
-        out[d.out_off + c] = Fp::raw(d.base[(uint64_t)c * d.stride + d.row]).to_canonical();
+    const bool raw = (d.count & OPEN_RAW) != 0;
+    const uint32_t count = d.count & ~OPEN_RAW;
+    for (uint32_t c = threadIdx.x; c < count; c += blockDim.x) {
+        const uint32_t v = d.base[(uint64_t)c * d.stride + d.row];
+        out[d.out_off + c] = raw ? v : Fp::raw(v).to_canonical();
+    }
 }
 // every descriptor copies `count` strided words (a matrix row or a digest) to out[out_off..], canonical form;
 // one launch and one device-to-host copy for the whole list
@@ -160,7 +164,7 @@ void gather_open(b2s_engine* e, const b2s_pcs_data* d, uint64_t index, uint32_t*
     }
     uint32_t rows_words = off;
     for (unsigned l = 0; l < d->log_max_height; l++) {
-        descs.push_back(OpenDesc{d->layers[l], d->layer_nodes[l], (index >> l) ^ 1, 8u, off});
+        descs.push_back(OpenDesc{d->layers[l], d->layer_nodes[l], (index >> l) ^ 1, digest_words_desc(e), off});
         off += 8;
     }
     std::vector<uint32_t> tmp(off);
@@ -174,7 +178,7 @@ void download_layer(b2s_engine* e, const b2s_pcs_data* d, uint32_t level, uint32
     uint64_t n = d->layer_nodes[level];
     // planes (8 x n) -> node-major (n x 8), canonical
     uint32_t* tmp = (uint32_t*)e->dmalloc(n * 32);
-    transpose_to_rowmajor(e, d->layers[level], tmp, n, 8, true);
+    transpose_to_rowmajor(e, d->layers[level], tmp, n, 8, e->hash_kind == 0);
     B2_CUDA(cudaMemcpyAsync(h_out, tmp, n * 32, cudaMemcpyDeviceToHost, e->stream));
     B2_CUDA(cudaStreamSynchronize(e->stream));
     e->dfree(tmp, n * 32);

@@ -298,9 +298,20 @@ class B2Device:
         e._check(e._lib.b2s_poseidon2_permute(e._h, a.ctypes.data, a.shape[0]))
         return a
 
+    def poseidon2_bn254_permute(self, states):
+        """Poseidon2 over the BN254 scalar field, width 3: states of 3 x 8 canonical 32-bit limbs."""
+        e = self._e
+        a = np.ascontiguousarray(states, dtype=np.uint32).reshape(-1, 24).copy()
+        e._check(e._lib.b2s_poseidon2_bn254_permute(e._h, a.ctypes.data, a.shape[0]))
+        return a
+
+
+HASH_POSEIDON2_BABYBEAR = 0   # BabyBearPoseidon2Config
+HASH_POSEIDON2_BN254 = 1      # BabyBearPoseidon2RootConfig (crates/continuations/src/lib.rs:17)
+
 
 class B2Engine:
-    """StarkFriEngine<SC = BabyBearPoseidon2Config> on one B200."""
+    """StarkFriEngine<SC = BabyBearPoseidon2Config> on one B200 (set_hash selects the root configuration's hash)."""
 
     def __init__(self, fri_params=FriParameters(), cuda_device=0):
         self._lib = _lib.load()
@@ -322,6 +333,12 @@ class B2Engine:
 
     def fri_params(self):
         return self._params
+
+    def set_hash(self, kind):
+        self._check(self._lib.b2s_engine_set_hash(self._h, int(kind)))
+
+    def hash(self):
+        return int(self._lib.b2s_engine_hash(self._h))
 
     def prove(self, pk, ctx):
         """StarkEngine::prove(&pk, ctx) -> proof bytes in the reference wire format (crates/sdk/src/codec.rs).

@@ -230,4 +230,40 @@ int orc_proof_hint_stream(const uint8_t* proof, size_t len, uint32_t** words_out
     }
 }
 
+// configuration switch: 0 BabyBearPoseidon2Config, 1 BabyBearPoseidon2RootConfig (oracle/bn254.hpp); every hash, tree,
+// transcript, prover and verifier entry above follows it
+void orc_set_hash(int kind) { hash_kind() = kind; }
+int orc_get_hash() { return hash_kind(); }
+// Poseidon2-BN254 width 3 on n states of 3 x 8 canonical 32-bit limbs, in place
+void orc_bn254_permute(uint32_t* st, size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        Bn s[3];
+        for (int k = 0; k < 3; k++) {
+            uint64_t w[4];
+            for (int j = 0; j < 4; j++) w[j] = (uint64_t)st[24 * i + 8 * k + 2 * j] | ((uint64_t)st[24 * i + 8 * k + 2 * j + 1] << 32);
+            s[k] = bn::from_words(w);
+        }
+        bn::permute(s);
+        for (int k = 0; k < 3; k++) {
+            uint64_t w[4];
+            bn::to_words(s[k], w);
+            for (int j = 0; j < 8; j++) st[24 * i + 8 * k + j] = (uint32_t)(w[j / 2] >> (32 * (j & 1)));
+        }
+    }
+}
+// transcript hook with digests: ops[i] = 0 observe value a[i], 1 observe the digest at a[i] (index into digests, 8 words
+// each), 2 sample into out
+void orc_challenger_script(const uint32_t* ops, const uint32_t* args, size_t n_ops, const uint32_t* digests, uint32_t* out) {
+    Challenger ch;
+    size_t k = 0;
+    for (size_t i = 0; i < n_ops; i++) {
+        if (ops[i] == 0) ch.observe(F(args[i]));
+        else if (ops[i] == 1) {
+            Digest d;
+            for (int w = 0; w < 8; w++) d[w].v = digests[8 * args[i] + w];
+            ch.observe_digest(d);
+        } else out[k++] = ch.sample().v;
+    }
+}
+
 }

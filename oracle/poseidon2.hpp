@@ -128,7 +128,7 @@ typedef std::array<F, 8> Digest;
 
 // PaddingFreeSponge<Perm,16,8,8> (hints.rs:36; extensions/native/circuit/src/poseidon2/README.md:9-17;
 // execution.rs:478-522): overwrite-mode absorb, no padding, permute after every (possibly short) chunk.
-struct Sponge {
+struct SpongeBabyBear {
     F st[16];
     int pos = 0;
     void absorb(F x) {
@@ -143,14 +143,8 @@ struct Sponge {
     }
 };
 
-inline Digest hash_slice(const F* x, size_t n) {
-    Sponge s;
-    for (size_t i = 0; i < n; i++) s.absorb(x[i]);
-    return s.finish();
-}
-
 // TruncatedPermutation<Perm,2,8,16> (hints.rs:37-38; crates/vm/src/arch/hasher/poseidon2.rs:33-43)
-inline Digest compress(const Digest& l, const Digest& r) {
+inline Digest compress_babybear(const Digest& l, const Digest& r) {
     F s[16];
     for (int i = 0; i < 8; i++) { s[i] = l[i]; s[8 + i] = r[i]; }
     poseidon2_permute(s);
@@ -160,3 +154,5 @@ inline Digest compress(const Digest& l, const Digest& r) {
 }
 
 }  // namespace orc
+
+#include "bn254.hpp"  // Sponge / hash_slice / compress of the selected configuration

@@ -108,7 +108,17 @@ struct Reader {
     uint32_t len() { uint32_t l = u32(); if ((size_t)l > n) throw std::runtime_error("proof: bad length"); return l; }
     F f() { uint32_t x = u32(); if (x >= P) throw std::runtime_error("proof: non-canonical field element"); return F(x); }
     EF ef() { EF e; for (int k = 0; k < 4; k++) e.c[k] = f(); return e; }
-    Digest digest() { Digest d; for (int k = 0; k < 8; k++) d[k] = f(); return d; }
+    // root configuration: a digest is the canonical scalar in eight limbs (there is no reference wire format for it --
+    // crates/sdk/src/codec.rs covers BabyBearPoseidon2Config only; the inner layout is kept, limbs in place of words)
+    Digest digest() {
+        Digest d;
+        if (!hash_kind()) { for (int k = 0; k < 8; k++) d[k] = f(); return d; }
+        uint64_t w[4];
+        for (int k = 0; k < 8; k++) d[k].v = u32();
+        for (int k = 0; k < 4; k++) w[k] = (uint64_t)d[2 * k].v | ((uint64_t)d[2 * k + 1].v << 32);
+        if (bn::geq_mod(w)) throw std::runtime_error("proof: non-canonical digest");
+        return d;
+    }
     std::vector<EF> efs() { std::vector<EF> v(len()); for (auto& e : v) e = ef(); return v; }
     std::vector<F> fs() { std::vector<F> v(len()); for (auto& e : v) e = f(); return v; }
     std::vector<Digest> digests() { std::vector<Digest> v(len()); for (auto& d : v) d = digest(); return v; }

@@ -184,6 +184,23 @@ class Oracle:
         self.lib.orc_free(words)
         return unflatten_stream(flat)
 
+    # ---- root configuration (oracle/bn254.hpp)
+    def set_hash(self, kind):
+        self.lib.orc_set_hash(int(kind))
+
+    def bn254_permute(self, states):
+        a = np.ascontiguousarray(states, dtype=np.uint32).reshape(-1, 24).copy()
+        self.lib.orc_bn254_permute(C.c_void_p(a.ctypes.data), C.c_size_t(a.shape[0]))
+        return a
+
+    def challenger_script(self, ops, args, digests):
+        ops = np.ascontiguousarray(ops, dtype=np.uint32); args = np.ascontiguousarray(args, dtype=np.uint32)
+        digests = np.ascontiguousarray(digests, dtype=np.uint32).reshape(-1)
+        out = np.zeros(max(1, int((ops == 2).sum())), dtype=np.uint32)
+        self.lib.orc_challenger_script(C.c_void_p(ops.ctypes.data), C.c_void_p(args.ctypes.data), C.c_size_t(ops.size),
+                                       C.c_void_p(digests.ctypes.data), C.c_void_p(out.ctypes.data))
+        return out[:int((ops == 2).sum())]
+
     def challenger_run(self, observed, n_samples):
         obs = np.ascontiguousarray(observed, dtype=np.uint32)
         out = np.zeros(n_samples, dtype=np.uint32)

@@ -120,3 +120,91 @@ def coset_lde_naive(col, log_blowup, shift_in=1):
         br = int(format(k, "0%db" % logm_)[::-1], 2) if logm_ else 0
         out[br] = acc
     return out
+
+
+# ---- root configuration: Poseidon2 over the BN254 scalar field, width 3 (oracle/bn254.hpp names the in-tree sources) ----
+BN_R = 21888242871839275222246405745257275088548364400416034343698204186575808495617
+BN_EXT_INIT, BN_PARTIAL, BN_EXT_TERM = round_constants(BN_R, 254, 3, 8, 56)
+
+
+def bn_permute(s):
+    def external(v):
+        t = sum(v) % BN_R
+        return [(x + t) % BN_R for x in v]
+
+    s = external(list(s))
+    for rc in BN_EXT_INIT:
+        s = external([pow((x + k) % BN_R, 5, BN_R) for x, k in zip(s, rc)])
+    for k in BN_PARTIAL:
+        s[0] = pow((s[0] + k) % BN_R, 5, BN_R)
+        t = sum(s) % BN_R
+        s = [(s[0] + t) % BN_R, (s[1] + t) % BN_R, (2 * s[2] + t) % BN_R]
+    for rc in BN_EXT_TERM:
+        s = external([pow((x + k) % BN_R, 5, BN_R) for x, k in zip(s, rc)])
+    return s
+
+
+def bn_reduce_32(vals):
+    return sum(v << (32 * i) for i, v in enumerate(vals)) % BN_R
+
+
+def bn_split_32(x, n):
+    return [((x >> (64 * j)) & 0xFFFFFFFFFFFFFFFF) % P for j in range(n)]
+
+
+def bn_hash_slice(xs):
+    """outer_poseidon2.rs:26-50: blocks of 16 values, 8 per element, overwrite mode, no padding."""
+    xs = list(xs)
+    st = [0, 0, 0]
+    for b in range(0, len(xs), 16):
+        block = xs[b:b + 16]
+        for h in range(0, len(block), 8):
+            st[h // 8] = bn_reduce_32(block[h:h + 8])
+        st = bn_permute(st)
+    return st[0]
+
+
+def bn_compress(l, r):
+    return bn_permute([l, r, 0])[0]
+
+
+def bn_limbs(x):
+    return [(x >> (32 * i)) & 0xFFFFFFFF for i in range(8)]
+
+
+def bn_from_limbs(w):
+    return sum(int(v) << (32 * i) for i, v in enumerate(w))
+
+
+class BnChallenger:
+    """challenger/multi_field32.rs:24-108."""
+
+    def __init__(self):
+        self.state = [0, 0, 0]
+        self.inp = []
+        self.out = []
+
+    def duplexing(self):
+        assert len(self.inp) <= 6
+        for i in range(0, len(self.inp), 3):
+            self.state[i // 3] = bn_reduce_32(self.inp[i:i + 3])
+        self.inp = []
+        self.state = bn_permute(self.state)
+        self.out = []
+        for x in self.state:
+            self.out += bn_split_32(x, 3)
+
+    def observe(self, v):
+        self.out = []
+        self.inp.append(v)
+        if len(self.inp) == 6:
+            self.duplexing()
+
+    def observe_digest(self, x):
+        for f in bn_split_32(x, 3):
+            self.observe(f)
+
+    def sample(self):
+        if self.inp or not self.out:
+            self.duplexing()
+        return self.out.pop()
