@@ -588,7 +588,6 @@ int32_t b2s_prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size
     *proof_len = 0;
     return guarded(e, [&] {
         std::vector<uint8_t> bytes;
-        B2_REQUIRE(e->hash_kind == 0, B2S_ERR_BAD_ARG, "prove: the BN254 hash covers commitments and openings only");
         prove(e, pk, airs, n_airs, bytes);
         uint8_t* buf = (uint8_t*)malloc(bytes.size() ? bytes.size() : 1);
         if (!buf) fail(B2S_ERR_OOM, "proof buffer allocation failed");
@@ -656,7 +655,6 @@ int32_t b2s_verify(b2s_engine* e, const b2s_pk* pk, const uint8_t* proof_bytes, 
     if (!e || !pk || !proof_bytes) return B2S_ERR_BAD_ARG;
     return guarded(e, [&] {
         B2_REQUIRE(pk->eng == e, B2S_ERR_BAD_ARG, "verify: key was loaded on a different engine");
-        B2_REQUIRE(e->hash_kind == 0, B2S_ERR_BAD_ARG, "verify: the BN254 hash covers commitments and openings only");
         verify(e, pk, proof_bytes, proof_len);
     });
 }
@@ -666,6 +664,8 @@ int32_t b2s_proof_hint_stream(b2s_engine* e, const uint8_t* proof_bytes, size_t 
     *words = nullptr;
     *n_words = 0;
     return guarded(e, [&] {
+        // the hint layout is the inner verifier program's (hints.rs); root proofs feed the static halo2 verifier instead
+        B2_REQUIRE(!e || e->hash_kind == 0, B2S_ERR_BAD_ARG, "hint stream: defined for BabyBearPoseidon2Config proofs only");
         const std::vector<uint32_t> v = proof_hint_stream(proof_bytes, proof_len);
         uint32_t* out = (uint32_t*)malloc(v.size() * 4);
         B2_REQUIRE(out != nullptr, B2S_ERR_OOM, "hint stream: out of host memory");

@@ -139,7 +139,8 @@ struct AirKeyDev {
 
 struct b2s_pk {
     b2s_engine* eng = nullptr;
-    uint32_t pre_hash[8] = {0};          // Montgomery
+    uint32_t pre_hash[8] = {0};          // layer form: Montgomery words, or (hash_kind 1) canonical limbs of one scalar
+    int hash_kind = 0;                   // the engine's hash when the key was loaded (preprocessed commitments depend on it)
     uint32_t log_up_pow_bits = 0;
     std::vector<b2::AirKeyDev> airs;
 };
@@ -183,6 +184,9 @@ void bn_launch_level(b2s_engine* e, const uint32_t* const* cols, uint32_t ncols,
 void bn_leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_t n, uint32_t* state, uint32_t* out, bool first,
                     bool last);
 void bn_permute_states(b2s_engine* e, uint32_t* d_states, uint64_t n);
+// proof-of-work search over the multi-field transcript: state = 3 x 8 Montgomery limbs, pending = canonical observed words
+void bn_pow_grind(b2s_engine* e, const uint32_t state24[24], const uint32_t pending[6], uint32_t n_pending, uint32_t bits,
+                  uint32_t base, uint32_t count, uint32_t* d_result);
 
 void leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_t n, uint32_t* state, uint32_t* out, bool first,
                  bool last);

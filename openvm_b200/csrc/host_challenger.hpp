@@ -9,6 +9,8 @@
 #include "field.cuh"
 #include "poseidon2_constants.cuh"
 #include <cstdlib>
+#include <array>
+#include "bn254.cuh"
 
 // host_poseidon2_avx2.cpp: the same permutation eight lanes at a time
 extern "C" int b2_host_has_avx2();
@@ -63,24 +65,76 @@ struct HostPoseidon2 {
     }
 };
 
+// DuplexChallenger<BabyBear, Poseidon2BabyBear<16>, 16, 8>, or -- hash_kind 1, the root configuration --
+// MultiField32Challenger<BabyBear, Bn254Fr, Poseidon2Bn254<3>, 3, 2> as the in-tree circuit twin states it
+// (extensions/native/recursion/src/challenger/multi_field32.rs:24-108): observed values are buffered, six of them (two
+// scalars of three 32-bit-spaced words) trigger a duplexing; a duplexing overwrites the leading scalars with the packed
+// buffer, permutes, and refills the outputs with the three low 64-bit limbs (mod p) of each of the three scalars; sample
+// pops from the end; a digest is observed as the three low limbs of its scalar.
 struct HostChallenger {
     HostPoseidon2 perm;
     Fp st[16];
     int in_ptr = 0, out_ptr = 0;
     uint64_t permutations = 0;
+    bool root = false;
+    Fr bst[3] = {fr_zero(), fr_zero(), fr_zero()};
+    uint32_t bin[6] = {0, 0, 0, 0, 0, 0};   // canonical
+    Fp bout[9];
 
-    void duplexing() { in_ptr = 0; perm.permute(st); out_ptr = 8; permutations++; }
+    explicit HostChallenger(int hash_kind = 0) : root(hash_kind != 0) {}
+
+    void duplexing() {
+        permutations++;
+        if (root) {
+            for (int h = 0; 3 * h < in_ptr; h++) {
+                uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                for (int k = 0; k < 3 && 3 * h + k < in_ptr; k++) w[k] = bin[3 * h + k];
+                bst[h] = bn_reduce_32(w);
+            }
+            in_ptr = 0;
+            poseidon2_bn254_permute(bst);
+            for (int k = 0; k < 3; k++) {
+                uint32_t f[3];
+                bn_split_32(bst[k], f);
+                for (int j = 0; j < 3; j++) bout[3 * k + j] = Fp::from_canonical(f[j]);
+            }
+            out_ptr = 9;
+            return;
+        }
+        in_ptr = 0;
+        perm.permute(st);
+        out_ptr = 8;
+    }
     void observe(Fp v) {
         out_ptr = 0;
+        if (root) {
+            bin[in_ptr++] = v.to_canonical();
+            if (in_ptr == 6) duplexing();
+            return;
+        }
         st[in_ptr++] = v;
         if (in_ptr == 8) duplexing();
     }
     void observe_canonical(uint32_t c) { observe(Fp::from_canonical(c)); }
-    void observe_digest(const uint32_t* monty8) { for (int i = 0; i < 8; i++) observe(Fp::raw(monty8[i])); }
+    // a digest as it sits in a tree layer: Montgomery words, or (root) the canonical limbs of its scalar
+    void observe_digest(const uint32_t* words8) {
+        if (root) {
+            for (int j = 0; j < 3; j++)
+                observe_canonical((uint32_t)((((uint64_t)words8[2 * j + 1] << 32) | words8[2 * j]) % P));
+            return;
+        }
+        for (int i = 0; i < 8; i++) observe(Fp::raw(words8[i]));
+    }
+    void observe_digest(const std::array<Fp, 8>& d) {
+        uint32_t w[8];
+        for (int i = 0; i < 8; i++) w[i] = d[i].v;
+        observe_digest(w);
+    }
     void observe_ext(const Fp4& e) { for (int i = 0; i < 4; i++) observe(e.c[i]); }
     Fp sample() {
         if (in_ptr != 0 || out_ptr == 0) duplexing();
-        return st[--out_ptr];
+        --out_ptr;
+        return root ? bout[out_ptr] : st[out_ptr];
     }
     Fp4 sample_ext() {
         Fp4 e;

@@ -127,6 +127,43 @@ __global__ void __launch_bounds__(BN_THREADS) bn_permute_kernel(uint32_t* st, ui
     }
 }
 
+// proof of work under the multi-field transcript (challenger/multi_field32.rs:99-107): the witness joins the pending
+// observations, one duplexing follows (at once when it completes six words, else at the sample), and the sample is the
+// last output word -- limb 2 of the third scalar, mod p.
+struct BnPowParams {
+    uint32_t st[24];
+    uint32_t pending[6];
+    uint32_t n_pending, bits, base;
+};
+__global__ void __launch_bounds__(BN_THREADS) bn_pow_grind_kernel(BnPowParams p, uint32_t count, uint32_t* result) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const uint32_t wit = p.base + t;
+    if (wit >= P) return;
+    Fr s[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+#pragma unroll
+        for (int j = 0; j < 8; j++) s[k].l[j] = p.st[8 * k + j];
+    const uint32_t n = p.n_pending + 1;
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        if (3u * h < n) {
+            uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const uint32_t idx = 3 * h + k;
+                if (idx < n) w[k] = idx == p.n_pending ? wit : p.pending[idx];
+            }
+            s[h] = bn_reduce_32(w);
+        }
+    }
+    bn_permute_call(s);
+    uint32_t f[3];
+    bn_split_32(s[2], f);
+    if ((f[2] & ((1u << p.bits) - 1)) == 0) atomicMin(result, wit);
+}
+
 static inline unsigned bn_grid(uint64_t n) { return (unsigned)((n + BN_THREADS - 1) / BN_THREADS); }
 
 void bn_launch_level(b2s_engine* e, const uint32_t* const* cols, uint32_t ncols, uint64_t n, const uint32_t* prev, uint32_t* out,
@@ -137,6 +174,17 @@ void bn_leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_
                     bool last) {
     B2_REQUIRE(last || ncols % 16 == 0, B2S_ERR_SHAPE, "bn254 leaf sponge: a column group must be a multiple of 16 wide");
     bn_leaf_absorb_kernel<<<bn_grid(n), BN_THREADS, 0, e->stream>>>(base, ncols, n, state, out, first ? 1 : 0, last ? 1 : 0);
+}
+void bn_pow_grind(b2s_engine* e, const uint32_t state24[24], const uint32_t pending[6], uint32_t n_pending, uint32_t bits,
+                  uint32_t base, uint32_t count, uint32_t* d_result) {
+    B2_REQUIRE(n_pending < 6, B2S_ERR_INTERNAL, "pow: transcript buffer is full");
+    BnPowParams p{};
+    for (int i = 0; i < 24; i++) p.st[i] = state24[i];
+    for (int i = 0; i < 6; i++) p.pending[i] = pending[i];
+    p.n_pending = n_pending;
+    p.bits = bits;
+    p.base = base;
+    bn_pow_grind_kernel<<<bn_grid(count), BN_THREADS, 0, e->stream>>>(p, count, d_result);
 }
 void bn_permute_states(b2s_engine* e, uint32_t* d_states, uint64_t n) {
     if (!n) return;

@@ -224,11 +224,13 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n, bool host_only, uint
     B2_REQUIRE(rd() == 2, B2S_ERR_BAD_ARG, "key blob: unsupported version");
     b2s_pk* pk = new b2s_pk();
     pk->eng = host_only ? nullptr : e;
+    pk->hash_kind = e ? e->hash_kind : 0;
+    const bool root = pk->hash_kind != 0;
     try {
         for (int j = 0; j < 8; j++) {
             uint32_t v = rd();
-            B2_REQUIRE(v < P, B2S_ERR_BAD_ARG, "key blob: non-canonical pre_hash");
-            pk->pre_hash[j] = Fp::from_canonical(v).v;
+            B2_REQUIRE(root || v < P, B2S_ERR_BAD_ARG, "key blob: non-canonical pre_hash");
+            pk->pre_hash[j] = root ? v : Fp::from_canonical(v).v;
         }
         pk->log_up_pow_bits = rd();
         const uint32_t na = rd();
@@ -245,7 +247,10 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n, bool host_only, uint
                        "key: after-challenge shape");
             if (a.log_qd > log_blowup) fail(B2S_ERR_CONSTRAINT_DEGREE, "key: quotient degree exceeds the engine's blowup");
             if (a.width_prep) {
-                for (int j = 0; j < 8; j++) a.prep_commit[j] = Fp::from_canonical(rd()).v;
+                for (int j = 0; j < 8; j++) {
+                    const uint32_t v = rd();
+                    a.prep_commit[j] = root ? v : Fp::from_canonical(v).v;
+                }
                 a.prep_log_height = rd();
                 B2_REQUIRE(a.prep_log_height + log_blowup <= TWO_ADICITY, B2S_ERR_SHAPE, "key: preprocessed height");
                 const size_t cnt = (size_t)a.width_prep << a.prep_log_height;
@@ -821,7 +826,11 @@ struct ByteWriter {
     void f(Fp x) { u32(x.to_canonical()); }
     void ef(const Fp4& e) { for (int i = 0; i < 4; i++) f(e.c[i]); }
     void efs(const std::vector<Fp4>& v) { u32((uint32_t)v.size()); for (auto& e : v) ef(e); }
-    void digest_monty(const uint32_t* d) { for (int i = 0; i < 8; i++) f(Fp::raw(d[i])); }
+    bool raw_digests = false;  // root configuration: a digest is already the canonical limbs of its scalar
+    void digest_monty(const uint32_t* d) {
+        if (raw_digests) return words(d, 8);
+        for (int i = 0; i < 8; i++) f(Fp::raw(d[i]));
+    }
     void words(const uint32_t* w, size_t n) {  // already canonical
         const size_t at = buf.size();
         buf.resize(at + 4 * n);
@@ -863,6 +872,9 @@ static Fp grind_device(b2s_engine* e, Scratch& scratch, HostChallenger& ch, unsi
         return w;
     }
     uint32_t* d_res = scratch.words(1);
+    uint32_t bn_state[24];
+    for (int k = 0; k < 3; k++)
+        for (int j = 0; j < 8; j++) bn_state[8 * k + j] = ch.bst[k].l[j];
     PowParams pp{};
     for (int i = 0; i < 16; i++) pp.st[i] = ch.st[i].v;
     pp.in_ptr = (uint32_t)ch.in_ptr;
@@ -873,7 +885,8 @@ static Fp grind_device(b2s_engine* e, Scratch& scratch, HostChallenger& ch, unsi
     for (uint64_t base = 0; base < P && found == 0xFFFFFFFFu; base += batch, batch = std::min(1u << 22, batch * 2)) {
         pp.base = (uint32_t)base;
         B2_CUDA(cudaMemsetAsync(d_res, 0xFF, 4, e->stream));
-        pow_grind_kernel<<<batch / 128, 128, 0, e->stream>>>(pp, batch, d_res);
+        if (ch.root) bn_pow_grind(e, bn_state, ch.bin, (uint32_t)ch.in_ptr, bits, (uint32_t)base, batch, d_res);
+        else pow_grind_kernel<<<batch / 128, 128, 0, e->stream>>>(pp, batch, d_res);
         B2_CHECK_LAUNCH();
         e->launches[3]++;
         e->permutations += batch;
@@ -914,7 +927,8 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     Scratch scratch(e);
     HostTrace trace(e);
     const unsigned b = e->params.log_blowup;
-    HostChallenger ch;
+    B2_REQUIRE(pk->hash_kind == e->hash_kind, B2S_ERR_BAD_ARG, "prove: the key was loaded under a different hash configuration");
+    HostChallenger ch(e->hash_kind);
     std::vector<unsigned> logn(n_airs);
     std::vector<const AirKeyDev*> keys(n_airs);
     unsigned log_max_height = 0;
@@ -1384,9 +1398,9 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     for (auto& ix : indices) ix = ch.sample_bits(L);
     std::vector<OpenDesc> descs;
     size_t off = 0;
-    auto push = [&](const uint32_t* base, uint64_t stride, uint64_t row, uint32_t count) {
+    auto push = [&](const uint32_t* base, uint64_t stride, uint64_t row, uint32_t count, bool digest = false) {
         B2_REQUIRE(off + count < 0xFFFFFFFFull, B2S_ERR_INTERNAL, "prove: opening buffer too large");
-        descs.push_back(OpenDesc{base, stride, row, count, (uint32_t)off});
+        descs.push_back(OpenDesc{base, stride, row, digest ? digest_words_desc(e) : count, (uint32_t)off});
         off += count;
     };
     for (uint32_t ix : indices) {
@@ -1394,7 +1408,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             const b2s_pcs_data* d = r.pcs;
             const uint64_t idx = (uint64_t)ix >> (L - d->log_max_height);
             for (auto* m : d->mats) push(m->d, m->height, idx >> (d->log_max_height - log2_exact(m->height)), (uint32_t)m->width);
-            for (unsigned l = 0; l < d->log_max_height; l++) push(d->layers[l], d->layer_nodes[l], (idx >> l) ^ 1, 8);
+            for (unsigned l = 0; l < d->log_max_height; l++) push(d->layers[l], d->layer_nodes[l], (idx >> l) ^ 1, 8, true);
         }
         for (size_t i = 0; i < fri_trees.size(); i++) {
             const b2s_pcs_data* d = fri_trees[i];
@@ -1402,7 +1416,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             // sibling value: the other element of the leaf pair = 4 columns of the leaf matrix
             const b2s_matrix* leaf = d->mats[0];
             push(leaf->d + (uint64_t)4 * ((pos & 1) ^ 1) * leaf->height, leaf->height, pair, 4);
-            for (unsigned l = 0; l < d->log_max_height; l++) push(d->layers[l], d->layer_nodes[l], (pair >> l) ^ 1, 8);
+            for (unsigned l = 0; l < d->log_max_height; l++) push(d->layers[l], d->layer_nodes[l], (pair >> l) ^ 1, 8, true);
         }
     }
     std::vector<uint32_t> opened(off);
@@ -1413,6 +1427,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     out.clear();
     out.reserve(opened.size() * 4 + (1u << 16));
     ByteWriter w{out};
+    w.raw_digests = e->hash_kind != 0;
     w.u32(1);  // CODEC_VERSION
     w.u32((uint32_t)main_commits.size());
     for (auto& c : main_commits) w.digest_monty(c.data());

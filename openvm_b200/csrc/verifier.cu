@@ -49,6 +49,7 @@ struct DecodedProof {
 struct ProofReader {
     const uint8_t* p;
     size_t n, i = 0;
+    bool root = false;
     uint32_t u32() {
         if (i + 4 > n) reject("InvalidProofShape: proof truncated");
         uint32_t x = (uint32_t)p[i] | ((uint32_t)p[i + 1] << 8) | ((uint32_t)p[i + 2] << 16) | ((uint32_t)p[i + 3] << 24);
@@ -66,7 +67,20 @@ struct ProofReader {
         return Fp::from_canonical(x);
     }
     Fp4 ef() { Fp4 e; for (int k = 0; k < 4; k++) e.c[k] = f(); return e; }
-    Digest digest() { Digest d; for (int k = 0; k < 8; k++) d[k] = f(); return d; }
+    // root configuration: a digest is one BN254 scalar, eight limbs of its canonical value (kept as raw words)
+    Digest digest() {
+        Digest d;
+        if (!root) { for (int k = 0; k < 8; k++) d[k] = f(); return d; }
+        constexpr uint32_t N[8] = B2_BN_MODULUS;
+        for (int k = 0; k < 8; k++) d[k] = Fp::raw(u32());
+        bool below = false;
+        for (int k = 7; k >= 0 && !below; k--) {
+            if (d[k].v > N[k]) break;
+            if (d[k].v < N[k]) below = true;
+        }
+        if (!below) reject("InvalidProofShape: non-canonical digest");
+        return d;
+    }
     std::vector<Fp4> efs() { std::vector<Fp4> v(len()); for (auto& e : v) e = ef(); return v; }
     std::vector<Fp> fs() { std::vector<Fp> v(len()); for (auto& e : v) e = f(); return v; }
     std::vector<Digest> digests() { std::vector<Digest> v(len()); for (auto& d : v) d = digest(); return v; }
@@ -74,8 +88,9 @@ struct ProofReader {
     std::vector<AdjacentOpened> adjs() { std::vector<AdjacentOpened> v(len()); for (auto& a : v) a = adj(); return v; }
 };
 
-DecodedProof decode(const uint8_t* bytes, size_t n) {
+DecodedProof decode(const uint8_t* bytes, size_t n, bool root = false) {
     ProofReader r{bytes, n};
+    r.root = root;
     if (r.u32() != 1) reject("InvalidProofShape: codec version");
     DecodedProof p;
     p.main_commits = r.digests();
@@ -127,7 +142,33 @@ DecodedProof decode(const uint8_t* bytes, size_t n) {
 // PaddingFreeSponge<16, 8, 8> and TruncatedPermutation (crates/vm/src/arch/hasher/poseidon2.rs:33-43)
 struct HostHasher {
     HostPoseidon2 perm;
+    bool root = false;  // MultiField32PaddingFreeSponge<_, _, _, 3, 16, 1> / TruncatedPermutation<_, 2, 1, 3> (bn254.cuh)
     Digest hash_rows(const std::vector<const std::vector<Fp>*>& rows) const {
+        if (root) {
+            Fr st[3] = {fr_zero(), fr_zero(), fr_zero()};
+            uint32_t buf[16];
+            int k = 0;
+            auto flush = [&]() {
+                for (int h = 0; 8 * h < k; h++) {
+                    uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                    for (int j = 0; j < 8 && 8 * h + j < k; j++) w[j] = buf[8 * h + j];
+                    st[h] = bn_reduce_32(w);
+                }
+                poseidon2_bn254_permute(st);
+                k = 0;
+            };
+            for (auto* row : rows)
+                for (Fp x : *row) {
+                    buf[k++] = x.to_canonical();
+                    if (k == 16) flush();
+                }
+            if (k) flush();
+            uint32_t w[8];
+            fr_to_words(st[0], w);
+            Digest d;
+            for (int j = 0; j < 8; j++) d[j] = Fp::raw(w[j]);
+            return d;
+        }
         Fp st[16];
         int k = 0;
         for (auto* row : rows)
@@ -141,6 +182,14 @@ struct HostHasher {
         return d;
     }
     Digest compress(const Digest& l, const Digest& r) const {
+        if (root) {
+            uint32_t a[8], b[8], o[8];
+            for (int j = 0; j < 8; j++) { a[j] = l[j].v; b[j] = r[j].v; }
+            bn_compress(a, b, o);
+            Digest d;
+            for (int j = 0; j < 8; j++) d[j] = Fp::raw(o[j]);
+            return d;
+        }
         Fp st[16];
         for (int j = 0; j < 8; j++) { st[j] = l[j]; st[8 + j] = r[j]; }
         perm.permute(st);
@@ -209,7 +258,7 @@ void verify_pcs(const HostHasher& hh, const std::vector<VerifyRound>& rounds, co
     if (proof.fri_commits.size() != log_max_height) reject("InvalidProofShape: commit phase");
     std::vector<Fp4> betas;
     for (auto& c : proof.fri_commits) {
-        for (int j = 0; j < 8; j++) ch.observe(c[j]);
+        ch.observe_digest(c);
         betas.push_back(ch.sample_ext());
     }
     ch.observe_ext(final_poly);
@@ -334,9 +383,12 @@ static Fp4 fold_constraints(const AirKeyDev& k, const ZetaInputs& in, const Fp4&
 void verify(const b2s_engine* e, const b2s_pk* pk, const uint8_t* bytes, size_t len) {
     const b2s_fri_params& fp = e->params;
     const unsigned b = fp.log_blowup;
-    const DecodedProof proof = decode(bytes, len);
+    if (pk->hash_kind != e->hash_kind) reject("InvalidProofShape: the key was loaded under a different hash configuration");
+    const bool root = e->hash_kind != 0;
+    const DecodedProof proof = decode(bytes, len, root);
     HostHasher hh;
-    HostChallenger ch;
+    hh.root = root;
+    HostChallenger ch(e->hash_kind);
     const size_t na = proof.per_air.size();
     if (na == 0) reject("InvalidProofShape: no AIRs");
     std::vector<const AirKeyDev*> keys(na);
@@ -358,7 +410,7 @@ void verify(const b2s_engine* e, const b2s_pk* pk, const uint8_t* bytes, size_t 
         }
     }
     // transcript prefix (stark/mod.rs:140-149, 231-254)
-    for (int j = 0; j < 8; j++) ch.observe(Fp::raw(pk->pre_hash[j]));
+    ch.observe_digest(pk->pre_hash);
     ch.observe_canonical((uint32_t)na);
     for (auto& a : proof.per_air) ch.observe_canonical(a.air_id);
     for (auto& a : proof.per_air) for (Fp v : a.public_values) ch.observe(v);
@@ -373,7 +425,7 @@ void verify(const b2s_engine* e, const b2s_pk* pk, const uint8_t* bytes, size_t 
     if (phase != !proof.after_commits.empty() || phase != !proof.opened_after.empty() || phase != proof.has_logup_witness ||
         proof.after_commits.size() > 1 || proof.opened_after.size() > 1)
         reject("InvalidProofShape: challenge phase");
-    for (auto& c : proof.main_commits) for (int j = 0; j < 8; j++) ch.observe(c[j]);
+    for (auto& c : proof.main_commits) ch.observe_digest(c);
     for (unsigned l : logn) ch.observe_canonical(l);
     Fp4 challenges[2];
     if (phase) {  // stark/mod.rs:307-358, 1129-1160
@@ -388,10 +440,10 @@ void verify(const b2s_engine* e, const b2s_pk* pk, const uint8_t* bytes, size_t 
                 total += cs;
             }
         if (total != Fp4::zero()) reject("NonZeroCumulativeSum");
-        for (int j = 0; j < 8; j++) ch.observe(proof.after_commits[0][j]);
+        ch.observe_digest(proof.after_commits[0]);
     }
     const Fp4 alpha = ch.sample_ext();
-    for (int j = 0; j < 8; j++) ch.observe(proof.quotient_commit[j]);
+    ch.observe_digest(proof.quotient_commit);
     const Fp4 zeta = ch.sample_ext();
 
     // opening rounds: [preprocessed per AIR][cached mains][common main][after challenge][quotient]

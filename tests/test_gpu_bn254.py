@@ -112,12 +112,85 @@ def test_streamed_commit_carries_the_sponge_state(root_engine, orc):
     assert np.array_equal(root_small, orc.commit([small], 1))
 
 
-def test_proofs_are_refused_until_built(root_engine):
-    from openvm_b200 import B2StarkError
+# ---- whole proofs under the root configuration ----------------------------------------------------------------------------
+def _root_engine(orc, b, queries, pow_bits):
+    from openvm_b200 import B2Engine, FriParameters
+    e = B2Engine.new(FriParameters(log_blowup=b, num_queries=queries, proof_of_work_bits=pow_bits))
+    e.set_hash(1)
+    orc.set_hash(1)
+    return e
+
+
+def _same_proof(orc, eng, key, inputs, air_objs, b, queries, pow_bits, expect=None):
+    from test_gpu_prove import gpu_prove, gpu_verify
+    proof = gpu_prove(eng, key, inputs, air_objs)
+    res, mine = orc.stark_verify(key, proof, b, queries, pow_bits), gpu_verify(eng, key, proof)
+    if expect is None:
+        assert res is None and mine is None
+    else:
+        assert expect in res and expect in mine
+    assert proof == orc.stark_prove(key, inputs, b, queries, pow_bits)
+    return proof
+
+
+@pytest.mark.parametrize("n,b,queries,pow_bits", [(32, 1, 4, 3), (8, 2, 3, 0), (1 << 10, 1, 5, 8)])
+def test_root_fibonacci_proof_bytes(orc, n, b, queries, pow_bits):
     import airs
-    dev = root_engine.device()
-    pk = dev.transport_pk_to_device(airs.key_blob([airs.fibonacci_air()]))
-    trace, pvs = airs.fibonacci_trace(16)
-    from openvm_b200 import AirProvingContext
-    with pytest.raises(B2StarkError):
-        root_engine.prove(pk, [AirProvingContext(0, dev.transport_matrix_to_device(trace), pvs)])
+    from test_oracle_stark import build_key
+    eng = _root_engine(orc, b, queries, pow_bits)
+    try:
+        air = airs.fibonacci_air()
+        key = build_key(orc, [air], b)
+        trace, pvs = airs.fibonacci_trace(n)
+        proof = _same_proof(orc, eng, key, [(0, [trace], pvs)], [air], b, queries, pow_bits)
+        # the inner configuration rejects it, on both sides
+        orc.set_hash(0)
+        assert orc.stark_verify(key, proof, b, queries, pow_bits) is not None
+    finally:
+        orc.set_hash(0)
+        eng.close()
+
+
+def test_root_multi_air_prep_cached_logup_bytes(orc):
+    import airs
+    from test_oracle_stark import build_key, interaction_traces
+    from test_gpu_prove import gpu_prove, gpu_verify
+    b, queries, pow_bits = 1, 6, 4
+    eng = _root_engine(orc, b, queries, pow_bits)
+    try:
+        a0 = airs.fibonacci_air()
+        a1 = airs.chain_air(7, with_prep=True, cached_width=3, height=64, seed=1)
+        a2 = airs.chain_air(5)
+        snd, rcv = airs.dummy_interaction_air(2, True), airs.dummy_interaction_air(2, False)
+        air_objs = [a0, a1, a2, snd, rcv]
+        for a in air_objs:
+            a.prep_commit = None
+        key = build_key(orc, air_objs, b)      # preprocessed commitments under the root hash
+        t0, pv0 = airs.fibonacci_trace(256)
+        p1, pv1 = airs.chain_trace(a1, 64, seed=5)
+        p2, pv2 = airs.chain_trace(a2, 512, seed=6)
+        send, recv = interaction_traces(64, 128, 2, seed=4)
+        none = np.zeros(0, dtype=np.uint32)
+        inputs = [(0, [t0], pv0), (1, p1, pv1), (2, p2, pv2), (3, [send], none), (4, [recv], none)]
+        proof = _same_proof(orc, eng, key, inputs, air_objs, b, queries, pow_bits)
+        _same_proof(orc, eng, key, inputs[:3], air_objs, b, queries, pow_bits)          # no challenge phase
+        send2, recv2 = interaction_traces(64, 128, 2, seed=4, unbalanced=True)
+        _same_proof(orc, eng, key, inputs[:3] + [(3, [send2], none), (4, [recv2], none)], air_objs, b, queries, pow_bits,
+                    expect="NonZeroCumulativeSum")
+        bad = [m.copy() for m in p2]
+        bad[0][7, 2] = (int(bad[0][7, 2]) + 1) % P
+        _same_proof(orc, eng, key, inputs[:2] + [(2, bad, pv2)] + inputs[3:], air_objs, b, queries, pow_bits,
+                    expect="OodEvaluationMismatch")
+        # tampered bytes: both verifiers reject
+        rng2 = np.random.default_rng(5)
+        for pos in rng2.integers(4, len(proof), size=25):
+            q = bytearray(proof)
+            q[pos] ^= 1 << int(rng2.integers(0, 8))
+            assert orc.stark_verify(key, bytes(q), b, queries, pow_bits) is not None
+            assert gpu_verify(eng, key, bytes(q)) is not None
+        # a key loaded under the inner hash cannot be used with the root engine's proofs
+        with pytest.raises(Exception):
+            eng.proof_hint_stream(proof)
+    finally:
+        orc.set_hash(0)
+        eng.close()
