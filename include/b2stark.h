@@ -248,6 +248,12 @@ int32_t b2s_verify(b2s_engine* e, const b2s_pk* pk, const uint8_t* proof_bytes, 
  * words. Fails with B2S_ERR_VERIFY_FAILED (InvalidProofShape) on bytes that do not decode. */
 int32_t b2s_proof_hint_stream(b2s_engine* e, const uint8_t* proof_bytes, size_t proof_len, uint32_t** words,
                               size_t* n_words);
+/* A proof made under B2S_HASH_POSEIDON2_BN254 as the witness of the static (halo2) verifier: Witnessable::write for
+ * Proof<BabyBearPoseidon2RootConfig> (extensions/native/recursion/src/witness.rs:147-190, fri/witness.rs:61-117), the input
+ * of the wrapper circuit (crates/sdk/src/prover/halo2.rs). e may be NULL (host only). *words (b2s_free) holds n_vars,
+ * n_felts, n_exts, then the vars (BN254 scalars, 8 little-endian limbs each), the felts, the exts (4 words each). */
+int32_t b2s_proof_witness_stream(b2s_engine* e, const uint8_t* proof_bytes, size_t proof_len, uint32_t** words,
+                                 size_t* n_words);
 
 /* The quotient kernels of an AIR are generated as PTX from its constraint DAG when the key is loaded and compiled by
  * the driver (openvm_b200/csrc/qjit.cu; B2S_QUOTIENT_JIT=0 selects the interpreter instead). This entry point returns

@@ -56,6 +56,7 @@ SIGNATURES = {
     "b2s_coset_lde": (C.c_int32, [vp, vp, C.c_uint32, C.c_uint32, C.POINTER(vp)]),
     "b2s_mmcs_commit": (C.c_int32, [vp, C.POINTER(vp), C.c_size_t, u32p, C.POINTER(vp)]),
     "b2s_proof_hint_stream": (C.c_int32, [vp, C.c_char_p, C.c_size_t, C.POINTER(C.POINTER(C.c_uint32)), C.POINTER(C.c_size_t)]),
+    "b2s_proof_witness_stream": (C.c_int32, [vp, C.c_char_p, C.c_size_t, C.POINTER(C.POINTER(C.c_uint32)), C.POINTER(C.c_size_t)]),
     "b2s_shared_alloc": (C.c_int32, [vp, C.c_uint64, C.POINTER(vp), C.c_char_p]),
     "b2s_shared_free": (C.c_int32, [vp, vp]),
     "b2s_shared_open": (C.c_int32, [vp, C.c_char_p, C.POINTER(vp)]),

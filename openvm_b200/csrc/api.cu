@@ -675,6 +675,20 @@ int32_t b2s_proof_hint_stream(b2s_engine* e, const uint8_t* proof_bytes, size_t 
     });
 }
 
+int32_t b2s_proof_witness_stream(b2s_engine* e, const uint8_t* proof_bytes, size_t proof_len, uint32_t** words, size_t* n_words) {
+    if (!proof_bytes || !words || !n_words) return B2S_ERR_BAD_ARG;
+    *words = nullptr;
+    *n_words = 0;
+    return guarded(e, [&] {
+        const std::vector<uint32_t> v = proof_witness_stream(proof_bytes, proof_len);
+        uint32_t* out = (uint32_t*)malloc(v.size() * 4);
+        B2_REQUIRE(out != nullptr, B2S_ERR_OOM, "witness stream: out of host memory");
+        memcpy(out, v.data(), v.size() * 4);
+        *words = out;
+        *n_words = v.size();
+    });
+}
+
 size_t b2s_pcs_num_matrices(const b2s_pcs_data* d) { return d ? d->mats.size() : 0; }
 uint32_t b2s_pcs_log_max_height(const b2s_pcs_data* d) { return d ? d->log_max_height : 0; }
 const b2s_matrix* b2s_pcs_matrix(const b2s_pcs_data* d, size_t i) { return (d && i < d->mats.size()) ? d->mats[i] : nullptr; }

@@ -223,6 +223,7 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* words, size_t n, bool host_only =
 void pk_free(b2s_pk* pk);
 void verify(const b2s_engine* e, const b2s_pk* pk, const uint8_t* proof, size_t len);
 std::vector<uint32_t> proof_hint_stream(const uint8_t* proof, size_t len);
+std::vector<uint32_t> proof_witness_stream(const uint8_t* bytes, size_t len);
 void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_airs, std::vector<uint8_t>& out);
 // api.cu helpers shared with the prover
 b2s_matrix* new_matrix(b2s_engine* e, uint64_t height, uint64_t width);

@@ -649,4 +649,57 @@ std::vector<uint32_t> proof_hint_stream(const uint8_t* bytes, size_t len) {
     return w.out;
 }
 
+// Root proof -> witness of the static halo2 verifier (b2s_proof_witness_stream): what Witnessable::write produces for
+// Proof<BabyBearPoseidon2RootConfig> (extensions/native/recursion/src/witness.rs:36-293, fri/witness.rs:19-141), i.e. the input
+// crates/sdk/src/prover/halo2.rs feeds the wrapper circuit. Three append-only streams: vars (every digest, one scalar of
+// eight canonical limbs), felts (opened rows, public values, both proof-of-work witnesses), exts (opened values, FRI
+// siblings, final polynomial, exposed sums). Lengths, air ids, degrees and the height permutation are constants of the
+// static circuit and write nothing. Layout returned: n_vars, n_felts, n_exts, vars, felts, exts.
+std::vector<uint32_t> proof_witness_stream(const uint8_t* bytes, size_t len) {
+    const DecodedProof p = decode(bytes, len, true);
+    std::vector<uint32_t> vars, felts, exts;
+    auto var = [&](const Digest& d) { for (int k = 0; k < 8; k++) vars.push_back(d[k].v); };
+    auto felt = [&](Fp x) { felts.push_back(x.to_canonical()); };
+    auto ext = [&](const Fp4& e) { for (int k = 0; k < 4; k++) exts.push_back(e.c[k].to_canonical()); };
+    auto adjs = [&](const std::vector<AdjacentOpened>& v) {
+        for (auto& a : v) {
+            for (auto& e : a.local) ext(e);
+            for (auto& e : a.next) ext(e);
+        }
+    };
+    // Commitments are written after_challenge, main_trace, quotient (witness.rs:218-240)
+    for (auto& c : p.after_commits) var(c);
+    for (auto& c : p.main_commits) var(c);
+    var(p.quotient_commit);
+    // FriProof (fri/witness.rs:61-83)
+    for (auto& c : p.fri_commits) var(c);
+    for (auto& q : p.queries) {
+        for (auto& b : q.input_proof) {
+            for (auto& row : b.opened_values) for (Fp x : row) felt(x);
+            for (auto& d : b.opening_proof) var(d);
+        }
+        for (auto& st : q.commit_phase_openings) {
+            ext(st.sibling_value);
+            for (auto& d : st.opening_proof) var(d);
+        }
+    }
+    for (auto& e : p.final_poly) ext(e);
+    felt(p.pow_witness);
+    // OpenedValues: preprocessed, main, quotient, after_challenge (witness.rs:250-274)
+    adjs(p.opened_prep);
+    for (auto& part : p.opened_main) adjs(part);
+    for (auto& air : p.opened_quotient) for (auto& chunk : air) for (auto& e : chunk) ext(e);
+    for (auto& ph : p.opened_after) adjs(ph);
+    for (auto& a : p.per_air) {
+        for (auto& v : a.exposed) for (auto& e : v) ext(e);
+        for (Fp x : a.public_values) felt(x);
+    }
+    felts.push_back(p.has_logup_witness ? p.logup_witness.to_canonical() : 0u);
+    std::vector<uint32_t> out = {(uint32_t)(vars.size() / 8), (uint32_t)felts.size(), (uint32_t)(exts.size() / 4)};
+    out.insert(out.end(), vars.begin(), vars.end());
+    out.insert(out.end(), felts.begin(), felts.end());
+    out.insert(out.end(), exts.begin(), exts.end());
+    return out;
+}
+
 }  // namespace b2

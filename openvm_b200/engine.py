@@ -391,6 +391,17 @@ class B2Engine:
             i += 1 + ln
         return out
 
+    def proof_witness_stream(self, proof):
+        """Witnessable::write of a root-configuration proof (extensions/native/recursion/src/witness.rs:147-190): the witness
+        of the static halo2 verifier as (vars [n, 8 limbs], felts [n], exts [n, 4])."""
+        words, n = C.POINTER(C.c_uint32)(), C.c_size_t()
+        self._check(self._lib.b2s_proof_witness_stream(self._h, bytes(proof), len(proof), C.byref(words), C.byref(n)))
+        flat = np.ctypeslib.as_array(words, shape=(n.value,)).copy()
+        self._lib.b2s_free(words)
+        nv, nf, ne = (int(x) for x in flat[:3])
+        a, b = 3 + 8 * nv, 3 + 8 * nv + nf
+        return flat[3:a].reshape(nv, 8), flat[a:b], flat[b:b + 4 * ne].reshape(ne, 4)
+
     def set_pow_witnesses(self, logup_witness=None, fri_witness=None):
         """Replay aid: use the given proof-of-work witnesses instead of searching for the minimum ones."""
         s = 0xFFFFFFFF

@@ -144,6 +144,7 @@ void orc_fill_synthetic(uint32_t* out, uint64_t height, uint64_t width, uint64_t
 // ---- STARK prove / verify (oracle/stark.hpp, oracle/stark_verify.hpp) -------------------------------------
 #include "stark_verify.hpp"
 #include "hints.hpp"
+#include "witness.hpp"
 static std::string g_orc_error;
 extern "C" {
 const char* orc_last_error() { return g_orc_error.c_str(); }
@@ -263,6 +264,29 @@ void orc_challenger_script(const uint32_t* ops, const uint32_t* args, size_t n_o
             for (int w = 0; w < 8; w++) d[w].v = digests[8 * args[i] + w];
             ch.observe_digest(d);
         } else out[k++] = ch.sample().v;
+    }
+}
+
+// root proof bytes -> witness streams (oracle/witness.hpp), flattened as n_vars, n_felts, n_exts, then the vars (8 limbs
+// each), the felts, the exts (4 words each). Decoded under the root configuration whatever the switch says.
+int orc_proof_witness_stream(const uint8_t* proof, size_t len, uint32_t** words_out, size_t* n_out) {
+    const int saved = hash_kind();
+    try {
+        hash_kind() = 1;
+        const Witness w = witness_stream(decode_proof(proof, len));
+        hash_kind() = saved;
+        std::vector<uint32_t> flat = {(uint32_t)w.vars.size(), (uint32_t)w.felts.size(), (uint32_t)w.exts.size()};
+        for (auto& d : w.vars) for (int k = 0; k < 8; k++) flat.push_back(d[k].v);
+        for (auto& f : w.felts) flat.push_back(f.v);
+        for (auto& e : w.exts) for (int k = 0; k < 4; k++) flat.push_back(e.c[k].v);
+        *words_out = (uint32_t*)malloc(flat.size() * 4 + 4);
+        memcpy(*words_out, flat.data(), flat.size() * 4);
+        *n_out = flat.size();
+        return 0;
+    } catch (const std::exception& ex) {
+        hash_kind() = saved;
+        g_orc_error = ex.what();
+        return -1;
     }
 }
 

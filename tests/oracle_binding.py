@@ -201,6 +201,20 @@ class Oracle:
                                        C.c_void_p(digests.ctypes.data), C.c_void_p(out.ctypes.data))
         return out[:int((ops == 2).sum())]
 
+    def proof_witness_stream(self, proof):
+        """Root proof bytes -> (vars [n, 8], felts [n], exts [n, 4]): oracle/witness.hpp."""
+        buf = (C.c_uint8 * len(proof)).from_buffer_copy(proof)
+        words, n = C.POINTER(C.c_uint32)(), C.c_size_t()
+        self.lib.orc_proof_witness_stream.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.POINTER(C.c_uint32)), C.POINTER(C.c_size_t)]
+        rc = self.lib.orc_proof_witness_stream(buf, len(proof), C.byref(words), C.byref(n))
+        if rc != 0:
+            raise RuntimeError(self.lib.orc_last_error().decode())
+        flat = np.ctypeslib.as_array(words, shape=(n.value,)).copy()
+        self.lib.orc_free(words)
+        nv, nf, ne = (int(x) for x in flat[:3])
+        a, b = 3 + 8 * nv, 3 + 8 * nv + nf
+        return flat[3:a].reshape(nv, 8), flat[a:b], flat[b:b + 4 * ne].reshape(ne, 4)
+
     def challenger_run(self, observed, n_samples):
         obs = np.ascontiguousarray(observed, dtype=np.uint32)
         out = np.zeros(n_samples, dtype=np.uint32)

@@ -188,9 +188,11 @@ def test_root_multi_air_prep_cached_logup_bytes(orc):
             q[pos] ^= 1 << int(rng2.integers(0, 8))
             assert orc.stark_verify(key, bytes(q), b, queries, pow_bits) is not None
             assert gpu_verify(eng, key, bytes(q)) is not None
-        # a key loaded under the inner hash cannot be used with the root engine's proofs
+        # the inner verifier's hint stream is not defined for a root proof; its counterpart is the halo2 witness
         with pytest.raises(Exception):
             eng.proof_hint_stream(proof)
+        for a, b in zip(eng.proof_witness_stream(proof), orc.proof_witness_stream(proof)):
+            assert np.array_equal(a, b)
     finally:
         orc.set_hash(0)
         eng.close()
