@@ -183,7 +183,7 @@ void b2s_pcs_free(b2s_pcs_data* d);
  *                                                        crates/sdk/src/prover/vm/mod.rs:23
  * The reference's MultiStarkProvingKey is a serde type of the un-vendored openvm-stark-backend; the Rust shim
  *  flattens it into this library's key blob: little-endian u32 words
- *   'B2PK', 2, pre_hash[8], log_up_pow_bits, num_airs, then per AIR
+ *   'B2PK', version (2 or 3), pre_hash[8], log_up_pow_bits, num_airs, then per AIR
  *     width_preprocessed, n_cached, cached_widths[], width_common_main, width_after_challenge, log_quotient_degree,
  *     num_public_values, num_exposed_values,
  *     [if width_preprocessed: commit[8], log_height, row-major canonical trace]
@@ -191,6 +191,9 @@ void b2s_pcs_free(b2s_pcs_data* d);
  *     num_interactions, per interaction {bus, type (0 send / 1 receive), count_node, n_fields, field_nodes[]},
  *     num_chunks, per chunk {n, interaction indices[n]}   (FRI-LogUp: one reciprocal-sum column per chunk, then
  *     the running-sum column; width_after_challenge = num_chunks + 1 extension-field columns)
+ *   [version 3, after the AIRs: num_height_constraints, per constraint {coefficients[num_airs], threshold <= p} =
+ *    vk.trace_height_constraints (extensions/native/recursion/src/types.rs:70): b2s_prove refuses and b2s_verify rejects
+ *    heights with sum coefficients[air] * height >= threshold (crates/vm/src/arch/vm.rs:627-652, stark/mod.rs:836-901)]
  * (node kinds: 0 Constant 1 Preprocessed 2 Main 3 Permutation 4 Public 5 Challenge 6 Exposed 7 IsFirstRow
  *  8 IsLastRow 9 IsTransition 10 Add 11 Sub 12 Neg 13 Mul; content of SymbolicExpressionDag as consumed at
  *  extensions/native/recursion/src/stark/mod.rs:1023-1085, types.rs:19-95).

@@ -119,9 +119,11 @@ class Air:
         return self
 
 
-def key_blob(airs, pre_hash=None, log_up_pow_bits=0):
-    """airs: list of Air (prep_commit set where prep is not None). Returns the uint32 word array."""
-    w = [0x4B503242, 2]
+def key_blob(airs, pre_hash=None, log_up_pow_bits=0, trace_height_constraints=None):
+    """airs: list of Air (prep_commit set where prep is not None). Returns the uint32 word array.
+    trace_height_constraints: list of (coefficients[one per AIR], threshold) -- the verifying key's LinearConstraint list
+    (extensions/native/recursion/src/types.rs:70); given, the blob is version 3 and carries them after the AIRs."""
+    w = [0x4B503242, 2 if trace_height_constraints is None else 3]
     w += list(pre_hash if pre_hash is not None else range(101, 109))
     w += [log_up_pow_bits, len(airs)]
     for a in airs:
@@ -143,6 +145,11 @@ def key_blob(airs, pre_hash=None, log_up_pow_bits=0):
         w += [nch]
         for ch in a.chunks:
             w += [len(ch)] + ch
+    if trace_height_constraints is not None:
+        w += [len(trace_height_constraints)]
+        for coeffs, threshold in trace_height_constraints:
+            assert len(coeffs) == len(airs)
+            w += [int(c) for c in coeffs] + [int(threshold)]
     return np.array(w, dtype=np.uint32)
 
 

@@ -143,6 +143,20 @@ struct b2s_pk {
     int hash_kind = 0;                   // the engine's hash when the key was loaded (preprocessed commitments depend on it)
     uint32_t log_up_pow_bits = 0;
     std::vector<b2::AirKeyDev> airs;
+    // LinearConstraint list of the verifying key (extensions/native/recursion/src/types.rs:70): for every constraint,
+    // sum_i coefficients[air i] * height_i < threshold over the AIRs present in a proof (stark/mod.rs:836-901, vm.rs:627-652)
+    std::vector<std::vector<uint32_t>> height_coefficients;
+    std::vector<uint32_t> height_thresholds;
+    // index of the first violated constraint, or -1
+    template <class Ids, class Logs>
+    int violated_height_constraint(const Ids& air_ids, const Logs& log_heights, size_t n) const {
+        for (size_t c = 0; c < height_thresholds.size(); c++) {
+            unsigned __int128 sum = 0;
+            for (size_t k = 0; k < n; k++) sum += (unsigned __int128)height_coefficients[c][air_ids[k]] << log_heights[k];
+            if (sum >= height_thresholds[c]) return (int)c;
+        }
+        return -1;
+    }
 };
 
 namespace b2 {

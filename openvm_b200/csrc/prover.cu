@@ -221,7 +221,8 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n, bool host_only, uint
         return w[i++];
     };
     B2_REQUIRE(rd() == 0x4B503242u, B2S_ERR_BAD_ARG, "key blob: bad magic");
-    B2_REQUIRE(rd() == 2, B2S_ERR_BAD_ARG, "key blob: unsupported version");
+    const uint32_t version = rd();   // 2: no trace-height constraints; 3: they follow the AIRs
+    B2_REQUIRE(version == 2 || version == 3, B2S_ERR_BAD_ARG, "key blob: unsupported version");
     b2s_pk* pk = new b2s_pk();
     pk->eng = host_only ? nullptr : e;
     pk->hash_kind = e ? e->hash_kind : 0;
@@ -320,6 +321,18 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n, bool host_only, uint
                 a.iprogram = std::move(ip.program);
                 a.islots = ip.slots_f;
                 a.d_iprogram = up(a.iprogram);
+            }
+        }
+        if (version >= 3) {
+            const uint32_t nhc = rd();
+            B2_REQUIRE((uint64_t)nhc * (pk->airs.size() + 1) <= n - i, B2S_ERR_BAD_ARG, "key blob truncated (trace-height constraints)");
+            pk->height_coefficients.resize(nhc);
+            pk->height_thresholds.resize(nhc);
+            for (uint32_t c = 0; c < nhc; c++) {
+                pk->height_coefficients[c].resize(pk->airs.size());
+                for (auto& x : pk->height_coefficients[c]) x = rd();
+                pk->height_thresholds[c] = rd();
+                B2_REQUIRE(pk->height_thresholds[c] <= P, B2S_ERR_BAD_ARG, "key: trace-height threshold above the field order");
             }
         }
         B2_REQUIRE(i == n, B2S_ERR_BAD_ARG, "key blob: trailing words");
@@ -964,6 +977,12 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
         B2_REQUIRE(logn[i] + b <= TWO_ADICITY, B2S_ERR_SHAPE, "prove: trace too tall for this blowup");
         B2_REQUIRE(!k.width_prep || k.prep_log_height == logn[i], B2S_ERR_SHAPE, "prove: preprocessed trace height mismatch");
         log_max_height = std::max(log_max_height, logn[i]);
+    }
+    {   // crates/vm/src/arch/vm.rs:627-652: a proving context whose heights break a linear constraint of the key is refused
+        std::vector<uint32_t> ids(n_airs);
+        for (size_t i = 0; i < n_airs; i++) ids[i] = airs[i].air_id;
+        const int bad = pk->violated_height_constraint(ids, logn, n_airs);
+        B2_REQUIRE(bad < 0, B2S_ERR_SHAPE, "prove: trace heights violate linear constraint " + std::to_string(bad) + " of the key");
     }
     // transcript prefix (stark/mod.rs:140-149, 231-238, 247-254)
     ch.observe_digest(pk->pre_hash);

@@ -409,6 +409,11 @@ void verify(const b2s_engine* e, const b2s_pk* pk, const uint8_t* bytes, size_t 
             reject("InvalidProofShape: exposed values without interactions");
         }
     }
+    {   // stark/mod.rs:222-228, 836-901: the claimed heights satisfy the key's linear constraints
+        std::vector<uint32_t> ids(na);
+        for (size_t i = 0; i < na; i++) ids[i] = proof.per_air[i].air_id;
+        if (pk->violated_height_constraint(ids, logn, na) >= 0) reject("InvalidProofShape: trace heights violate a linear constraint");
+    }
     // transcript prefix (stark/mod.rs:140-149, 231-254)
     ch.observe_digest(pk->pre_hash);
     ch.observe_canonical((uint32_t)na);

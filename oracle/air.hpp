@@ -46,17 +46,36 @@ struct AirKey {
     uint32_t part_width(size_t p) const { return p < cached_widths.size() ? cached_widths[p] : width_common; }
 };
 
+// LinearConstraint of the verifying key (extensions/native/recursion/src/types.rs:70; checked at
+// extensions/native/recursion/src/stark/mod.rs:836-901 and, on the proving side, crates/vm/src/arch/vm.rs:627-652):
+// sum_i coefficients[air i] * height_i < threshold over the AIRs present in a proof
+struct HeightConstraint {
+    std::vector<uint32_t> coefficients;  // one per AIR of the key
+    uint32_t threshold = 0;              // <= p (view.rs:64)
+};
 struct KeyBlob {
     Digest pre_hash;
     uint32_t log_up_pow_bits = 0;
     std::vector<AirKey> airs;
+    std::vector<HeightConstraint> height_constraints;
+    // index of the first violated constraint for the given (air id, height) pairs, or -1
+    int violated_height_constraint(const std::vector<uint32_t>& ids, const std::vector<unsigned>& log_heights) const {
+        for (size_t c = 0; c < height_constraints.size(); c++) {
+            unsigned __int128 sum = 0;
+            for (size_t k = 0; k < ids.size(); k++)
+                sum += (unsigned __int128)height_constraints[c].coefficients[ids[k]] << log_heights[k];
+            if (sum >= height_constraints[c].threshold) return (int)c;
+        }
+        return -1;
+    }
 };
 
 inline KeyBlob parse_key(const uint32_t* w, size_t n) {
     size_t i = 0;
     auto rd = [&]() -> uint32_t { if (i >= n) throw std::runtime_error("key blob truncated"); return w[i++]; };
     if (rd() != 0x4B503242u) throw std::runtime_error("key blob: bad magic");
-    if (rd() != 2) throw std::runtime_error("key blob: bad version");
+    const uint32_t version = rd();   // 2: no trace-height constraints; 3: they follow the AIRs
+    if (version != 2 && version != 3) throw std::runtime_error("key blob: bad version");
     KeyBlob k;
     for (int j = 0; j < 8; j++) k.pre_hash[j] = F(rd());
     k.log_up_pow_bits = rd();
@@ -89,6 +108,15 @@ inline KeyBlob parse_key(const uint32_t* w, size_t n) {
         if (a.interactions.empty() != (a.width_after == 0) || (a.width_after && a.width_after != a.chunks.size() + 1) ||
             a.num_exposed != (a.width_after ? 1u : 0u))
             throw std::runtime_error("key blob: interaction / after-challenge shape mismatch");
+    }
+    if (version >= 3) {
+        k.height_constraints.resize(rd());
+        for (auto& hc : k.height_constraints) {
+            hc.coefficients.resize(k.airs.size());
+            for (auto& c : hc.coefficients) c = rd();
+            hc.threshold = rd();
+            if (hc.threshold > P) throw std::runtime_error("key blob: trace-height threshold above the field order");
+        }
     }
     if (i != n) throw std::runtime_error("key blob: trailing words");
     return k;

@@ -62,6 +62,8 @@ inline Proof stark_prove(const KeyBlob& key, const std::vector<AirInput>& airs, 
         if (k.log_qd > b) throw std::runtime_error("prove: quotient degree exceeds blowup");
         ids.push_back(a.air_id); pvs.push_back(a.public_values); logn.push_back(log2u(h));
     }
+    if (key.violated_height_constraint(ids, logn) >= 0)   // vm.rs:627-652 (LinearTraceHeightConstraintExceeded)
+        throw std::runtime_error("prove: trace heights violate a linear constraint of the key");
     observe_prefix(ch, key, ids, pvs);
     // --- commitments: preprocessed (from the key), cached mains (one tree each), all common mains in one tree
     std::vector<std::shared_ptr<Committed>> prep(airs.size()), cached;

@@ -37,6 +37,8 @@ inline void stark_verify(const KeyBlob& key, const Proof& proof, const FriParams
         }
         ids.push_back(a.air_id); pvs.push_back(a.public_values); logn.push_back(l);
     }
+    // stark/mod.rs:222-228, 836-901: the heights claimed by the proof satisfy the key's linear constraints
+    if (key.violated_height_constraint(ids, logn) >= 0) throw VerifyError("InvalidProofShape: trace heights violate a linear constraint");
     observe_prefix(ch, key, ids, pvs);
     size_t num_cached = 0, num_prep = 0;
     for (uint32_t id : ids) { num_cached += key.airs[id].cached_widths.size(); num_prep += key.airs[id].width_prep ? 1 : 0; }

@@ -305,3 +305,30 @@ def test_mixed_quotient_degrees_with_logup_bytes(orc):
                    expect="NonZeroCumulativeSum")
     finally:
         eng.close()
+
+
+def test_trace_height_constraints_bytes_and_rejection(orc):
+    """The key's LinearConstraint list (types.rs:70): b2s_prove refuses heights that break it (vm.rs:627-652), b2s_verify
+    rejects proofs that claim such heights (stark/mod.rs:836-901); same verdicts as the oracle."""
+    from openvm_b200 import B2StarkError
+    b, queries, pow_bits = 1, 3, 2
+    fib, ch = airs.fibonacci_air(), airs.chain_air(5)
+    air_objs = [fib, ch]
+    t0, pv0 = airs.fibonacci_trace(32)
+    p1, pv1 = airs.chain_trace(ch, 64, seed=6)
+    inputs = [(0, [t0], pv0), (1, p1, pv1)]
+    ok = airs.key_blob(air_objs, trace_height_constraints=[([1, 2], 161), ([0, 1], P)])
+    tight = airs.key_blob(air_objs, trace_height_constraints=[([0, 0], 1), ([1, 2], 160)])
+    eng = make_engine(b, queries, pow_bits)
+    try:
+        proof = check_same(orc, eng, ok, inputs, air_objs, b, queries, pow_bits)
+        assert proof == gpu_prove(eng, airs.key_blob(air_objs), inputs, air_objs)      # not part of the transcript
+        assert "trace heights" in gpu_verify(eng, tight, proof) and "trace heights" in orc.stark_verify(tight, proof, b, queries, pow_bits)
+        with pytest.raises(B2StarkError, match="linear constraint 1"):
+            gpu_prove(eng, tight, inputs, air_objs)
+        only_fib = gpu_prove(eng, tight, inputs[:1], air_objs)
+        assert gpu_verify(eng, tight, only_fib) is None
+        with pytest.raises(B2StarkError):
+            eng.device().transport_pk_to_device(airs.key_blob(air_objs, trace_height_constraints=[([1, 1], P + 1)]))
+    finally:
+        eng.close()

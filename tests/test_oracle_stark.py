@@ -228,3 +228,31 @@ def test_logup_three_per_chunk_quotient_degree4(orc):
     r2 = r.copy(); r2[17, 0] += 1          # one more copy of a message than was sent
     p2 = orc.stark_prove(key, [(0, [s], none), (1, [r2], none)], b, 4, 3)
     assert "NonZeroCumulativeSum" in orc.stark_verify(key, p2, b, 4, 3)
+
+
+def test_trace_height_constraints(orc):
+    """LinearConstraint list of the verifying key (extensions/native/recursion/src/types.rs:70): the verifier rejects heights
+    with sum coeff_i * height_i >= threshold (stark/mod.rs:836-901), the proving side refuses them (vm.rs:627-652)."""
+    fib, ch = airs.fibonacci_air(), airs.chain_air(5)
+    t0, pv0 = airs.fibonacci_trace(32)
+    p1, pv1 = airs.chain_trace(ch, 64, seed=6)
+    inputs = [(0, [t0], pv0), (1, p1, pv1)]
+    free = airs.key_blob([fib, ch])
+    proof = orc.stark_prove(free, inputs, 1, 3, 2)
+    # 1 * 32 + 2 * 64 = 160 < 161: satisfied, and the same proof (the constraints are not part of the transcript)
+    ok = airs.key_blob([fib, ch], trace_height_constraints=[([1, 2], 161), ([0, 1], P)])
+    assert orc.stark_prove(ok, inputs, 1, 3, 2) == proof
+    assert orc.stark_verify(ok, proof, 1, 3, 2) is None
+    # 160 >= 160: violated; an absent AIR contributes nothing
+    tight = airs.key_blob([fib, ch], trace_height_constraints=[([0, 0], 1), ([1, 2], 160)])
+    assert "trace heights" in orc.stark_verify(tight, proof, 1, 3, 2)
+    with pytest.raises(RuntimeError, match="linear constraint"):
+        orc.stark_prove(tight, inputs, 1, 3, 2)
+    only_fib = orc.stark_prove(tight, inputs[:1], 1, 3, 2)
+    assert orc.stark_verify(tight, only_fib, 1, 3, 2) is None
+    # large coefficients do not wrap: 2^31 * 64 is far above any threshold
+    big = airs.key_blob([fib, ch], trace_height_constraints=[([0, 1 << 31], P)])
+    assert "trace heights" in orc.stark_verify(big, proof, 1, 3, 2)
+    with pytest.raises(RuntimeError):
+        airs_bad = airs.key_blob([fib, ch], trace_height_constraints=[([1, 1], P + 1)])
+        orc.stark_prove(airs_bad, inputs, 1, 3, 2)
