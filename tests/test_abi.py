@@ -94,3 +94,21 @@ def test_quotient_ptx_assembles_for_sm_100a(tmp_path):
         assert len(mods) > 1   # the last case is split into several kernels
     finally:
         del os.environ["B2S_QUOTIENT_JIT_LINES"]
+
+
+def test_rust_ffi_bindings_are_current_and_complete():
+    """integration/b2stark-engine/src/ffi.rs (the binding a maintainer compiles into the reference) is the
+    output of tools/gen_ffi_rs.py on the current header and declares every function the header declares."""
+    import re
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import gen_ffi_rs as g
+    text = open(g.OUT).read()
+    assert text == g.render()
+    header = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "b2stark.h")).read(), flags=re.S)
+    declared = set(re.findall(r"\b(b2s_\w+)\s*\(", header))
+    bound = set(re.findall(r"pub fn (b2s_\w+)\(", text))
+    assert declared == bound and len(bound) >= 50
+    # every wrapper call in lib.rs goes to a bound symbol
+    lib_rs = open(os.path.join(ROOT, "integration", "b2stark-engine", "src", "lib.rs")).read()
+    assert set(re.findall(r"ffi::(b2s_\w+)", lib_rs)) <= bound
