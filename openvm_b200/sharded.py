@@ -46,6 +46,16 @@ def column_shards(width, world_size):
     return out
 
 
+def _compress_of(engine):
+    """The 2-to-1 compression of the engine's configuration: TruncatedPermutation over Poseidon2-BabyBear-16 (digests of
+    8 words), or over Poseidon2-BN254-3 on [left, right, 0] for the root configuration (digests of one scalar, 8 limbs)."""
+    dev = engine.device()
+    if engine.hash() != 0:
+        zero = np.zeros(8, dtype=np.uint32)
+        return lambda left, right: dev.poseidon2_bn254_permute(np.concatenate([left, right, zero]))[0, :8].copy()
+    return lambda left, right: dev.poseidon2_permute(np.concatenate([left, right]))[0, :8].copy()
+
+
 def combine_subroots(subroots, compress):
     """Top of the tree over G = 2^k sub-roots (in rank order). `compress(left8, right8) -> 8 words` is the 2-to-1
     Poseidon2 compression. Returns (root, levels) with levels[0] = the sub-roots, levels[-1] = [root]."""
@@ -160,10 +170,7 @@ def sharded_commit(engine, local_columns, width, log_blowup, group=None):
     dist.all_gather_into_tensor(allroots, mine, group=group)
     subroots = allroots.cpu().numpy().astype(np.uint32)
 
-    def compress(left, right):
-        return dev.poseidon2_permute(np.concatenate([left, right]))[0, :8].copy()
-
-    root, levels = combine_subroots(list(subroots), compress)
+    root, levels = combine_subroots(list(subroots), _compress_of(engine))
     log_height = rows.bit_length() - 1
     return root, ShardedPcsData(rank, world, log_height, width, local_pcs, levels, keep=(recv, block))
 
@@ -229,10 +236,7 @@ class ShardedCommitter:
         dist.all_gather_into_tensor(allroots, mine, group=self.group)
         subroots = allroots.cpu().numpy().astype(np.uint32)
 
-        def compress(left, right):
-            return dev.poseidon2_permute(np.concatenate([left, right]))[0, :8].copy()
-
-        root, levels = combine_subroots(list(subroots), compress)
+        root, levels = combine_subroots(list(subroots), _compress_of(self.engine))
         return root, ShardedPcsData(self.rank, self.world, self.rows.bit_length() - 1, self.width, local_pcs, levels,
                                     keep=(self,))
 

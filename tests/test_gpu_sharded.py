@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 P = 2013265921
 
 
-def _worker(rank, world, port, q, height, width, b, fused):
+def _worker(rank, world, port, q, height, width, b, fused, hash_kind=0):
     try:
         import torch.distributed as dist
         from openvm_b200 import B2Engine, FriParameters, sharded
@@ -21,6 +21,7 @@ def _worker(rank, world, port, q, height, width, b, fused):
         torch.cuda.set_device(rank)
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
         eng = B2Engine.new(FriParameters(log_blowup=b), rank)
+        eng.set_hash(hash_kind)
         dev = eng.device()
         trace = np.random.default_rng(9).integers(0, P, size=(height, width), dtype=np.uint64).astype(np.uint32)
         lo, hi = sharded.column_shards(width, world)[rank]
@@ -58,14 +59,15 @@ def _worker(rank, world, port, q, height, width, b, fused):
 
 
 @pytest.mark.parametrize("fused", [False, True], ids=["nccl_all_to_all", "fused_peer_stores"])
-@pytest.mark.parametrize("height,width,b", [(1 << 12, 19, 1), (1 << 18, 64, 1), (1 << 14, 9, 2), (4, 2, 1)])
-def test_sharded_commit_two_gpus(height, width, b, fused):
+@pytest.mark.parametrize("height,width,b,hash_kind", [(1 << 12, 19, 1, 0), (1 << 18, 64, 1, 0), (1 << 14, 9, 2, 0), (4, 2, 1, 0),
+                                                      (1 << 12, 19, 1, 1)], ids=["h12", "h18", "h14b2", "h2", "h12_root_hash"])
+def test_sharded_commit_two_gpus(height, width, b, hash_kind, fused):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, q, height, width, b, fused)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q, height, width, b, fused, hash_kind)) for r in range(2)]
     for p in procs: p.start()
     res = [q.get(timeout=600) for _ in range(2)]
     for p in procs: p.join(timeout=120)
