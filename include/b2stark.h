@@ -243,6 +243,10 @@ int32_t b2s_engine_set_pow_witnesses(b2s_engine* e, uint32_t logup_witness, uint
  * Returns B2S_OK, or B2S_ERR_VERIFY_FAILED with b2s_last_error naming the reference's VerificationError variant
  * (InvalidProofShape, InvalidOpeningArgument, InvalidPowWitness, NonZeroCumulativeSum, OodEvaluationMismatch ...). */
 int32_t b2s_verify(b2s_engine* e, const b2s_pk* pk, const uint8_t* proof_bytes, size_t proof_len);
+/* The same verdicts with no device and no engine (the verifier is host code): the key blob is parsed on the host, its
+ * preprocessed traces skipped and their commitments kept. hash_kind: B2S_HASH_*. */
+int32_t b2s_verify_host(const b2s_fri_params* params, int32_t hash_kind, const uint32_t* key_words, size_t n_words,
+                        const uint8_t* proof_bytes, size_t proof_len);
 
 /* Proof -> hint stream of the recursive verifier: what the next aggregation layer feeds its verifier program
  * (`proof.write()` of `Hintable for Proof<BabyBearPoseidon2Config>`, extensions/native/recursion/src/hints.rs:272-316,

@@ -15,7 +15,8 @@ from .engine import (  # noqa: F401
     B2StarkError,
     VerificationError,
     library_path,
+    verify_host,
 )
 
 __all__ = ["B2Engine", "B2Device", "DeviceMatrix", "PcsData", "ProvingKey", "AirProvingContext", "FriParameters", "B2StarkError", "VerificationError",
-           "library_path"]
+           "library_path", "verify_host"]

@@ -77,6 +77,7 @@ SIGNATURES = {
     "b2s_prove": (C.c_int32, [vp, vp, vp, C.c_size_t, C.POINTER(vp), C.POINTER(C.c_size_t)]),
     "b2s_poseidon2_permute": (C.c_int32, [vp, vp, C.c_size_t]),
     "b2s_poseidon2_bn254_permute": (C.c_int32, [vp, vp, C.c_size_t]),
+    "b2s_verify_host": (C.c_int32, [C.c_void_p, C.c_int32, vp, C.c_size_t, C.c_char_p, C.c_size_t]),
     "b2s_host_poseidon2_bn254_permute": (C.c_int32, [vp, C.c_size_t]),
     "b2s_engine_set_hash": (C.c_int32, [vp, C.c_int32]),
     "b2s_engine_hash": (C.c_int32, [vp]),

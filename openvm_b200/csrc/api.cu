@@ -659,6 +659,29 @@ int32_t b2s_verify(b2s_engine* e, const b2s_pk* pk, const uint8_t* proof_bytes, 
     });
 }
 
+// The verifier is host code (transcript, Merkle paths, constraint evaluation at zeta): this entry needs no device and no
+// engine -- the key blob is parsed on the host (preprocessed traces are skipped, their commitments kept).
+int32_t b2s_verify_host(const b2s_fri_params* params, int32_t hash_kind, const uint32_t* key_words, size_t n_words,
+                        const uint8_t* proof_bytes, size_t proof_len) {
+    if (!params || !key_words || !proof_bytes) return B2S_ERR_BAD_ARG;
+    return guarded(nullptr, [&] {
+        B2_REQUIRE(hash_kind == B2S_HASH_POSEIDON2_BABYBEAR || hash_kind == B2S_HASH_POSEIDON2_BN254, B2S_ERR_BAD_ARG, "unknown hash kind");
+        B2_REQUIRE(params->log_blowup >= 1 && params->log_blowup <= 4 && params->log_final_poly_len == 0, B2S_ERR_BAD_ARG,
+                   "verify: unsupported FRI parameters");
+        b2s_engine host;          // parameters only: no stream, no device memory, nothing to release
+        host.params = *params;
+        host.hash_kind = hash_kind;
+        b2s_pk* pk = pk_load(&host, key_words, n_words, true, params->log_blowup);
+        try {
+            verify(&host, pk, proof_bytes, proof_len);
+        } catch (...) {
+            pk_free(pk);
+            throw;
+        }
+        pk_free(pk);
+    });
+}
+
 int32_t b2s_proof_hint_stream(b2s_engine* e, const uint8_t* proof_bytes, size_t proof_len, uint32_t** words, size_t* n_words) {
     if (!proof_bytes || !words || !n_words) return B2S_ERR_BAD_ARG;
     *words = nullptr;

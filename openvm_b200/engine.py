@@ -32,6 +32,20 @@ class VerificationError(Exception):
     """openvm_stark_backend::verifier::VerificationError (variant name in the message)."""
 
 
+def verify_host(key_words, proof, fri_params, hash_kind=0):
+    """StarkEngine::verify without a device (b2s_verify_host): the verifier is host code. Returns None, or raises
+    VerificationError carrying the reference's error variant name."""
+    lib = _lib.load()
+    key = np.ascontiguousarray(key_words, dtype=np.uint32)
+    p = _lib.FriParams(fri_params.log_blowup, fri_params.log_final_poly_len, fri_params.num_queries, fri_params.proof_of_work_bits)
+    proof = bytes(proof)
+    st = lib.b2s_verify_host(C.byref(p), int(hash_kind), key.ctypes.data, key.size, proof, len(proof))
+    if st == _lib.ERR_VERIFY_FAILED:
+        raise VerificationError((lib.b2s_last_error(None) or b"").decode())
+    if st != 0:
+        raise B2StarkError(st, (lib.b2s_last_error(None) or b"").decode())
+
+
 def library_path():
     return _lib.LIB_PATH
 
