@@ -1033,6 +1033,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
         logup_witness = grind_device(e, scratch, ch, pk->log_up_pow_bits, e->pow_override[0]);
         challenges[0] = ch.sample_ext();
         challenges[1] = ch.sample_ext();
+        trace.mark("  logup: pow + challenges", 2);
         for (size_t i = 0; i < n_airs; i++) if (keys[i]->width_after) after_of.push_back(i);
         after_views.reserve(after_of.size());
         std::vector<uint32_t*> last_rows;
@@ -1075,6 +1076,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             v.eng = e; v.d = lp.out; v.height = N; v.width = (uint64_t)4 * k.width_after; v.owned = false;
             after_views.push_back(v);
         }
+        trace.mark("  logup: traces enqueued", 2);
         // cumulative sums = last row of each phi column
         {
             std::vector<OpenDesc> descs;
@@ -1090,9 +1092,11 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
                 ch.observe_ext(cs);
             }
         }
+        trace.mark("  logup: sums on host", 2);
         std::vector<const b2s_matrix*> ptrs;
         for (auto& v : after_views) ptrs.push_back(&v);
         after_pcs = commit_matrices(e, ptrs.data(), nullptr, ptrs.size());
+        trace.mark("  logup: commit enqueued", 2);
         scratch.pcs.push_back(after_pcs);
         root_monty(e, after_pcs, after_commit.data());
         ch.observe_digest(after_commit.data());
