@@ -101,3 +101,49 @@ def test_bad_arguments():
         verify_host(np.array([1, 2, 3], dtype=np.uint32), b"\x01\x00\x00\x00", FriParameters(log_blowup=1))
     with pytest.raises(B2StarkError):
         verify_host(airs.key_blob([airs.fibonacci_air()]), b"\x01\x00\x00\x00", FriParameters(log_blowup=1), 7)
+
+
+def test_decoder_and_key_parser_survive_structured_mutations(orc, kind):
+    """Length fields overwritten with extreme values, truncations, insertions, deletions and byte noise in the proof, extreme
+    words in the key blob: the library answers with a status (never a crash, a hang or a giant allocation) and accepts a mutant
+    only when it is byte-identical to the proof."""
+    import struct
+    from openvm_b200 import B2StarkError, FriParameters, VerificationError, verify_host
+    fib, snd, rcv = airs.fibonacci_air(), airs.dummy_interaction_air(2, True), airs.dummy_interaction_air(2, False)
+    key = airs.key_blob([fib, snd, rcv], log_up_pow_bits=3)
+    send, recv = interaction_traces(16, 32, 2, seed=4)
+    t0, pv0 = airs.fibonacci_trace(16)
+    proof = orc.stark_prove(key, [(0, [t0], pv0), (1, [send], NONE), (2, [recv], NONE)], 1, 3, 2)
+    fp = FriParameters(log_blowup=1, num_queries=3, proof_of_work_bits=2)
+    verify_host(key, proof, fp, kind)
+    rng = np.random.default_rng(7 + kind)
+    extremes = [0, 1, 2, 0xFFFFFFFF, 0x7FFFFFFF, len(proof), len(proof) // 4, 1 << 20]
+    for _ in range(600):
+        q = bytearray(proof)
+        m = int(rng.integers(0, 5))
+        if m == 0:
+            pos = int(rng.integers(0, len(q) - 4)) & ~3
+            q[pos:pos + 4] = struct.pack("<I", int(rng.choice(extremes)))
+        elif m == 1:
+            q = q[:int(rng.integers(0, len(q)))]
+        elif m == 2:
+            pos = int(rng.integers(0, len(q)))
+            q[pos:pos] = bytes(rng.integers(0, 256, size=int(rng.integers(1, 9)), dtype=np.uint8))
+        elif m == 3:
+            a = int(rng.integers(0, len(q) - 8))
+            del q[a:int(rng.integers(a, min(len(q), a + 64)))]
+        else:
+            for _ in range(int(rng.integers(1, 6))):
+                q[int(rng.integers(0, len(q)))] = int(rng.integers(0, 256))
+        try:
+            verify_host(key, bytes(q), fp, kind)
+            assert bytes(q) == proof
+        except VerificationError:
+            assert bytes(q) != proof
+    for _ in range(300):
+        k = key.copy()
+        k[int(rng.integers(0, k.size))] = int(rng.choice([0, 1, 2, 0xFFFFFFFF, 0x7FFFFFFF, 1 << 20, k.size]))
+        try:
+            verify_host(k, proof, fp, kind)
+        except (VerificationError, B2StarkError):
+            pass
