@@ -142,16 +142,23 @@ __global__ void gather_kernel(const OpenDesc* descs, uint32_t ndesc, uint32_t* o
 // one launch and one device-to-host copy for the whole list
 void gather_rows(b2s_engine* e, const std::vector<OpenDesc>& descs, size_t total_words, uint32_t* h_out) {
     if (descs.empty()) return;
-    OpenDesc* dd = (OpenDesc*)e->dmalloc(descs.size() * sizeof(OpenDesc));
-    uint32_t* dout = (uint32_t*)e->dmalloc(total_words * 4);
-    B2_CUDA(cudaMemcpyAsync(dd, descs.data(), descs.size() * sizeof(OpenDesc), cudaMemcpyHostToDevice, e->stream));
+    // both directions go through the engine's pinned buffer: a proof's query phase moves ~2 MB of descriptors down and
+    // ~1.4 MB of rows and paths up, and pageable copies of that size cost several times the kernel
+    const size_t db = descs.size() * sizeof(OpenDesc), ob = total_words * 4;
+    const size_t db_pad = (db + 255) & ~(size_t)255;
+    uint8_t* pin = (uint8_t*)e->host_pinned(db_pad + ob);
+    memcpy(pin, descs.data(), db);
+    OpenDesc* dd = (OpenDesc*)e->dmalloc(db);
+    uint32_t* dout = (uint32_t*)e->dmalloc(ob);
+    B2_CUDA(cudaMemcpyAsync(dd, pin, db, cudaMemcpyHostToDevice, e->stream));
     gather_kernel<<<(unsigned)descs.size(), 128, 0, e->stream>>>(dd, (uint32_t)descs.size(), dout);
     B2_CHECK_LAUNCH();
     e->launches[3]++;
-    B2_CUDA(cudaMemcpyAsync(h_out, dout, total_words * 4, cudaMemcpyDeviceToHost, e->stream));
+    B2_CUDA(cudaMemcpyAsync(pin + db_pad, dout, ob, cudaMemcpyDeviceToHost, e->stream));
     B2_CUDA(cudaStreamSynchronize(e->stream));
-    e->dfree(dd, descs.size() * sizeof(OpenDesc));
-    e->dfree(dout, total_words * 4);
+    memcpy(h_out, pin + db_pad, ob);
+    e->dfree(dd, db);
+    e->dfree(dout, ob);
 }
 void gather_open(b2s_engine* e, const b2s_pcs_data* d, uint64_t index, uint32_t* h_rows, uint32_t* h_proof) {
     B2_REQUIRE(index < ((uint64_t)1 << d->log_max_height), B2S_ERR_BAD_ARG, "open: index out of range");
