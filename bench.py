@@ -161,7 +161,7 @@ def main():
                     help="N > 1 only: also time ONE commitment of the same trace sharded across the N GPUs (strong scaling; "
                          "openvm_b200/sharded.py, last NTT pass storing into the peers' buffers over NVLink)")
     ap.add_argument("--proof-scale-log", type=int, default=0, help="log2 scale of the shape-replay segment heights")
-    ap.add_argument("--proof-engines", type=int, default=3,
+    ap.add_argument("--proof-engines", type=int, default=8,
                     help="engines proving concurrently on each GPU for the segments/s figure (one host thread each)")
     args = ap.parse_args()
     if args.impl == "reference":
