@@ -41,3 +41,136 @@ def gather_counts(value):
     out = [None] * dist.get_world_size()
     dist.all_gather_object(out, int(value))
     return out
+
+
+class ProverPool:
+    """K engines on one GPU, one host thread each, fed from one FIFO of proving jobs with dependencies.
+
+    Why: a proof alternates host work (transcript, round trips) with kernels too small to fill a B200, so several proofs in
+    flight raise segments/s (one engine 50/s, eight 81/s for the RV32IM-shaped segment) -- the reference keeps
+    one engine per VM kind on a GPU (crates/sdk/src/prover/stark.rs:62-75) and proves segments one after the other
+    (crates/vm/src/arch/vm.rs:979-1007). Jobs are the nodes of the continuation / aggregation DAG (segment i, leaf i after
+    segment i, an internal node after its <= 3 children: SURVEY.md 8e); a job becomes ready when its dependencies are done
+    and receives their results.
+
+        pool = ProverPool(lambda k: make_worker(k), engines=8)
+        a = pool.submit(lambda worker: worker.prove_segment(0))
+        b = pool.submit(lambda worker, proof: worker.prove_leaf(proof), deps=[a])
+        proofs = pool.results([a, b]); pool.close()
+
+    `make_worker(k)` runs on worker thread k and returns whatever the jobs need (typically an object holding a B2Engine, its
+    device keys and resident traces); the pool never touches CUDA itself, so it is tested on CPU with plain callables."""
+
+    def __init__(self, make_worker, engines=8):
+        import queue
+        import threading
+        if engines < 1:
+            raise ValueError("engines must be >= 1")
+        self._lock = threading.Condition()
+        self._ready = queue.Queue()
+        self._jobs = {}          # id -> [fn, deps, state, result]  state: 0 waiting, 1 queued/running, 2 done, 3 failed
+        self._waiters = {}       # dep id -> [job ids]
+        self._next = 0
+        self._closed = False
+        self._threads = [threading.Thread(target=self._run, args=(make_worker, k), daemon=True) for k in range(engines)]
+        self._startup_error = None
+        for t in self._threads:
+            t.start()
+
+    def submit(self, fn, deps=()):
+        """Queue `fn(worker, *results_of_deps)`; returns the job id. A job whose dependency failed fails with it."""
+        with self._lock:
+            if self._closed:
+                raise RuntimeError("pool is closed")
+            jid = self._next
+            self._next += 1
+            deps = list(deps)
+            for d in deps:
+                if d not in self._jobs:
+                    raise ValueError("unknown dependency %r" % (d,))
+            self._jobs[jid] = [fn, deps, 0, None]
+            pending = [d for d in deps if self._jobs[d][2] < 2]
+            for d in pending:
+                self._waiters.setdefault(d, []).append(jid)
+            if not pending:
+                self._release(jid)
+            return jid
+
+    def _release(self, jid):       # lock held: every dependency is finished
+        job = self._jobs[jid]
+        failed = [d for d in job[1] if self._jobs[d][2] == 3]
+        if failed:
+            self._finish(jid, 3, self._jobs[failed[0]][3])
+        else:
+            job[2] = 1
+            self._ready.put(jid)
+
+    def _finish(self, jid, state, result):   # lock held
+        job = self._jobs[jid]
+        job[2], job[3] = state, result
+        for w in self._waiters.pop(jid, []):
+            if all(self._jobs[d][2] >= 2 for d in self._jobs[w][1]):
+                self._release(w)
+        self._lock.notify_all()
+
+    def _run(self, make_worker, k):
+        try:
+            worker = make_worker(k)
+        except BaseException as ex:            # noqa: BLE001 - reported to whoever waits
+            with self._lock:
+                self._startup_error = ex
+                self._lock.notify_all()
+            worker = None
+        while True:
+            jid = self._ready.get()
+            if jid is None:
+                return
+            with self._lock:
+                fn, deps = self._jobs[jid][0], self._jobs[jid][1]
+                args = [self._jobs[d][3] for d in deps]
+            try:
+                if worker is None:
+                    raise RuntimeError("worker %d failed to start: %r" % (k, self._startup_error))
+                out, state = fn(worker, *args), 2
+            except BaseException as ex:        # noqa: BLE001
+                out, state = ex, 3
+            with self._lock:
+                self._finish(jid, state, out)
+
+    def result(self, jid, timeout=None):
+        """Blocks until job `jid` is done; returns its result or raises its exception."""
+        with self._lock:
+            if not self._lock.wait_for(lambda: self._jobs[jid][2] >= 2, timeout):
+                raise TimeoutError("job %d still running" % jid)
+            state, out = self._jobs[jid][2], self._jobs[jid][3]
+        if state == 3:
+            raise out
+        return out
+
+    def results(self, jids, timeout=None):
+        return [self.result(j, timeout) for j in jids]
+
+    def close(self):
+        with self._lock:
+            self._closed = True
+        for _ in self._threads:
+            self._ready.put(None)
+        for t in self._threads:
+            t.join()
+
+
+def submit_aggregation_tree(pool, n_segments, prove_segment, prove_leaf, prove_internal, num_children_internal=3):
+    """Queues the whole continuation DAG on `pool`: segment i; leaf i after segment i (1:1,
+    crates/sdk/src/config/mod.rs:26); internal nodes of arity 3 (:27) layer by layer until one proof is left. The callables
+    get (worker, index, *child_proofs). Returns (root job id, all job ids by layer)."""
+    segs = [pool.submit(lambda w, i=i: prove_segment(w, i)) for i in range(n_segments)]
+    layer = [pool.submit(lambda w, p, i=i: prove_leaf(w, i, p), deps=[s]) for i, s in enumerate(segs)]
+    layers = [segs, layer]
+    while len(layer) > 1:
+        nxt = []
+        for i in range(0, len(layer), num_children_internal):
+            kids = layer[i:i + num_children_internal]
+            nxt.append(pool.submit(lambda w, *ps, i=i // num_children_internal: prove_internal(w, i, *ps), deps=kids))
+        layer = nxt
+        layers.append(layer)
+    return layer[0], layers

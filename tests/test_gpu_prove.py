@@ -332,3 +332,46 @@ def test_trace_height_constraints_bytes_and_rejection(orc):
             eng.device().transport_pk_to_device(airs.key_blob(air_objs, trace_height_constraints=[([1, 1], P + 1)]))
     finally:
         eng.close()
+
+
+def test_prover_pool_concurrent_engines_give_the_oracle_bytes(orc):
+    """Several engines on one GPU, one host thread each (openvm_b200.scheduler.ProverPool): proofs made concurrently are the
+    proofs made alone, and a dependent job receives its parent's proof."""
+    from openvm_b200 import AirProvingContext, B2Engine, FriParameters, scheduler
+    b, queries, pow_bits = 1, 4, 3
+    air = airs.fibonacci_air()
+    key = build_key(orc, [air], b)
+    sizes = [32, 64, 128, 256, 512, 1024]
+    want = {n: orc.stark_prove(key, [(0, [airs.fibonacci_trace(n)[0]], airs.fibonacci_trace(n)[1])], b, queries, pow_bits) for n in sizes}
+
+    class Worker:
+        def __init__(self, k):
+            self.eng = B2Engine.new(FriParameters(log_blowup=b, num_queries=queries, proof_of_work_bits=pow_bits))
+            self.pk = self.eng.device().transport_pk_to_device(key)
+
+        def prove(self, n):
+            trace, pvs = airs.fibonacci_trace(n)
+            return self.eng.prove(self.pk, [AirProvingContext(0, self.eng.device().transport_matrix_to_device(trace), pvs)])
+
+        def check(self, proof):
+            self.eng.verify(self.pk, proof)
+            return len(proof)
+
+    workers = []
+
+    def make(k):
+        w = Worker(k)
+        workers.append(w)
+        return w
+
+    pool = scheduler.ProverPool(make, engines=3)
+    try:
+        jobs = {n: pool.submit(lambda w, n=n: w.prove(n)) for n in sizes for _ in range(1)}
+        checks = {n: pool.submit(lambda w, proof: w.check(proof), deps=[j]) for n, j in jobs.items()}
+        for n in sizes:
+            assert pool.result(jobs[n], timeout=120) == want[n]
+            assert pool.result(checks[n], timeout=120) == len(want[n])
+    finally:
+        pool.close()
+        for w in workers:
+            w.eng.close()

@@ -45,3 +45,70 @@ def test_gloo_world_size_2():
     assert res[0][1] == [0, 2, 4, 6] and res[1][1] == [1, 3, 5]
     assert res[0][2] == res[1][2] == 11.0
     assert res[0][3] == res[1][3] == [4, 3]
+
+
+def test_prover_pool_runs_the_aggregation_dag_in_dependency_order():
+    import threading
+    import time
+    started = []
+    lock = threading.Lock()
+
+    def make_worker(k):
+        return {"id": k}
+
+    def seg(w, i):
+        time.sleep(0.002 * (7 - i % 7))            # finish out of order
+        with lock:
+            started.append(("seg", i))
+        return ("seg", i, w["id"])
+
+    def leaf(w, i, proof):
+        assert proof[:2] == ("seg", i)
+        with lock:
+            started.append(("leaf", i))
+        return ("leaf", [i])
+
+    def internal(w, i, *kids):
+        assert 1 <= len(kids) <= 3 and all(k[0] in ("leaf", "node") for k in kids)
+        return ("node", sorted(x for k in kids for x in k[1]))
+
+    pool = scheduler.ProverPool(make_worker, engines=4)
+    try:
+        root, layers = scheduler.submit_aggregation_tree(pool, 16, seg, leaf, internal)
+        assert [len(l) for l in layers] == [16] + scheduler.aggregation_layers(16)
+        assert pool.result(root, timeout=30) == ("node", list(range(16)))
+        used = {r[2] for r in pool.results(layers[0])}
+        assert len(used) > 1                        # more than one engine took segments
+        for i in range(16):                         # a leaf never starts before its segment is done
+            assert started.index(("seg", i)) < started.index(("leaf", i))
+    finally:
+        pool.close()
+
+
+def test_prover_pool_failures_propagate_and_do_not_wedge():
+    def boom(w):
+        raise ValueError("bad trace")
+
+    pool = scheduler.ProverPool(lambda k: k, engines=2)
+    try:
+        a = pool.submit(boom)
+        b = pool.submit(lambda w, x: x, deps=[a])
+        c = pool.submit(lambda w: 7)
+        assert pool.result(c, timeout=10) == 7
+        import pytest
+        with pytest.raises(ValueError, match="bad trace"):
+            pool.result(a, timeout=10)
+        with pytest.raises(ValueError, match="bad trace"):
+            pool.result(b, timeout=10)
+        with pytest.raises(ValueError):
+            pool.submit(lambda w: 0, deps=[999])
+    finally:
+        pool.close()
+    bad = scheduler.ProverPool(lambda k: (_ for _ in ()).throw(RuntimeError("no device")), engines=1)
+    try:
+        j = bad.submit(lambda w: 1)
+        import pytest
+        with pytest.raises(RuntimeError, match="failed to start"):
+            bad.result(j, timeout=10)
+    finally:
+        bad.close()
