@@ -84,3 +84,15 @@ def test_product_reproduces_the_fixtures(orc):
             assert [int(x) for x in root] == INDEX["commit"][f"synthetic_2^8x40_b1_{tag}"]
         finally:
             eng.close()
+
+
+def test_product_verifier_accepts_the_fixtures_on_the_host(orc):
+    """b2s_verify_host (no device) on the frozen proofs: accepted under their configuration, rejected under the other."""
+    import make_golden
+    from openvm_b200 import FriParameters, VerificationError, verify_host
+    for name, (key, _, b, q, pw) in make_golden.cases(orc).items():
+        fp = FriParameters(log_blowup=b, num_queries=q, proof_of_work_bits=pw)
+        for tag, kind in (("inner", 0), ("root", 1)):
+            verify_host(key, read(f"{name}_{tag}.proof"), fp, kind)
+            with pytest.raises(VerificationError):
+                verify_host(key, read(f"{name}_{tag}.proof"), fp, 1 - kind)
