@@ -283,6 +283,25 @@ int32_t b2s_bench_modmul(b2s_engine* e, uint64_t threads, uint32_t iters, int32_
 /* Poseidon2 permutations/s with state in registers and no memory traffic */
 int32_t b2s_bench_poseidon2(b2s_engine* e, uint64_t threads, uint32_t iters, double* ms_out);
 
+/* ---- allocation-free entry point -----------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Poseidon2 Merkle root of ONE already-extended matrix (column-major, Montgomery form, on the CURRENT device,
+ * power-of-two height): the same tree b2s_mmcs_commit builds for that single matrix, bit for bit. The digest layers,
+ * which b2s_mmcs_commit takes from the engine's pool, live in a file-scope __device__ array of
+ * B2S_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit. The call takes no engine, launches on
+ * `cuda_stream` (cudaStream_t as void*, NULL = default stream), does not synchronise, and calls no cudaMalloc /
+ * cudaFree / allocating routine. d_root8 is DEVICE memory for 8 canonical words. Heights above B2S_STATIC_MAX_ROWS or
+ * widths above B2S_STATIC_MAX_WIDTH are refused with B2S_ERR_SHAPE (message: b2s_last_error(NULL)).
+ * All calls on a device share the scratch array (it keeps the last call's contents; nothing in it needs clearing,
+ * every word read was written earlier in the same call): calls that overlap on the GPU race -- order them on one stream
+ * or with events. (openvm_b200/csrc/noalloc.cu) */
+#define B2S_STATIC_MAX_ROWS 65536u
+#define B2S_STATIC_MAX_WIDTH 4096u
+#define B2S_STATIC_SCRATCH_BYTES (4u << 20)
+int32_t b2s_merkle_root_static(const uint32_t* d_matrix, uint64_t height, uint64_t width, uint32_t* d_root8,
+                               void* cuda_stream);
+
 void b2s_free(void* p); /* releases host buffers returned by the library */
 
 #ifdef __cplusplus

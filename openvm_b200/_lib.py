@@ -83,6 +83,7 @@ SIGNATURES = {
     "b2s_engine_hash": (C.c_int32, [vp]),
     "b2s_bench_modmul": (C.c_int32, [vp, C.c_uint64, C.c_uint32, C.c_int32, C.POINTER(C.c_double)]),
     "b2s_bench_poseidon2": (C.c_int32, [vp, C.c_uint64, C.c_uint32, C.POINTER(C.c_double)]),
+    "b2s_merkle_root_static": (C.c_int32, [vp, C.c_uint64, C.c_uint64, vp, vp]),
     "b2s_free": (None, [vp]),
 }
 

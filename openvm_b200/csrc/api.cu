@@ -11,6 +11,11 @@ namespace b2 {
 void free_scales(b2s_engine* e);
 static std::string g_last_error;
 static std::mutex g_err_mu;
+// message of a failure outside any engine (entry points that take no engine: noalloc.cu)
+void set_global_error(const std::string& msg) {
+    std::lock_guard<std::mutex> lk(g_err_mu);
+    g_last_error = msg;
+}
 }  // namespace b2
 
 // ---- engine internals ------------------------------------------------------------------------------------
