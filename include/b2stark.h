@@ -56,22 +56,34 @@ typedef struct {
     uint32_t proof_of_work_bits;
 } b2s_fri_params;
 
-/* Stage gauges, named after the reference's metrics (crates/prof/data/metrics.example.json). Times are
- * device milliseconds accumulated since the last b2s_reset_metrics, measured with CUDA events on the
- * engine's stream; *_launches count kernels launched by this library. */
+/* Device milliseconds accumulated since the last b2s_reset_metrics, measured with CUDA events on the engine's stream;
+ * *_launches count kernels launched by this library.
+ *  - lde / leaf_hash / compress: kernel classes. They run INSIDE commitments, so they break commit_total_ms (and the
+ *    *_commit gauges) down; they are not additive with them.
+ *  - commit_total_ms: every commitment made through the engine (b2s_commit*, b2s_mmcs_commit, and those inside b2s_prove).
+ *  - the seven gauges of the reference (crates/prof/data/metrics.example.json; emitted around
+ *    crates/vm/src/arch/vm.rs:1328-1399) for b2s_prove: the first six are DISJOINT intervals of one proof, in the order
+ *    they occur, so their sum is <= stark_prove_excluding_trace_time_ms (the remainder: transcript set-up, key lookups,
+ *    proof encoding). The FRI-LogUp proof-of-work grind is counted in generate_perm_trace_time_ms. */
 typedef struct {
     double lde_ms;              /* iNTT + coset NTT passes                      */
     double leaf_hash_ms;        /* Poseidon2 sponge over LDE rows                */
     double compress_ms;         /* Poseidon2 2-to-1 layers                       */
-    double commit_total_ms;     /* = main_trace_commit_time_ms for one commit    */
-    double quotient_ms;         /* quotient_poly_compute_time_ms                 */
-    double opening_ms;          /* pcs_opening_time_ms                           */
-    double prove_total_ms;      /* stark_prove_excluding_trace_time_ms           */
+    double commit_total_ms;
+    double main_trace_commit_time_ms;            /* LDE + Merkle tree of the common main traces               */
+    double generate_perm_trace_time_ms;          /* LogUp PoW, challenges, after-challenge traces, running sums */
+    double perm_trace_commit_time_ms;            /* commitment of the after-challenge traces                   */
+    double quotient_poly_compute_time_ms;        /* constraint evaluation on the quotient domain               */
+    double quotient_poly_commit_time_ms;         /* commitment of the quotient chunks                          */
+    double pcs_opening_time_ms;                  /* values at zeta, reduced openings, FRI commit phase, PoW, queries */
+    double stark_prove_excluding_trace_time_ms;  /* whole b2s_prove                                            */
     uint64_t lde_launches;
     uint64_t leaf_hash_launches;
     uint64_t compress_launches;
     uint64_t other_launches;
     uint64_t poseidon2_permutations; /* permutations executed on the device */
+    uint64_t quotient_jit_launches;          /* generated straight-line quotient kernels (qjit.cu)        */
+    uint64_t quotient_interpreter_launches;  /* quotient_kernel (B2S_QUOTIENT_JIT=0)                      */
 } b2s_metrics;
 
 /* ---- engine ------------------------------------------------------------------------------------------
@@ -197,9 +209,11 @@ void b2s_pcs_free(b2s_pcs_data* d);
  * (node kinds: 0 Constant 1 Preprocessed 2 Main 3 Permutation 4 Public 5 Challenge 6 Exposed 7 IsFirstRow
  *  8 IsLastRow 9 IsTransition 10 Add 11 Sub 12 Neg 13 Mul; content of SymbolicExpressionDag as consumed at
  *  extensions/native/recursion/src/stark/mod.rs:1023-1085, types.rs:19-95).
- * Loading uploads and commits the preprocessed traces (the root must equal the key's commit) and compiles each
- * constraint DAG into the register-allocated program the quotient kernel interprets, and each AIR's interaction
- * list into the program the LogUp trace kernel interprets. */
+ * Loading uploads and commits the preprocessed traces (the root must equal the key's commit), validates every DAG node,
+ * generates each AIR's quotient kernels as straight-line PTX from its constraint DAG (openvm_b200/csrc/qjit.cu; the
+ * driver compiles them once per key), and compiles each AIR's interaction list into the program the LogUp trace kernel
+ * interprets. With B2S_QUOTIENT_JIT=0 in the environment at load time the constraints run through an interpreter
+ * instead (same results; tests/test_gpu_prove.py compares both with the oracle). */
 typedef struct b2s_pk b2s_pk;
 int32_t b2s_pk_load(b2s_engine* e, const uint32_t* key_words, size_t n_words, b2s_pk** out);
 void b2s_pk_free(b2s_pk* pk);

@@ -16,10 +16,14 @@ class FriParams(C.Structure):
 
 class Metrics(C.Structure):
     _fields_ = [("lde_ms", C.c_double), ("leaf_hash_ms", C.c_double), ("compress_ms", C.c_double),
-                ("commit_total_ms", C.c_double), ("quotient_ms", C.c_double), ("opening_ms", C.c_double),
-                ("prove_total_ms", C.c_double), ("lde_launches", C.c_uint64), ("leaf_hash_launches", C.c_uint64),
+                ("commit_total_ms", C.c_double), ("main_trace_commit_time_ms", C.c_double),
+                ("generate_perm_trace_time_ms", C.c_double), ("perm_trace_commit_time_ms", C.c_double),
+                ("quotient_poly_compute_time_ms", C.c_double), ("quotient_poly_commit_time_ms", C.c_double),
+                ("pcs_opening_time_ms", C.c_double), ("stark_prove_excluding_trace_time_ms", C.c_double),
+                ("lde_launches", C.c_uint64), ("leaf_hash_launches", C.c_uint64),
                 ("compress_launches", C.c_uint64), ("other_launches", C.c_uint64),
-                ("poseidon2_permutations", C.c_uint64)]
+                ("poseidon2_permutations", C.c_uint64), ("quotient_jit_launches", C.c_uint64),
+                ("quotient_interpreter_launches", C.c_uint64)]
 
 
 ERR_VERIFY_FAILED = -6

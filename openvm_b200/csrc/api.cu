@@ -9,13 +9,10 @@ using namespace b2;
 
 namespace b2 {
 void free_scales(b2s_engine* e);
-static std::string g_last_error;
-static std::mutex g_err_mu;
-// message of a failure outside any engine (entry points that take no engine: noalloc.cu)
-void set_global_error(const std::string& msg) {
-    std::lock_guard<std::mutex> lk(g_err_mu);
-    g_last_error = msg;
-}
+// Message of the last failure on THIS host thread (b2s_last_error(NULL)): thread-local, so K proving threads cannot read
+// each other's messages or a string another thread is rewriting.
+static thread_local std::string g_last_error;
+void set_global_error(const std::string& msg) { g_last_error = msg; }
 }  // namespace b2
 
 // ---- engine internals ------------------------------------------------------------------------------------
@@ -103,17 +100,19 @@ int32_t guarded(const b2s_engine* e_const, F&& fn) {
         return B2S_OK;
     } catch (const StatusError& se) {
         if (e) e->last_error = se.msg;
-        std::lock_guard<std::mutex> lk(g_err_mu);
-        g_last_error = se.msg;
+        set_global_error(se.msg);
         return se.code;
     } catch (const std::bad_alloc&) {
         if (e) e->last_error = "host allocation failed";
+        set_global_error("host allocation failed");
         return B2S_ERR_OOM;
     } catch (const std::exception& ex) {
         if (e) e->last_error = ex.what();
+        set_global_error(ex.what());
         return B2S_ERR_INTERNAL;
     } catch (...) {
         if (e) e->last_error = "unknown failure";
+        set_global_error("unknown failure");
         return B2S_ERR_INTERNAL;
     }
 }
@@ -153,6 +152,8 @@ b2s_pcs_data* commit_host_streamed(b2s_engine* e, const uint32_t* host, uint64_t
     const uint64_t gq = e->hash_kind ? 16 : 8;          // columns per sponge block: a group ends on a block boundary
     const size_t state_bytes = e->hash_kind ? 96 : 64;  // sponge state of one row between groups
     uint64_t G = (((uint64_t)1 << 27) / N) & ~(gq - 1);
+    // B2S_COMMIT_HOST_GROUP_COLS (tuning / test aid): columns per upload group, rounded down to whole sponge blocks
+    if (const char* env = getenv("B2S_COMMIT_HOST_GROUP_COLS")) G = strtoull(env, nullptr, 10) & ~(gq - 1);
     if (G < gq) G = gq;
     if (G > W) G = W;
     const uint64_t ngroups = (W + G - 1) / G;
@@ -264,8 +265,19 @@ int32_t b2s_engine_new(const b2s_fri_params* params, int32_t cuda_device, b2s_en
         B2_CUDA(cudaGetDeviceProperties(&prop, cuda_device));
         B2_REQUIRE(prop.major >= 10, B2S_ERR_NO_DEVICE,
                    std::string("device ") + prop.name + " is not sm_100-class; this library is built for sm_100a only");
-        b2s_engine* e = new b2s_engine();
+        B2_REQUIRE(params->log_final_poly_len == 0, B2S_ERR_BAD_ARG,
+                   "log_final_poly_len must be 0 (the prover emits a constant final polynomial)");
+        struct Holder {   // the engine is released if stream or pool set-up throws
+            b2s_engine* e = new b2s_engine();
+            ~Holder() {
+                if (!e) return;
+                if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);
+                delete e;
+            }
+        } hold;
+        b2s_engine* e = hold.e;
         e->device = cuda_device;
+        e->num_sms = prop.multiProcessorCount;
         e->params = *params;
         B2_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
         e->own_stream = true;
@@ -274,6 +286,7 @@ int32_t b2s_engine_new(const b2s_fri_params* params, int32_t cuda_device, b2s_en
         uint64_t thresh = UINT64_MAX;
         B2_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
         *out = e;
+        hold.e = nullptr;
     });
 }
 
@@ -305,7 +318,7 @@ int32_t b2s_engine_fri_params(const b2s_engine* e, b2s_fri_params* out) {
 
 const char* b2s_last_error(const b2s_engine* e) {
     if (e) return e->last_error.c_str();
-    return g_last_error.c_str();
+    return g_last_error.c_str();   // this thread's own message
 }
 
 void* b2s_engine_stream(const b2s_engine* e) { return e ? (void*)e->stream : nullptr; }
@@ -331,6 +344,7 @@ int32_t b2s_reset_metrics(b2s_engine* e) {
         e->collect_timers();
         for (int s = 0; s < ST_COUNT; s++) e->timers[s].ms = 0;
         for (auto& l : e->launches) l = 0;
+        for (auto& l : e->quotient_launches) l = 0;
         e->permutations = 0;
     });
 }
@@ -344,9 +358,15 @@ int32_t b2s_get_metrics(b2s_engine* e, b2s_metrics* out) {
         out->leaf_hash_ms = e->timers[ST_LEAF].ms;
         out->compress_ms = e->timers[ST_COMPRESS].ms;
         out->commit_total_ms = e->timers[ST_COMMIT].ms;
-        out->quotient_ms = e->timers[ST_QUOTIENT].ms;
-        out->opening_ms = e->timers[ST_OPENING].ms;
-        out->prove_total_ms = e->timers[ST_PROVE].ms;
+        out->main_trace_commit_time_ms = e->timers[ST_MAIN_COMMIT].ms;
+        out->generate_perm_trace_time_ms = e->timers[ST_PERM_GEN].ms;
+        out->perm_trace_commit_time_ms = e->timers[ST_PERM_COMMIT].ms;
+        out->quotient_poly_compute_time_ms = e->timers[ST_QUOTIENT].ms;
+        out->quotient_poly_commit_time_ms = e->timers[ST_QUOTIENT_COMMIT].ms;
+        out->pcs_opening_time_ms = e->timers[ST_OPENING].ms;
+        out->stark_prove_excluding_trace_time_ms = e->timers[ST_PROVE].ms;
+        out->quotient_jit_launches = e->quotient_launches[0];
+        out->quotient_interpreter_launches = e->quotient_launches[1];
         out->lde_launches = e->launches[0];
         out->leaf_hash_launches = e->launches[1];
         out->compress_launches = e->launches[2];

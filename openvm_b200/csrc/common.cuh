@@ -15,7 +15,6 @@
 
 namespace b2 {
 
-constexpr int NUM_SMS_B200 = 148;
 
 struct StatusError {
     int32_t code;
@@ -43,7 +42,8 @@ struct StatusError {
 struct TwiddleSet;
 struct ScaleSet;
 
-enum Stage { ST_LDE = 0, ST_LEAF, ST_COMPRESS, ST_COMMIT, ST_QUOTIENT, ST_OPENING, ST_PROVE, ST_COUNT };
+enum Stage { ST_LDE = 0, ST_LEAF, ST_COMPRESS, ST_COMMIT, ST_MAIN_COMMIT, ST_PERM_GEN, ST_PERM_COMMIT, ST_QUOTIENT,
+             ST_QUOTIENT_COMMIT, ST_OPENING, ST_PROVE, ST_COUNT };
 
 struct StageTimer {
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending;
@@ -54,6 +54,7 @@ struct StageTimer {
 
 struct b2s_engine {
     int device = 0;
+    int num_sms = 0;                 // cudaDevAttrMultiProcessorCount of `device`, set by b2s_engine_new
     b2s_fri_params params{};
     cudaStream_t stream = nullptr;
     bool own_stream = false;
@@ -63,6 +64,7 @@ struct b2s_engine {
     b2::StageTimer timers[b2::ST_COUNT];
     std::vector<cudaEvent_t> event_pool;
     uint64_t launches[4] = {0, 0, 0, 0};  // lde, leaf, compress, other
+    uint64_t quotient_launches[2] = {0, 0};  // generated kernels, interpreter
     uint64_t permutations = 0;
     cudaStream_t copy_stream = nullptr;                     // host -> device staging of the streaming commit
     std::map<uint64_t, uint32_t*> selector_cache;           // (log height, log quotient degree, blowup) -> 4 planes

@@ -26,6 +26,8 @@
 //     per tile (several runs per block for small D), 1-in-32 padded shared memory, radix-16 register blocks.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace b2 {
 
 constexpr int K1_THREADS = 256;
@@ -508,10 +510,14 @@ __global__ void replicate_kernel(const uint32_t* in, uint64_t in_col_stride, uin
 template <int D, bool GATHER>
 static void launch_strided_t(b2s_engine* e, const PassParams& p, dim3 grid) {
     constexpr size_t smem = ((size_t)1 << D) * (GATHER ? 33 : 32) * 4;
-    static bool configured[64] = {};  // per device
-    if (smem > 48 * 1024 && !configured[e->device & 63]) {
-        B2_CUDA(cudaFuncSetAttribute(ntt_strided_kernel<D, GATHER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured[e->device & 63] = true;
+    if (smem > 48 * 1024) {
+        // once per device and instantiation; engines on several host threads share the flags
+        static std::once_flag configured[64];
+        cudaError_t err = cudaSuccess;
+        std::call_once(configured[e->device & 63], [&] {
+            err = cudaFuncSetAttribute(ntt_strided_kernel<D, GATHER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        });
+        B2_CUDA(err);
     }
     ntt_strided_kernel<D, GATHER><<<grid, K1_THREADS, smem, e->stream>>>(p);
     B2_CHECK_LAUNCH();

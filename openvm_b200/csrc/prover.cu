@@ -194,6 +194,31 @@ static Compiled compile_dag(const AirKeyDev& air, const std::vector<HostNode>& n
     return out;
 }
 
+// Every node of the DAG, live or dead, must be well-formed: the verifier evaluates all of them at zeta
+// (verifier.cu fold_constraints), so a malformed dead node would load, prove, and then fail every verification.
+static void validate_nodes(const AirKeyDev& air, const std::vector<HostNode>& nodes) {
+    const size_t parts = air.cached_widths.size() + (air.width_common ? 1 : 0);
+    auto part_width = [&](uint32_t p) { return p < air.cached_widths.size() ? air.cached_widths[p] : air.width_common; };
+    for (size_t i = 0; i < nodes.size(); i++) {
+        const HostNode& nd = nodes[i];
+        bool ok;
+        switch (nd.kind) {
+            case N_CONST: ok = nd.a < P; break;
+            case N_PREP: ok = nd.a < air.width_prep && nd.b < 2; break;
+            case N_MAIN: ok = nd.c < parts && nd.a < part_width(nd.c) && nd.b < 2; break;
+            case N_PERM: ok = nd.a < air.width_after && nd.b < 2; break;
+            case N_PUBLIC: ok = nd.a < air.num_pv; break;
+            case N_CHALLENGE: ok = nd.a < 2 && air.width_after; break;
+            case N_EXPOSED: ok = nd.a < air.num_exposed; break;
+            case N_FIRST: case N_LAST: case N_TRANS: ok = true; break;
+            case N_ADD: case N_SUB: case N_MUL: ok = nd.a < i && nd.b < i; break;
+            case N_NEG: ok = nd.a < i; break;
+            default: ok = false;
+        }
+        B2_REQUIRE(ok, B2S_ERR_BAD_ARG, "key: malformed DAG node " + std::to_string(i) + " (kind " + std::to_string(nd.kind) + ")");
+    }
+}
+
 static void root_monty(b2s_engine* e, const b2s_pcs_data* d, uint32_t out[8]) {
     B2_CUDA(cudaMemcpyAsync(out, d->layers.back(), 32, cudaMemcpyDeviceToHost, e->stream));
     B2_CUDA(cudaStreamSynchronize(e->stream));
@@ -250,6 +275,7 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n, bool host_only, uint
             if (a.width_prep) {
                 for (int j = 0; j < 8; j++) {
                     const uint32_t v = rd();
+                    B2_REQUIRE(root || v < P, B2S_ERR_BAD_ARG, "key blob: non-canonical preprocessed commitment");
                     a.prep_commit[j] = root ? v : Fp::from_canonical(v).v;
                 }
                 a.prep_log_height = rd();
@@ -303,6 +329,7 @@ b2s_pk* pk_load(b2s_engine* e, const uint32_t* w, size_t n, bool host_only, uint
             }
             B2_REQUIRE((ni == 0) == (a.width_after == 0) && (a.width_after == 0 || a.width_after == nch + 1), B2S_ERR_BAD_ARG,
                        "key: interaction / after-challenge shape mismatch");
+            validate_nodes(a, nodes);
             a.num_chunks = nch;
             for (auto& nd : nodes) a.nodes.push_back(make_uint4(nd.kind, nd.a, nd.b, nd.c));
             a.constraint_idx = cidx;
@@ -482,6 +509,7 @@ static void launch_quotient_t(b2s_engine* e, const QuotientParams& p) {
     quotient_kernel<NSLOT, NE><<<(rows + 127) / 128, 128, 0, e->stream>>>(p);
     B2_CHECK_LAUNCH();
     e->launches[3]++;
+    e->quotient_launches[1]++;
 }
 template <int NSLOT>
 static void launch_quotient_e(b2s_engine* e, uint32_t eslots, const QuotientParams& p) {
@@ -1006,9 +1034,11 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     std::vector<size_t> common_of;
     for (size_t i = 0; i < n_airs; i++) if (airs[i].common_main) { commons.push_back(airs[i].common_main); common_of.push_back(i); }
     B2_REQUIRE(!commons.empty(), B2S_ERR_SHAPE, "prove: no common main trace");
-    b2s_pcs_data* common_pcs = commit_matrices(e, commons.data(), nullptr, commons.size());
-    scratch.pcs.push_back(common_pcs);
+    b2s_pcs_data* common_pcs;
     {
+        StageScope ms(e, ST_MAIN_COMMIT);
+        common_pcs = commit_matrices(e, commons.data(), nullptr, commons.size());
+        scratch.pcs.push_back(common_pcs);
         std::array<uint32_t, 8> r;
         root_monty(e, common_pcs, r.data());
         main_commits.push_back(r);
@@ -1029,7 +1059,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     b2s_pcs_data* after_pcs = nullptr;
     std::array<uint32_t, 8> after_commit{};
     if (phase) {
-        StageScope ls(e, ST_QUOTIENT);
+        e->stage_begin(ST_PERM_GEN);
         logup_witness = grind_device(e, scratch, ch, pk->log_up_pow_bits, e->pow_override[0]);
         challenges[0] = ch.sample_ext();
         challenges[1] = ch.sample_ext();
@@ -1093,6 +1123,8 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             }
         }
         trace.mark("  logup: sums on host", 2);
+        e->stage_end(ST_PERM_GEN);
+        StageScope cs(e, ST_PERM_COMMIT);
         std::vector<const b2s_matrix*> ptrs;
         for (auto& v : after_views) ptrs.push_back(&v);
         after_pcs = commit_matrices(e, ptrs.data(), nullptr, ptrs.size());
@@ -1161,21 +1193,20 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             }
             if (!k.jit_kernels.empty()) {
                 // straight-line kernels generated from the DAG at key load (qjit.cu); same inputs, same output layout
-                const uint32_t* mats[16];
-                uint32_t nm = 0;
-                if (k.width_prep) mats[nm++] = k.prep_pcs->mats[0]->d;
-                for (uint32_t p = 0; p < airs[i].n_cached; p++) mats[nm++] = airs[i].cached[p]->mats[0]->d;
+                std::vector<const uint32_t*> mats;   // one entry per partition: a key may carry up to 1024 cached mains
+                if (k.width_prep) mats.push_back(k.prep_pcs->mats[0]->d);
+                for (uint32_t p = 0; p < airs[i].n_cached; p++) mats.push_back(airs[i].cached[p]->mats[0]->d);
                 if (k.width_common) {
                     size_t pos = std::find(common_of.begin(), common_of.end(), i) - common_of.begin();
-                    mats[nm++] = common_pcs->mats[pos]->d;
+                    mats.push_back(common_pcs->mats[pos]->d);
                 }
                 if (k.width_after) {
                     size_t pos = std::find(after_of.begin(), after_of.end(), i) - after_of.begin();
-                    mats[nm++] = after_pcs->mats[pos]->d;
+                    mats.push_back(after_pcs->mats[pos]->d);
                 }
-                B2_REQUIRE(nm == k.jit_num_mats, B2S_ERR_INTERNAL, "quotient JIT: matrix count mismatch");
+                B2_REQUIRE(mats.size() == k.jit_num_mats, B2S_ERR_INTERNAL, "quotient JIT: matrix count mismatch");
                 uint32_t* accbuf = k.jit_kernels.size() > 1 ? scratch.words((size_t)4 << (n + lq)) : nullptr;
-                quotient_jit_launch(e, k, mats, d_pv, d_apow, d_efc, accbuf, qp.out, n, lq);
+                quotient_jit_launch(e, k, mats.data(), d_pv, d_apow, d_efc, accbuf, qp.out, n, lq);
             } else {
                 launch_quotient(e, k.num_slots, k.num_slots_e, qp);
             }
@@ -1193,10 +1224,14 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     trace.mark("quotient eval");
     std::vector<const b2s_matrix*> chunk_ptrs;
     for (auto& v : chunk_views) chunk_ptrs.push_back(&v);
-    b2s_pcs_data* quotient_pcs = commit_matrices(e, chunk_ptrs.data(), chunk_shifts.data(), chunk_ptrs.size());
-    scratch.pcs.push_back(quotient_pcs);
+    b2s_pcs_data* quotient_pcs;
     std::array<uint32_t, 8> quotient_commit;
-    root_monty(e, quotient_pcs, quotient_commit.data());
+    {
+        StageScope cs(e, ST_QUOTIENT_COMMIT);
+        quotient_pcs = commit_matrices(e, chunk_ptrs.data(), chunk_shifts.data(), chunk_ptrs.size());
+        scratch.pcs.push_back(quotient_pcs);
+        root_monty(e, quotient_pcs, quotient_commit.data());
+    }
     ch.observe_digest(quotient_commit.data());
     const Fp4 zeta = ch.sample_ext();
 

@@ -491,6 +491,7 @@ void quotient_jit_launch(b2s_engine* e, const AirKeyDev& a, const uint32_t* cons
     for (void* k : a.jit_kernels) {
         B2_CUDA(cudaLaunchKernel((const void*)k, dim3((rows + 127) / 128), dim3(128), args.data(), 0, e->stream));
         e->launches[3]++;
+        e->quotient_launches[0]++;
     }
 }
 

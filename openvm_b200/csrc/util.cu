@@ -32,7 +32,7 @@ __global__ void convert_kernel(uint32_t* d, size_t n, int to_monty) {
 }
 void convert_repr(b2s_engine* e, uint32_t* d, size_t n, bool to_monty) {
     if (!n) return;
-    unsigned blocks = (unsigned)std::min<size_t>((n + 255) / 256, (size_t)NUM_SMS_B200 * 16);
+    unsigned blocks = (unsigned)std::min<size_t>((n + 255) / 256, (size_t)e->num_sms * 16);
     convert_kernel<<<blocks, 256, 0, e->stream>>>(d, n, to_monty ? 1 : 0);
     B2_CHECK_LAUNCH();
     e->launches[3]++;
@@ -121,7 +121,7 @@ __global__ void fill_kernel(uint32_t* d, uint64_t height, uint64_t width, uint64
 }
 void fill_synthetic(b2s_engine* e, uint32_t* d, uint64_t height, uint64_t width, uint64_t seed) {
     if (!height || !width) return;
-    fill_kernel<<<NUM_SMS_B200 * 16, 256, 0, e->stream>>>(d, height, width, seed);
+    fill_kernel<<<e->num_sms * 16, 256, 0, e->stream>>>(d, height, width, seed);
     B2_CHECK_LAUNCH();
     e->launches[3]++;
 }

@@ -15,7 +15,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
-import airs  # noqa: E402
+from openvm_b200 import airs  # noqa: E402
 import oracle_binding  # noqa: E402
 import pyref  # noqa: E402
 

@@ -112,7 +112,7 @@ def test_oracle_challenger_matches_python(root_orc):
 def test_oracle_root_config_proof_verifies(orc):
     """The oracle's whole prover and verifier follow the switch: a proof made under the root configuration verifies under
     it, is rejected under the other, and differs from the inner configuration's proof of the same statement."""
-    import airs
+    from openvm_b200 import airs
     from test_oracle_stark import interaction_traces
     fib, snd, rcv = airs.fibonacci_air(), airs.dummy_interaction_air(2, True), airs.dummy_interaction_air(2, False)
     key = airs.key_blob([fib, snd, rcv], log_up_pow_bits=3)

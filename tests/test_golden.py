@@ -58,7 +58,7 @@ def test_product_reproduces_the_fixtures(orc):
     import make_golden
     from openvm_b200 import B2Engine, FriParameters, VerificationError
     from test_gpu_prove import gpu_prove
-    import airs
+    from openvm_b200 import airs
     objs = {"fib32": [airs.fibonacci_air()],
             "fib8_logup": [airs.fibonacci_air(), airs.dummy_interaction_air(2, True), airs.dummy_interaction_air(2, False)]}
     for kind, tag in ((0, "inner"), (1, "root")):

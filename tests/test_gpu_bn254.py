@@ -135,7 +135,7 @@ def _same_proof(orc, eng, key, inputs, air_objs, b, queries, pow_bits, expect=No
 
 @pytest.mark.parametrize("n,b,queries,pow_bits", [(32, 1, 4, 3), (8, 2, 3, 0), (1 << 10, 1, 5, 8)])
 def test_root_fibonacci_proof_bytes(orc, n, b, queries, pow_bits):
-    import airs
+    from openvm_b200 import airs
     from test_oracle_stark import build_key
     eng = _root_engine(orc, b, queries, pow_bits)
     try:
@@ -152,7 +152,7 @@ def test_root_fibonacci_proof_bytes(orc, n, b, queries, pow_bits):
 
 
 def test_root_multi_air_prep_cached_logup_bytes(orc):
-    import airs
+    from openvm_b200 import airs
     from test_oracle_stark import build_key, interaction_traces
     from test_gpu_prove import gpu_prove, gpu_verify
     b, queries, pow_bits = 1, 6, 4

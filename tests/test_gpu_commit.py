@@ -161,3 +161,51 @@ def test_leaf_hash_code_paths_agree(orc, knob):
         ms = [rng2.integers(0, P, size=(h, w), dtype=np.uint64).astype(np.uint32) for h, w in group]
         want_root = orc.commit(ms, 1)
         assert g == [int(x) for x in want_root], (knob, group)
+
+
+# ---- the two-pipe persistent leaf kernel at its SHIPPED threshold (levels of >= 2^19 nodes, merkle.cu MIX_MIN_ROWS) ------
+# No environment override: these are the code paths the full-size commit runs. Oracle cost: seconds.
+@pytest.mark.parametrize("shapes", [
+    [(1 << 19, 8)],                       # one full sponge block per row
+    [(1 << 19, 19)],                      # ragged last block
+    [(1 << 19, 40)],
+    [(1 << 20, 3), (1 << 19, 9)],         # compress-and-inject level of 2^19 nodes (leaf_mixed_kernel<ColTable, PREV>)
+    [(1 << 20, 11), (1 << 20, 6)],        # a sponge block straddling two matrices on a 2^20-row level
+])
+def test_mixed_pipe_leaf_kernel_at_shipped_threshold(engine, orc, shapes):
+    import os
+    assert "B2S_HASH_MIN_LOG" not in os.environ and "B2S_HASH_F64" not in os.environ
+    dev = engine.device()
+    big = np.random.default_rng(19)
+    mats = [big.integers(0, P, size=(h, w), dtype=np.uint64).astype(np.uint32) for h, w in shapes]
+    dmats = [dev.transport_matrix_to_device(m) for m in mats]
+    root, pcs = dev.mmcs_commit(dmats)
+    want_root, want_layers = orc.mmcs_commit(mats, want_layers=True)
+    assert np.array_equal(root, want_root)
+    hmax = max(h for h, _ in shapes)
+    for level in (0, 1):                  # the leaf level and the level above it (the injected one in case 4)
+        off = 0 if level == 0 else hmax
+        n = hmax >> level
+        assert np.array_equal(pcs.layer(level), want_layers[off:off + n]), f"layer {level}"
+    rows, proof = pcs.open_batch(hmax - 3)
+    ok, want_proof = orc.mmcs_open_verify(mats, hmax - 3)
+    assert ok and np.array_equal(proof, want_proof)
+    pcs.free()
+    for d in dmats:
+        d.free()
+
+
+def test_streamed_host_commit_at_shipped_threshold(engine, orc):
+    """b2s_commit_host on a trace tall enough for the persistent kernel's suspend / resume path (leaf_absorb over column
+    groups: state planes between groups) -- root equals the oracle's commit."""
+    dev = engine.device()
+    h, w = 1 << 18, 24                    # LDE 2^19 rows; column groups of 8 force three absorb calls
+    m = np.random.default_rng(23).integers(0, P, size=(h, w), dtype=np.uint64).astype(np.uint32)
+    import os
+    os.environ["B2S_COMMIT_HOST_GROUP_COLS"] = "8"
+    try:
+        root, pcs = dev.commit_host(m)
+    finally:
+        del os.environ["B2S_COMMIT_HOST_GROUP_COLS"]
+    assert np.array_equal(root, orc.commit([m], 1))
+    pcs.free()

@@ -3,7 +3,7 @@ and the oracle's verifier (transliterated from the in-tree recursive verifier) a
 import numpy as np
 import pytest
 
-import airs
+from openvm_b200 import airs
 from test_oracle_stark import build_key
 
 pytestmark = pytest.mark.gpu
@@ -177,6 +177,51 @@ def test_logup_prep_cached_rotated_fields_bytes(orc, n, b):
         check_same(orc, eng, key, [(0, parts, pv), (1, [recv], NONE)], air_objs, b, queries, pow_bits)
     finally:
         eng.close()
+
+
+# ---- every quotient code path against the ORACLE's bytes -----------------------------------------------------------------
+# (a) generated code split into several kernels (the accumulator plane carries the fold from kernel to kernel, qjit.cu), as
+#     bench.py's segment / Keccak shapes run it; (b) the interpreter (B2S_QUOTIENT_JIT=0). Both environment variables are read
+#     when the key is loaded. The metrics say which kernels actually ran.
+def _prove_lookup_parts(orc, monkeypatch, env, n, b):
+    queries, pow_bits = 4, 3
+    a0 = airs.lookup_chain_air_parts(6, n, seed=2)     # LogUp + preprocessed + cached partitions + rotated fields
+    a1 = airs.multi_receiver_air([2, 3], 5)
+    a2 = airs.chain_air(40)                            # widest byte-parity AIR, base field only
+    air_objs = [a0, a1, a2]
+    key = build_key(orc, air_objs, b)
+    parts, pv = airs.chain_trace(a0, n, seed=8)
+    recv = airs.lookup_chain_parts_receiver_trace(a0, parts)
+    p2, pv2 = airs.chain_trace(a2, 2 * n, seed=9)
+    inputs = [(0, parts, pv), (1, [recv], NONE), (2, p2, pv2)]
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    eng = make_engine(b, queries, pow_bits)
+    try:
+        eng.reset_metrics()
+        proof = gpu_prove(eng, key, inputs, air_objs)
+        m = eng.metrics()
+        assert gpu_verify(eng, key, proof) is None
+    finally:
+        eng.close()
+    assert orc.stark_verify(key, proof, b, queries, pow_bits) is None
+    assert proof == orc.stark_prove(key, inputs, b, queries, pow_bits)
+    return m
+
+
+@pytest.mark.parametrize("n,b", [(64, 1), (1 << 12, 2)])
+def test_split_generated_quotient_kernels_bytes(orc, monkeypatch, n, b):
+    m = _prove_lookup_parts(orc, monkeypatch, {"B2S_QUOTIENT_JIT_LINES": "150"}, n, b)
+    assert m["quotient_interpreter_launches"] == 0
+    assert m["quotient_jit_launches"] >= 12, m      # three AIRs, each split into several kernels
+    m1 = _prove_lookup_parts(orc, monkeypatch, {"B2S_QUOTIENT_JIT_LINES": "1000000"}, n, b)
+    assert m1["quotient_jit_launches"] == 3, m1      # one kernel per AIR when nothing forces a split
+
+
+@pytest.mark.parametrize("n,b", [(64, 1), (1 << 12, 2)])
+def test_interpreted_quotient_bytes(orc, monkeypatch, n, b):
+    m = _prove_lookup_parts(orc, monkeypatch, {"B2S_QUOTIENT_JIT": "0"}, n, b)
+    assert m["quotient_jit_launches"] == 0 and m["quotient_interpreter_launches"] == 3, m
 
 
 def test_verify_agrees_with_oracle_on_tampered_proofs(orc):

@@ -11,7 +11,7 @@ import struct
 import numpy as np
 import pytest
 
-import airs
+from openvm_b200 import airs
 from oracle_binding import unflatten_stream
 from test_oracle_stark import build_key, interaction_traces
 

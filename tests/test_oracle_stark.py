@@ -4,7 +4,7 @@ crates/circuits/poseidon2-air/src/tests.rs:56-74 (pranked trace -> OodEvaluation
 import numpy as np
 import pytest
 
-import airs
+from openvm_b200 import airs
 
 P = 2013265921
 

@@ -7,7 +7,7 @@ the shipped library are exercised on every round, not only on the GPU box."""
 import numpy as np
 import pytest
 
-import airs
+from openvm_b200 import airs
 from test_oracle_stark import build_key, interaction_traces
 
 P = 2013265921
@@ -101,6 +101,26 @@ def test_bad_arguments():
         verify_host(np.array([1, 2, 3], dtype=np.uint32), b"\x01\x00\x00\x00", FriParameters(log_blowup=1))
     with pytest.raises(B2StarkError):
         verify_host(airs.key_blob([airs.fibonacci_air()]), b"\x01\x00\x00\x00", FriParameters(log_blowup=1), 7)
+
+
+def test_key_with_malformed_dead_node_is_refused_at_load():
+    """A dead DAG node (not reachable from any constraint) with a bad column, operand or kind must fail key loading: the
+    verifier evaluates every node, so such a key would prove and then never verify. Same for a non-canonical preprocessed
+    commitment word."""
+    from openvm_b200 import B2StarkError, FriParameters, verify_host
+    fp = FriParameters(log_blowup=1)
+    for bad in [(airs.N_MAIN, 999, 0, 0), (airs.N_ADD, 0, 10 ** 6, 0), (99, 0, 0, 0), (airs.N_PUBLIC, 50, 0, 0),
+                (airs.N_CONST, P, 0, 0), (airs.N_PERM, 0, 0, 0)]:
+        air = airs.fibonacci_air()
+        air.dag.nodes.append(bad)
+        with pytest.raises(B2StarkError) as ei:
+            verify_host(airs.key_blob([air]), b"\x01\x00\x00\x00", fp)
+        assert ei.value.status == -1 and "malformed DAG node" in str(ei.value), bad
+    a = airs.chain_air(5, with_prep=True, height=16, seed=2)
+    a.prep_commit = np.full(8, P, dtype=np.uint32)
+    with pytest.raises(B2StarkError) as ei:
+        verify_host(airs.key_blob([a]), b"\x01\x00\x00\x00", fp)
+    assert "non-canonical preprocessed commitment" in str(ei.value)
 
 
 def test_decoder_and_key_parser_survive_structured_mutations(orc, kind):

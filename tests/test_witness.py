@@ -10,7 +10,7 @@ import struct
 import numpy as np
 import pytest
 
-import airs
+from openvm_b200 import airs
 from test_oracle_stark import build_key, interaction_traces
 
 P = 2013265921

@@ -27,7 +27,7 @@ for it in range(3):
     wall = (time.perf_counter() - t) * 1e3
     m = eng.metrics()
     print(f"proof {it}: wall {wall:.1f} ms, commit {m['commit_total_ms']:.1f} (lde {m['lde_ms']:.1f}, leaf {m['leaf_hash_ms']:.1f}), "
-          f"quotient+logup {m['quotient_ms']:.1f}, opening {m['opening_ms']:.1f}, {len(proof)} bytes", flush=True)
+          f"quotient+logup {(m['quotient_poly_compute_time_ms'] + m['generate_perm_trace_time_ms']):.1f}, opening {m['pcs_opening_time_ms']:.1f}, {len(proof)} bytes", flush=True)
 eng.verify(pk, proof)
 print("b2s_verify: accepted")
 eng.close()

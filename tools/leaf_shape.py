@@ -36,7 +36,7 @@ for it in range(proofs):
     wall = (time.perf_counter() - t) * 1e3
     m = eng.metrics()
     print(f"proof {it}: wall {wall:.1f} ms, commit {m['commit_total_ms']:.1f} (lde {m['lde_ms']:.1f}, leaf {m['leaf_hash_ms']:.1f}), "
-          f"quotient+logup {m['quotient_ms']:.1f}, opening {m['opening_ms']:.1f}, {len(proof)} bytes, "
+          f"quotient+logup {(m['quotient_poly_compute_time_ms'] + m['generate_perm_trace_time_ms']):.1f}, opening {m['pcs_opening_time_ms']:.1f}, {len(proof)} bytes, "
           f"device peak {eng.device_memory()[1] / 2**30:.1f} GiB", flush=True)
 t = time.perf_counter()
 eng.verify(pk, proof)

@@ -24,7 +24,7 @@ for kind, name in ((0, "inner (Poseidon2-BabyBear-16)"), (1, "root  (Poseidon2-B
         wall = (time.perf_counter() - t) * 1e3
         m = eng.metrics()
     print(f"{name}: 2^{log_h} x {width}: proof wall {wall:.1f} ms, commit {m['commit_total_ms']:.1f} (lde {m['lde_ms']:.1f}, leaf {m['leaf_hash_ms']:.1f}, "
-          f"compress {m['compress_ms']:.1f}), quotient+logup {m['quotient_ms']:.1f}, opening {m['opening_ms']:.1f}, "
+          f"compress {m['compress_ms']:.1f}), quotient+logup {(m['quotient_poly_compute_time_ms'] + m['generate_perm_trace_time_ms']):.1f}, opening {m['pcs_opening_time_ms']:.1f}, "
           f"{m['poseidon2_permutations']} permutations, {len(proof)} bytes", flush=True)
     eng.verify(pk, proof)
     if kind == 1:
