@@ -76,6 +76,9 @@ typedef struct {
     double quotient_poly_compute_time_ms;        /* constraint evaluation on the quotient domain               */
     double quotient_poly_commit_time_ms;         /* commitment of the quotient chunks                          */
     double pcs_opening_time_ms;                  /* values at zeta, reduced openings, FRI commit phase, PoW, queries */
+    double ood_eval_ms;                          /* part of pcs_opening: values at zeta (and zeta g), observed by the host */
+    double reduced_opening_ms;                   /* part of pcs_opening: reduced openings per LDE height                  */
+    double fri_commit_phase_ms;                  /* part of pcs_opening: FRI layers (pack, tree, root, fold)              */
     double stark_prove_excluding_trace_time_ms;  /* whole b2s_prove                                            */
     uint64_t lde_launches;
     uint64_t leaf_hash_launches;

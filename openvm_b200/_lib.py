@@ -19,7 +19,8 @@ class Metrics(C.Structure):
                 ("commit_total_ms", C.c_double), ("main_trace_commit_time_ms", C.c_double),
                 ("generate_perm_trace_time_ms", C.c_double), ("perm_trace_commit_time_ms", C.c_double),
                 ("quotient_poly_compute_time_ms", C.c_double), ("quotient_poly_commit_time_ms", C.c_double),
-                ("pcs_opening_time_ms", C.c_double), ("stark_prove_excluding_trace_time_ms", C.c_double),
+                ("pcs_opening_time_ms", C.c_double), ("ood_eval_ms", C.c_double), ("reduced_opening_ms", C.c_double),
+                ("fri_commit_phase_ms", C.c_double), ("stark_prove_excluding_trace_time_ms", C.c_double),
                 ("lde_launches", C.c_uint64), ("leaf_hash_launches", C.c_uint64),
                 ("compress_launches", C.c_uint64), ("other_launches", C.c_uint64),
                 ("poseidon2_permutations", C.c_uint64), ("quotient_jit_launches", C.c_uint64),

@@ -216,16 +216,28 @@ def chain_air(width, with_prep=False, cached_width=0, height=None, seed=0, degre
                cached_widths=[cached_width] if cached_width else [], prep=prep)
 
 
-def chain_trace(air, height, seed=0):
-    """Returns ([cached parts..., common], public values) satisfying chain_air."""
+_LCG_A, _LCG_C = 6364136223846793005, 1442695040888963407
+
+
+def _hash_pv0(seed):
+    return ((seed * _LCG_A + _LCG_C) % (1 << 64) >> 24) % P
+
+
+def chain_trace(air, height, seed=0, hashed=False):
+    """Returns ([cached parts..., common], public values) satisfying chain_air. `hashed`: the free values come from the
+    arithmetic formula chain_trace_device uses on the GPU instead of numpy's generator (same trace on both sides)."""
     W = air.width_common
     rng = np.random.default_rng(seed)
-    pv0 = int(rng.integers(0, P))
+    pv0 = _hash_pv0(seed) if hashed else int(rng.integers(0, P))
     p = np.uint64(P)
     t = np.zeros((height, W), dtype=np.uint64)
     t[:, 0] = (np.uint64(pv0) + np.arange(height, dtype=np.uint64)) % p
     if air.prep is not None:
         t[:, 1] = (air.prep[:, 0].astype(np.uint64) * air.prep[:, 1].astype(np.uint64) + np.uint64(pv0)) % p
+    elif hashed:
+        with np.errstate(over="ignore"):
+            x = (np.arange(height, dtype=np.uint64) + np.uint64(seed * 1000003 % (1 << 62))) * np.uint64(_LCG_A) + np.uint64(_LCG_C)
+        t[:, 1] = ((x >> np.uint64(20)) & np.uint64((1 << 40) - 1)) % p
     else:
         t[:, 1] = rng.integers(0, P, size=height, dtype=np.uint64)
     for j in range(W - 3):
@@ -237,6 +249,35 @@ def chain_trace(air, height, seed=0):
         parts.append(np.stack([(t[:, 0] + np.uint64(k)) % p for k in range(cw)], axis=1).astype(np.uint32))
     parts.append(common)
     return parts, np.array([pv0, int(common[height - 1, 1])], dtype=np.uint32)
+
+
+def chain_trace_device(air, height, seed, device):
+    """chain_trace(air, height, seed, hashed=True) computed ON THE GPU with torch ops on torch's current stream: returns
+    (columns, public values) where `columns` is a (width, height) int32 CUDA tensor = the column-major, Montgomery-form
+    matrix a device tracegen would leave in HBM (the reference's DeviceMatrix, crates/vm/src/system/cuda/program.rs:60,
+    119-125), ready for b2s_matrix_adopt_device without any copy. Only for AIRs with a single common-main partition."""
+    import torch
+    assert air.prep is None and not air.cached_widths
+    W = air.width_common
+    pv0 = _hash_pv0(seed)
+    r = torch.arange(height, dtype=torch.int64, device=device)
+    t = torch.empty((W, height), dtype=torch.int64, device=device)
+    t[0] = (r + pv0) % P
+    x = (r + (seed * 1000003 % (1 << 62))) * _signed64(_LCG_A) + _signed64(_LCG_C)     # wraps mod 2^64 like the host formula
+    t[1] = ((x >> 20) & ((1 << 40) - 1)) % P
+    for j in range(W - 3):
+        t[j + 2] = (t[j] * t[j + 1] + t[j]) % P
+    t[W - 1] = ((t[0] * t[1]) % P * t[2]) % P
+    # the second public value is the last row's x_1: recomputed here on the host, so that nothing waits on the device
+    xl = ((height - 1 + seed * 1000003 % (1 << 62)) * _LCG_A + _LCG_C) % (1 << 64)
+    pv1 = ((xl >> 20) & ((1 << 40) - 1)) % P
+    monty = ((t << 32) % P).to(torch.int32).contiguous()
+    return monty, np.array([pv0, pv1], dtype=np.uint32)
+
+
+def _signed64(x):
+    x %= 1 << 64
+    return x - (1 << 64) if x >= 1 << 63 else x
 
 
 def dummy_interaction_air(n_fields, is_send, bus=0, log_qd=1):
@@ -279,12 +320,26 @@ def build_key(air_list, commit_fn, **kw):
     return key_blob(air_list, **kw)
 
 
-def segment_shapes(scale_log=0):
-    """Shape replay of an RV32IM app segment: (log_height, main width) per AIR, after the per-AIR table of the
-    reference's example metrics (crates/prof/data/metrics.example.json, group ecrecover_program):
-    a few tall narrow range/lookup AIRs, ALU/branch/load-store chips of 20-40 columns, one wide hash chip."""
-    base = [(19, 5), (17, 36), (17, 40), (16, 28), (16, 20), (15, 32), (14, 66), (13, 200), (12, 16), (10, 8)]
-    return [(max(4, h + scale_log), w) for h, w in base]
+# (rows, main columns, after-challenge EF columns = perm_cols / 4) of every AIR present in segment 0 of the reference's example
+# run, group ecrecover_program of crates/prof/data/metrics.example.json (the table SURVEY.md 8d names), in AIR order
+_ECRECOVER_SEGMENT = [
+    (16384, 10, 2), (2, 4, 3), (4096, 20, 3), (4096, 32, 5), (256, 11, 6), (128, 13, 6), (32768, 17, 6), (16384, 25, 6),
+    (8192, 41, 6), (2048, 543, 207), (1024, 619, 212), (128, 3164, 322), (4096, 166, 14), (16, 261, 79), (8, 199, 48),
+    (256, 26, 9), (8, 57, 26), (8, 39, 25), (4096, 31, 20), (524288, 1, 2), (4096, 21, 7), (8192, 28, 9), (4096, 18, 11),
+    (32768, 32, 14), (16384, 26, 12), (4096, 35, 19), (131072, 40, 18), (16384, 53, 13), (2048, 37, 10), (131072, 36, 20),
+    (65536, 2, 2), (64, 6, 3), (4096, 300, 2), (262144, 1, 2)]
+
+
+def segment_shapes(scale_log=0, legacy=False):
+    """Shape replay of an RV32IM app segment: (log_height, main width, after-challenge EF columns) per AIR = the per-AIR table
+    of the reference's example metrics (34 AIRs with rows in segment 0: BaseAlu 131072 x 36 (+80 perm words), LoadStore
+    131072 x 40 (+72), RangeTuple 524288 x 1 (+8), KeccakVm 128 x 3164 (+1288) ...). scale_log = 3 makes the ALU / load-store
+    chips 2^20 rows. Main widths below the chain AIR's minimum of 5 are raised to 5.
+    legacy: the ten-AIR list of round 1 (kept for comparisons with profiles/r1*)."""
+    if legacy:
+        base = [(19, 5), (17, 36), (17, 40), (16, 28), (16, 20), (15, 32), (14, 66), (13, 200), (12, 16), (10, 8)]
+        return [(max(4, h + scale_log), w, None) for h, w in base]
+    return [(max(1, rows.bit_length() - 1 + scale_log), max(5, w), perm) for rows, w, perm in _ECRECOVER_SEGMENT]
 
 
 def leaf_shapes(scale_log=0):
@@ -335,14 +390,18 @@ def lookup_chain_parts_receiver_trace(air, parts):
     return t[::-1].copy()
 
 
-def segment_air(width, degree=3):
+def segment_air(width, degree=3, perm_cols=None):
     """One chip of the shape-replay segment: chain_air plus LogUp traffic shaped like an OpenVM chip's (BaseAlu:
     36 main columns and 20 extension-field permutation columns in crates/prof/data/metrics.example.json). Chunk c holds
     two interactions on bus c: send (x_j, x_{j+1}) of this row and receive the same pair of the NEXT row, so the bus
-    balances over the cyclic trace while every row's reciprocal sum is non-trivial. Degree 3 -> quotient degree 2."""
+    balances over the cyclic trace while every row's reciprocal sum is non-trivial. Degree 3 -> quotient degree 2.
+    perm_cols: after-challenge EF columns wanted (chunks + the running sum); default: the round-1 heuristic."""
     a = chain_air(width, degree=degree)
     d = a.dag
-    k = max(1, width // 2) if width <= 100 else width // 10
+    if perm_cols is not None:
+        k = max(1, perm_cols - 1)
+    else:
+        k = max(1, width // 2) if width <= 100 else width // 10
     for c in range(k):
         j = c % (width - 1)
         a.add_interaction(c, [d.main(j), d.main(j + 1)], d.const(1), True)

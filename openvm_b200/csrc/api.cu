@@ -364,6 +364,9 @@ int32_t b2s_get_metrics(b2s_engine* e, b2s_metrics* out) {
         out->quotient_poly_compute_time_ms = e->timers[ST_QUOTIENT].ms;
         out->quotient_poly_commit_time_ms = e->timers[ST_QUOTIENT_COMMIT].ms;
         out->pcs_opening_time_ms = e->timers[ST_OPENING].ms;
+        out->ood_eval_ms = e->timers[ST_OOD].ms;
+        out->reduced_opening_ms = e->timers[ST_REDUCED].ms;
+        out->fri_commit_phase_ms = e->timers[ST_FRI_COMMIT].ms;
         out->stark_prove_excluding_trace_time_ms = e->timers[ST_PROVE].ms;
         out->quotient_jit_launches = e->quotient_launches[0];
         out->quotient_interpreter_launches = e->quotient_launches[1];

@@ -43,7 +43,7 @@ struct TwiddleSet;
 struct ScaleSet;
 
 enum Stage { ST_LDE = 0, ST_LEAF, ST_COMPRESS, ST_COMMIT, ST_MAIN_COMMIT, ST_PERM_GEN, ST_PERM_COMMIT, ST_QUOTIENT,
-             ST_QUOTIENT_COMMIT, ST_OPENING, ST_PROVE, ST_COUNT };
+             ST_QUOTIENT_COMMIT, ST_OPENING, ST_OOD, ST_REDUCED, ST_FRI_COMMIT, ST_PROVE, ST_COUNT };
 
 struct StageTimer {
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending;

@@ -1268,6 +1268,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     }
     // (i) out-of-domain values. Weights are shared by all matrices of one trace height: index 0 = zeta, 1 = zeta * w_n.
     {
+        StageScope ood_scope(e, ST_OOD);
         std::map<unsigned, std::array<uint32_t*, 2>> weights;
         auto get_weights = [&](unsigned n, int which, const Fp4& z) {
             auto& slot = weights[n];
@@ -1337,6 +1338,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
     const unsigned L = log_max_height + b;
     std::map<unsigned, uint32_t*> ro;
     {
+        StageScope ro_scope(e, ST_REDUCED);
         uint64_t max_w = 1;
         for (auto& r : rounds) for (auto& m : r.mats) max_w = std::max<uint64_t>(max_w, m.lde->width);
         // alpha^t for t up to the widest matrix; the host copy lives in the scratch until the proof is done
@@ -1401,6 +1403,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
         std::vector<b2s_matrix*>& v;
         ~LeafGuard() { for (auto* m : v) b2s_matrix_free(m); }
     } leaf_guard{fri_leaves};
+    e->stage_begin(ST_FRI_COMMIT);
     for (unsigned lh = L; lh > b; lh--) {
         const uint32_t R = 1u << (lh - 1);
         b2s_matrix* leaf = new_matrix(e, R, 8);
@@ -1433,6 +1436,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
         folded = next;
         trace.mark("  fri layer: fold", 2);
     }
+    e->stage_end(ST_FRI_COMMIT);
     trace.mark("fri commit phase");
     // final polynomial: log_final_poly_len = 0, the constant (two_adic_pcs.rs:52-58)
     Fp4 final_poly;

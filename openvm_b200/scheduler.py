@@ -174,3 +174,80 @@ def submit_aggregation_tree(pool, n_segments, prove_segment, prove_leaf, prove_i
         layer = nxt
         layers.append(layer)
     return layer[0], layers
+
+
+def aggregation_dag(n_segments, num_children_internal=3):
+    """The continuation DAG as (kinds, deps): job ids in FIFO order -- segments 0..S-1, leaf S+i after segment i (1:1,
+    crates/sdk/src/config/mod.rs:26), then internal layers of arity 3 (:27; crates/sdk/src/prover/agg.rs:124-202) until one
+    proof is left. kinds[j] = ("segment" | "leaf" | "internal", index within its layer, layer number)."""
+    kinds = [("segment", i, 0) for i in range(n_segments)]
+    deps = [[] for _ in range(n_segments)]
+    layer = []
+    for i in range(n_segments):
+        layer.append(len(kinds))
+        kinds.append(("leaf", i, 1))
+        deps.append([i])
+    depth = 2
+    while len(layer) > 1:
+        nxt = []
+        for i in range(0, len(layer), num_children_internal):
+            nxt.append(len(kinds))
+            kinds.append(("internal", i // num_children_internal, depth))
+            deps.append(layer[i:i + num_children_internal])
+        layer = nxt
+        depth += 1
+    return kinds, deps
+
+
+def critical_path(deps, cost):
+    """Length of the longest dependency chain when job j costs cost[j] (the lower bound of the DAG's wall time)."""
+    done = [0.0] * len(deps)
+    for j, d in enumerate(deps):
+        done[j] = cost[j] + max((done[k] for k in d), default=0.0)
+    return max(done, default=0.0)
+
+
+class DagFifo:
+    """ONE FIFO of DAG jobs shared by every engine of every rank ("job -> first free engine"), over a
+    torch.distributed key-value store (the TCPStore the process group already has; a HashStore in one process). No
+    data-path collective: a worker claims the next job id with an atomic counter, waits until the results of its
+    dependencies are in the store, runs it, and publishes its result (proof bytes: what the parent's verifier program is fed,
+    crates/sdk/src/prover/agg.rs:307-321). Job ids are topologically ordered (aggregation_dag), so the unfinished job with
+    the smallest id never waits on an unclaimed one: no deadlock, and an engine only idles on a dependency at the tail of
+    the DAG, where the critical path is the limit anyway.
+
+        fifo = DagFifo(store, deps, tag="run0")
+        log = fifo.work(lambda jid, child_results: prove(jid, child_results))   # on every engine thread of every rank
+    """
+
+    def __init__(self, store, deps, tag="dag", poll_s=0.0005):
+        self.store, self.deps, self.tag, self.poll_s = store, deps, tag, poll_s
+
+    def _key(self, what, j=None):
+        return f"{self.tag}/{what}" if j is None else f"{self.tag}/{what}/{j}"
+
+    def work(self, fn, clock=None):
+        """Claims and runs jobs until the FIFO is empty. fn(jid, [results of deps]) -> bytes. Returns this worker's log:
+        [(jid, t_claimed, t_ready, t_done)] on `clock` (default time.perf_counter)."""
+        import time
+        clock = clock or time.perf_counter
+        log = []
+        n = len(self.deps)
+        while True:
+            jid = self.store.add(self._key("next"), 1) - 1
+            if jid >= n:
+                return log
+            t0 = clock()
+            keys = [self._key("done", d) for d in self.deps[jid]]
+            # poll instead of store.wait(): a blocking wait holds the store client of this PROCESS, and the engine thread
+            # that will publish the dependency may live in the same process
+            while keys and not self.store.check(keys):
+                time.sleep(self.poll_s)
+            args = [bytes(self.store.get(k)) for k in keys]
+            t1 = clock()
+            out = fn(jid, args)
+            self.store.set(self._key("done", jid), out if isinstance(out, (bytes, bytearray)) else bytes(out))
+            log.append((jid, t0, t1, clock()))
+
+    def result(self, jid):
+        return bytes(self.store.get(self._key("done", jid)))

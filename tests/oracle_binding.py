@@ -221,6 +221,25 @@ class Oracle:
         self.lib.orc_challenger_run(obs.ctypes.data, obs.size, out.ctypes.data, n_samples)
         return out
 
+    def fast_commit(self, log_h, width, log_blowup, matrix=None, seed=0, threads=8):
+        """orc_fast_commit (oracle/fast_commit.cpp): AVX2 / Montgomery / multi-threaded commit of one matrix -- either
+        `matrix` ((height, width) canonical) or the synthetic trace of `seed` generated column by column.
+        Returns (root, {"gen_s", "lde_s", "hash_s"})."""
+        self.lib.orc_fast_commit.restype = C.c_int
+        self.lib.orc_fast_commit.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32, C.c_int, C.c_void_p,
+                                             C.c_void_p]
+        cm = None
+        if matrix is not None:
+            cm = np.ascontiguousarray(np.asarray(matrix, dtype=np.uint32).T)
+            assert cm.shape == (width, 1 << log_h)
+        root = np.zeros(8, dtype=np.uint32)
+        times = np.zeros(3, dtype=np.float64)
+        rc = self.lib.orc_fast_commit(cm.ctypes.data if cm is not None else None, seed, log_h, width, log_blowup, threads,
+                                      root.ctypes.data, times.ctypes.data)
+        if rc != 0:
+            raise ValueError("orc_fast_commit: bad arguments")
+        return root, {"gen_s": float(times[0]), "lde_s": float(times[1]), "hash_s": float(times[2])}
+
     def fill_synthetic(self, height, width, seed):
         out = np.zeros((width, height), dtype=np.uint32)
         self.lib.orc_fill_synthetic(out.ctypes.data, height, width, seed)

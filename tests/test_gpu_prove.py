@@ -420,3 +420,61 @@ def test_prover_pool_concurrent_engines_give_the_oracle_bytes(orc):
         pool.close()
         for w in workers:
             w.eng.close()
+
+
+# ---- zero-copy hand-off from a device tracegen ------------------------------------------------------------
+def test_prove_from_adopted_device_traces_on_the_callers_stream(orc):
+    """The reference's GPU flow: the trace is written by the caller's kernels into the caller's device memory and handed over
+    as DeviceMatrix{buffer, height, width} (crates/vm/src/system/cuda/program.rs:60,119-125; crates/vm/src/arch/vm.rs:588-599).
+    Here torch ops on a torch stream play the tracegen; the engine shares that stream (b2s_engine_set_stream), adopts the
+    buffers (b2s_matrix_adopt_device) and proves -- no copy and no host synchronisation between generation and proof. The
+    proof equals the oracle's proof of the same trace byte for byte."""
+    import torch
+    from openvm_b200 import AirProvingContext
+    b, queries, pow_bits = 1, 4, 3
+    air_objs = [airs.segment_air(8, perm_cols=3), airs.segment_air(12, perm_cols=4)]
+    heights = [1 << 9, 1 << 6]
+    key = airs.key_blob(air_objs, log_up_pow_bits=3)
+    eng = make_engine(b, queries, pow_bits)
+    try:
+        dev = eng.device()
+        pk = dev.transport_pk_to_device(key)
+        s = torch.cuda.Stream()
+        eng.set_stream(s.cuda_stream)
+        assert eng.stream == s.cuda_stream
+        with torch.cuda.stream(s):
+            gen = [airs.chain_trace_device(a, h, seed=31 + i, device="cuda") for i, (a, h) in enumerate(zip(air_objs, heights))]
+            ctx = []
+            for i, ((cols, pv), a, h) in enumerate(zip(gen, air_objs, heights)):
+                m = dev.adopt_device_matrix(cols.data_ptr(), h, a.width_common)
+                assert m.device_ptr == cols.data_ptr()
+                ctx.append(AirProvingContext(i, m, pv))
+            proof = eng.prove(pk, ctx)                       # enqueued behind the generation on the same stream
+        inputs = []
+        for i, (a, h) in enumerate(zip(air_objs, heights)):
+            parts, pv = airs.chain_trace(a, h, seed=31 + i, hashed=True)
+            assert np.array_equal(pv, gen[i][1])
+            assert np.array_equal(ctx[i].common_main.to_host(), parts[-1])   # what the device generator wrote
+            inputs.append((i, parts, pv))
+        assert proof == orc.stark_prove(key, inputs, b, queries, pow_bits)
+        assert orc.stark_verify(key, proof, b, queries, pow_bits) is None
+        pk.free()
+    finally:
+        eng.close()
+
+
+@pytest.mark.parametrize("heights", [(2, 4), (8, 2), (16, 1 << 10)])
+def test_tiny_trace_heights_bytes(orc, heights):
+    """heights of 2, 4, 8 rows next to taller AIRs (the reference's example segment has AIRs of 2, 8 and 16 rows)"""
+    b, queries, pow_bits = 1, 4, 2
+    air_objs = [airs.segment_air(5, perm_cols=3), airs.segment_air(9, perm_cols=2)]
+    key = airs.key_blob(air_objs, log_up_pow_bits=2)
+    inputs = []
+    for i, (a, h) in enumerate(zip(air_objs, heights)):
+        parts, pv = airs.chain_trace(a, h, seed=3 + i)
+        inputs.append((i, parts, pv))
+    eng = make_engine(b, queries, pow_bits)
+    try:
+        check_same(orc, eng, key, inputs, air_objs, b, queries, pow_bits)
+    finally:
+        eng.close()

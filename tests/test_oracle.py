@@ -1,5 +1,6 @@
 """The C++ oracle against an independent pure-Python restatement and against definitional checks."""
 import numpy as np
+import pytest
 
 import pyref
 
@@ -121,3 +122,25 @@ def test_synthetic_fill_is_deterministic(orc):
     assert a.shape == (16, 3) and (a < P).all()
     assert np.array_equal(a, orc.fill_synthetic(16, 3, 0xB200000000000001))
     assert not np.array_equal(a, orc.fill_synthetic(16, 3, 2))
+
+
+@pytest.mark.parametrize("log_h,w,b", [(0, 3, 1), (1, 8, 1), (2, 9, 1), (3, 1, 2), (5, 17, 1), (10, 19, 1), (12, 40, 2),
+                                       (14, 64, 1), (16, 24, 1), (13, 100, 2)])
+def test_fast_commit_equals_plain_oracle(orc, log_h, w, b):
+    """oracle/fast_commit.cpp (AVX2, Montgomery, multi-threaded; bench.py's CPU baseline and the checker of the full-size root)
+    against the plain oracle's commit (canonical % arithmetic, pinned by the golden vectors): same root for tiny, ragged and
+    multi-batch shapes, for any thread count."""
+    rng = np.random.default_rng(log_h * 131 + w)
+    m = rng.integers(0, 2013265921, size=(1 << log_h, w), dtype=np.uint64).astype(np.uint32)
+    want = orc.commit([m], b)
+    for threads in (1, 3, 8):
+        got, times = orc.fast_commit(log_h, w, b, matrix=m, threads=threads)
+        assert np.array_equal(got, want), (threads, got, want)
+        assert times["lde_s"] >= 0 and times["hash_s"] >= 0
+
+
+def test_fast_commit_generates_the_synthetic_trace(orc):
+    m = orc.fill_synthetic(1 << 11, 16, 0xB200000000000001)
+    assert np.array_equal(orc.commit([m], 1), orc.fast_commit(11, 16, 1, seed=0xB200000000000001, threads=4)[0])
+    with pytest.raises(ValueError):
+        orc.fast_commit(27, 1, 1, seed=1)

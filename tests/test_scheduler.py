@@ -112,3 +112,59 @@ def test_prover_pool_failures_propagate_and_do_not_wedge():
             bad.result(j, timeout=10)
     finally:
         bad.close()
+
+
+def _dag_worker(rank, world, port, q):
+    import threading
+    import time
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    store = dist.distributed_c10d._get_default_store()
+    kinds, deps = scheduler.aggregation_dag(7)
+    fifo = scheduler.DagFifo(store, deps, tag="t")
+    logs = []
+
+    def fn(jid, args):
+        # a job sees exactly the results of its dependencies
+        assert [int(a.decode().split(":")[0]) for a in args] == deps[jid]
+        time.sleep(0.003 * (1 + jid % 3))
+        return f"{jid}:{rank}".encode()
+
+    def run():
+        logs.extend(fifo.work(fn, clock=time.time))
+
+    ths = [threading.Thread(target=run) for _ in range(2)]
+    for t in ths: t.start()
+    for t in ths: t.join()
+    dist.barrier()
+    root = fifo.result(len(deps) - 1).decode()
+    q.put((rank, logs, root))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_dag_fifo_shared_by_two_ranks_over_gloo():
+    """world_size 2, two engine threads per rank: every job of the 7-segment aggregation DAG runs exactly once somewhere, never
+    before its dependencies finished, and both ranks take part (one FIFO, job -> first free engine)."""
+    kinds, deps = scheduler.aggregation_dag(7)
+    assert [k for k, _, _ in kinds] == ["segment"] * 7 + ["leaf"] * 7 + ["internal"] * 3 + ["internal"]
+    assert deps[14] == [7, 8, 9] and deps[16] == [13] and deps[17] == [14, 15, 16]
+    assert scheduler.critical_path(deps, [1.0] * len(deps)) == 4.0
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_dag_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs: p.start()
+    res = [q.get(timeout=120) for _ in range(2)]
+    for p in procs: p.join(timeout=60)
+    done_at, ran_on = {}, {}
+    for rank, logs, root in res:
+        assert root.split(":")[0] == str(len(deps) - 1)
+        for jid, t0, t1, t2 in logs:
+            assert jid not in done_at, "job ran twice"
+            done_at[jid], ran_on[jid] = (t1, t2), rank
+    assert sorted(done_at) == list(range(len(deps)))
+    for j, d in enumerate(deps):
+        for k in d:
+            assert done_at[k][1] <= done_at[j][0] + 1e-3, (j, k)
+    assert set(ran_on.values()) == {0, 1}

@@ -6,9 +6,9 @@ from openvm_b200 import B2Engine, FriParameters, AirProvingContext, airs as A
 K = int(sys.argv[1]) if len(sys.argv) > 1 else 2
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 20
 shapes = A.segment_shapes(0)
-air_objs = [A.segment_air(w) for _, w in shapes]
+air_objs = [A.segment_air(w, perm_cols=pc) for _, w, pc in shapes]
 key = A.build_key(air_objs, None, log_up_pow_bits=16)
-traces = [A.chain_trace(air_objs[i], 1 << lh, seed=i) for i, (lh, w) in enumerate(shapes)]
+traces = [A.chain_trace(air_objs[i], 1 << lh, seed=i) for i, (lh, w, _pc) in enumerate(shapes)]
 engines = []
 for k in range(K):
     eng = B2Engine.new(FriParameters.standard_with_100_bits_conjectured_security(1))

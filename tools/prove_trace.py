@@ -7,10 +7,10 @@ from openvm_b200 import B2Engine, FriParameters, AirProvingContext, airs as A
 eng = B2Engine.new(FriParameters.standard_with_100_bits_conjectured_security(1))
 dev = eng.device()
 shapes = A.segment_shapes(int(sys.argv[1]) if len(sys.argv) > 1 else 0)
-air_objs = [A.segment_air(w) for _, w in shapes]
+air_objs = [A.segment_air(w, perm_cols=pc) for _, w, pc in shapes]
 pk = dev.transport_pk_to_device(A.build_key(air_objs, None, log_up_pow_bits=16))
 ctx = []
-for i, (lh, w) in enumerate(shapes):
+for i, (lh, w, _pc) in enumerate(shapes):
     parts, pv = A.chain_trace(air_objs[i], 1 << lh, seed=i)
     ctx.append(AirProvingContext(i, dev.transport_matrix_to_device(parts[-1]), pv))
 for it in range(3):
