@@ -365,9 +365,10 @@ def dag_weights(air):
 
 
 class ShapeProver:
-    """One engine proving one multi-AIR shape: key built from authored chain AIRs, traces generated ON THE DEVICE by torch ops
-    on the engine's stream and adopted without a copy (b2s_matrix_adopt_device + b2s_engine_set_stream: the reference's
-    tracegen -> prover hand-off, crates/vm/src/system/cuda/program.rs:60,119-125)."""
+    """One engine proving one multi-AIR shape: key built from authored chain AIRs, traces generated ON THE DEVICE by a kernel on
+    the engine's stream, which is a caller-owned (torch) stream shared through b2s_engine_set_stream -- the reference's device
+    tracegen -> prover hand-off (crates/vm/src/system/cuda/program.rs:60,119-125); the adoption of caller-owned buffers
+    (b2s_matrix_adopt_device) is exercised by tests/test_gpu_prove.py."""
 
     def __init__(self, cx, shapes, b, log_up_pow_bits=16, key=None, air_objs=None):
         from openvm_b200 import airs as A
@@ -384,19 +385,18 @@ class ShapeProver:
         self.key_load_s = time.perf_counter() - t0
         self.cells = sum(w << lh for lh, w, _, _ in shapes)
         self.perm_cells = sum((4 * (len(a.chunks) + 1)) << lh for a, (lh, _, _, _) in zip(self.air_objs, shapes))
-        self.ctx, self.keep = None, None
+        self.ctx, self.mats = None, None
 
     def generate(self, seed):
-        """Traces of one proof, written by torch kernels on the engine's stream; no host synchronisation."""
-        from openvm_b200 import AirProvingContext, airs as A
-        torch = self.cx.torch
-        ctx, keep = [], []
-        with torch.cuda.stream(self.tstream):
-            for i, (a, (lh, w, _, _)) in enumerate(zip(self.air_objs, self.shapes)):
-                cols, pv = A.chain_trace_device(a, 1 << lh, seed * 1000 + i, f"cuda:{self.cx.local_rank}")
-                keep.append(cols)
-                ctx.append(AirProvingContext(i, self.dev.adopt_device_matrix(cols.data_ptr(), 1 << lh, w), pv))
-        self.ctx, self.keep = ctx, keep
+        """Traces of one proof, written by a device kernel on the engine's stream (b2s_matrix_fill_chain, the stand-in for a
+        device tracegen): one launch per AIR, no host copy, no synchronisation."""
+        from openvm_b200 import AirProvingContext
+        if self.mats is None:
+            self.mats = [self.dev.alloc_matrix(1 << lh, w) for lh, w, _, _ in self.shapes]
+        ctx = []
+        for i, m in enumerate(self.mats):
+            ctx.append(AirProvingContext(i, m, self.dev.fill_chain(m, seed * 1000 + i)))
+        self.ctx = ctx
         return ctx
 
     def prove(self, seed=None):
@@ -416,7 +416,7 @@ class ShapeProver:
         return tot
 
     def close(self):
-        self.ctx = self.keep = None
+        self.ctx = self.mats = None
         self.pk.free()
         self.eng.close()
 
@@ -450,7 +450,7 @@ def leg_shape(cx, name, shapes, b, steps, what, orc=None, modmul_peak=None, hbm_
     stage = {k: m[k] / steps for k in GAUGES}
     stage["sum_of_six"] = sum(stage[k] for k in GAUGES[:-1])
     out = {"workload": f"{what}: {len(shapes)} AIRs, {sp.cells} main cells + {sp.perm_cells} after-challenge cells, FRI log_blowup "
-                       f"{b}, {q} queries, 16 + 16 PoW bits; traces generated on the device and adopted without a copy",
+                       f"{b}, {q} queries, 16 + 16 PoW bits; traces generated on the device, no host copy",
            "accepted_by": accepted, "device_ms_per_proof": pms, "wall_ms_per_proof": wall, "proofs_per_s": cx.world * 1e3 / wall,
            "proof_bytes": len(proof), "stage_ms": stage, "opening_parts_ms": {k: m[k] / steps for k in OPENING_PARTS},
            "key_load_s": sp.key_load_s, "device_peak_gib": sp.eng.device_memory()[1] / 2 ** 30,

@@ -130,6 +130,11 @@ int32_t b2s_matrix_alloc(b2s_engine* e, uint64_t height, uint64_t width, b2s_mat
 /* deterministic synthetic contents generated on the device: element(r,c) =
  * splitmix64(seed ^ ((c << 32) | r)) mod p; same generator in oracle/. */
 int32_t b2s_matrix_fill_synthetic(b2s_engine* e, b2s_matrix* m, uint64_t seed);
+/* deterministic SATISFYING trace of the tests' chain AIR (openvm_b200/airs.py chain_air; width >= 5), generated on the
+ * device on the engine's stream: stands in for the reference's device tracegen (crates/vm/src/system/cuda/, out of scope)
+ * in bench.py and the tests. pv_out receives the AIR's two public values (canonical). Same values as
+ * airs.chain_trace(air, height, seed, hashed=True) on the host. */
+int32_t b2s_matrix_fill_chain(b2s_engine* e, b2s_matrix* m, uint64_t seed, uint32_t pv_out[2]);
 uint64_t b2s_matrix_height(const b2s_matrix* m);
 uint64_t b2s_matrix_width(const b2s_matrix* m);
 void* b2s_matrix_device_ptr(const b2s_matrix* m);

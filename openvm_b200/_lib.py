@@ -53,6 +53,7 @@ SIGNATURES = {
     "b2s_matrix_adopt_device": (C.c_int32, [vp, vp, C.c_uint64, C.c_uint64, C.POINTER(vp)]),
     "b2s_matrix_alloc": (C.c_int32, [vp, C.c_uint64, C.c_uint64, C.POINTER(vp)]),
     "b2s_matrix_fill_synthetic": (C.c_int32, [vp, vp, C.c_uint64]),
+    "b2s_matrix_fill_chain": (C.c_int32, [vp, vp, C.c_uint64, u32p]),
     "b2s_matrix_height": (C.c_uint64, [vp]),
     "b2s_matrix_width": (C.c_uint64, [vp]),
     "b2s_matrix_device_ptr": (vp, [vp]),

@@ -225,6 +225,7 @@ b2s_pcs_data* commit_matrices(b2s_engine* e, const b2s_matrix* const* mats, cons
     d->eng = e;
     try {
         const uint32_t lb = e->params.log_blowup;
+
         for (size_t i = 0; i < n; i++) {
             const b2s_matrix* in = mats[i];
             B2_REQUIRE(in != nullptr, B2S_ERR_BAD_ARG, "null matrix");
@@ -449,6 +450,11 @@ int32_t b2s_matrix_alloc(b2s_engine* e, uint64_t height, uint64_t width, b2s_mat
 int32_t b2s_matrix_fill_synthetic(b2s_engine* e, b2s_matrix* m, uint64_t seed) {
     if (!e || !m) return B2S_ERR_BAD_ARG;
     return guarded(e, [&] { fill_synthetic(e, m->d, m->height, m->width, seed); });
+}
+
+int32_t b2s_matrix_fill_chain(b2s_engine* e, b2s_matrix* m, uint64_t seed, uint32_t pv_out[2]) {
+    if (!e || !m || !pv_out) return B2S_ERR_BAD_ARG;
+    return guarded(e, [&] { fill_chain(e, m->d, m->height, m->width, seed, pv_out); });
 }
 
 uint64_t b2s_matrix_height(const b2s_matrix* m) { return m ? m->height : 0; }

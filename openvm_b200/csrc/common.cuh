@@ -213,6 +213,7 @@ void transpose_to_colmajor(b2s_engine* e, const uint32_t* d_rowmajor, uint32_t* 
 void transpose_to_rowmajor(b2s_engine* e, const uint32_t* d_colmajor, uint32_t* d_rowmajor, uint64_t height,
                            uint64_t width, bool to_canonical);
 void fill_synthetic(b2s_engine* e, uint32_t* d, uint64_t height, uint64_t width, uint64_t seed);
+void fill_chain(b2s_engine* e, uint32_t* d, uint64_t height, uint64_t width, uint64_t seed, uint32_t pv[2]);
 void gather_open(b2s_engine* e, const b2s_pcs_data* d, uint64_t index, uint32_t* h_rows, uint32_t* h_proof);
 void download_layer(b2s_engine* e, const b2s_pcs_data* d, uint32_t level, uint32_t* h_out);
 double bench_modmul(b2s_engine* e, uint64_t threads, uint32_t iters, int ilp);

@@ -126,6 +126,41 @@ void fill_synthetic(b2s_engine* e, uint32_t* d, uint64_t height, uint64_t width,
     e->launches[3]++;
 }
 
+// Satisfying trace of the authored chain AIR (openvm_b200/airs.py chain_air / chain_trace(hashed=True)), one thread per row:
+// x_0 = pv0 + r, x_1 = hash(r, seed), x_{j+2} = x_j x_{j+1} + x_j for j + 2 <= W - 2, x_{W-1} = x_0 x_1 x_2. Stands in for a
+// device tracegen in bench.py and the tests (the reference's tracegen is out of scope): a segment's 34 traces in 34 launches.
+constexpr uint64_t CHAIN_LCG_A = 6364136223846793005ull, CHAIN_LCG_C = 1442695040888963407ull;
+__host__ __device__ inline uint32_t chain_x1(uint64_t r, uint64_t seed) {
+    const uint64_t x = (r + (seed * 1000003ull) % ((uint64_t)1 << 62)) * CHAIN_LCG_A + CHAIN_LCG_C;
+    return (uint32_t)(((x >> 20) & (((uint64_t)1 << 40) - 1)) % P);
+}
+__global__ void chain_fill_kernel(uint32_t* d, uint64_t height, uint32_t width, uint32_t pv0, uint64_t seed) {
+    const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= height) return;
+    Fp a = Fp::from_canonical((uint32_t)((pv0 + r) % P)), b = Fp::from_canonical(chain_x1(r, seed));
+    const Fp x0 = a, x1 = b;
+    Fp x2 = Fp::zero();
+    d[r] = a.v;
+    d[height + r] = b.v;
+    for (uint32_t j = 2; j + 1 < width; j++) {
+        const Fp c = a * b + a;
+        if (j == 2) x2 = c;
+        d[(uint64_t)j * height + r] = c.v;
+        a = b;
+        b = c;
+    }
+    d[(uint64_t)(width - 1) * height + r] = (x0 * x1 * x2).v;
+}
+void fill_chain(b2s_engine* e, uint32_t* d, uint64_t height, uint64_t width, uint64_t seed, uint32_t pv[2]) {
+    B2_REQUIRE(width >= 5 && width < ((uint64_t)1 << 31) && height >= 1, B2S_ERR_SHAPE, "fill_chain: width >= 5 and height >= 1");
+    const uint32_t pv0 = (uint32_t)(((seed * CHAIN_LCG_A + CHAIN_LCG_C) >> 24) % P);
+    chain_fill_kernel<<<(unsigned)((height + 127) / 128), 128, 0, e->stream>>>(d, height, (uint32_t)width, pv0, seed);
+    B2_CHECK_LAUNCH();
+    e->launches[3]++;
+    pv[0] = pv0;
+    pv[1] = chain_x1(height - 1, seed);
+}
+
 // ---- Merkle opening gather ---------------------------------------------------------------------------
 __global__ void gather_kernel(const OpenDesc* descs, uint32_t ndesc, uint32_t* out) {
     uint32_t di = blockIdx.x;

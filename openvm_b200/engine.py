@@ -240,6 +240,13 @@ class B2Device:
         e = self._e
         e._check(e._lib.b2s_matrix_fill_synthetic(e._h, matrix._h, seed))
 
+    def fill_chain(self, matrix, seed):
+        """Satisfying trace of airs.chain_air written on the device (b2s_matrix_fill_chain); returns the two public values."""
+        e = self._e
+        pv = np.zeros(2, dtype=np.uint32)
+        e._check(e._lib.b2s_matrix_fill_chain(e._h, matrix._h, seed, pv.ctypes.data_as(_lib.u32p)))
+        return pv
+
     def transport_matrix_from_device_to_host(self, matrix, layout="row", repr="canonical"):
         e = self._e
         h, w = matrix.height, matrix.width

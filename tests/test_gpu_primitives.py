@@ -91,3 +91,16 @@ def test_lde_linearity_at_scale(engine):
     # evaluations on g*H_N, which differ from the trace (shifted coset), so check degree instead:
     # interpolating the LDE back must give zero high coefficients -> LDE of the LDE's coset-0 block is consistent
     assert la.shape == (h * 2, w)
+
+
+@pytest.mark.parametrize("h,w,seed", [(1, 5, 0), (2, 5, 3), (64, 9, 7), (1 << 12, 40, 123456789), (128, 300, 2 ** 40 + 5)])
+def test_fill_chain_equals_host_chain_trace(engine, h, w, seed):
+    """b2s_matrix_fill_chain (bench.py's device tracegen stand-in) writes airs.chain_trace(hashed=True)"""
+    from openvm_b200 import airs
+    dev = engine.device()
+    m = dev.alloc_matrix(h, w)
+    pv = dev.fill_chain(m, seed)
+    parts, want_pv = airs.chain_trace(airs.chain_air(w), h, seed=seed, hashed=True)
+    assert np.array_equal(pv, want_pv)
+    assert np.array_equal(m.to_host(), parts[-1])
+    m.free()
