@@ -6,16 +6,19 @@
 // in-tree: leaf i of an LDE of height 2^h is the evaluation at GENERATOR * w_h^{bitrev_h(i)}
 // (extensions/native/recursion/src/fri/two_adic_pcs.rs:178-186; domain: fri/domain.rs:142-154).
 //
-// Design (B200). On this part the transform is bound by the integer-multiply pipe, not by HBM: a Montgomery
-// product is three 4-cycle IMADs on fmaheavy (profiles/r1a_ncu_full_summary.md), so the kernels are built to
-// execute exactly one product per butterfly and nothing else:
+// Design (B200). On this part the transform is bound by the integer-multiply pipe and the dispatch slots its 64-bit
+// forms hold, not by HBM (profiles/r2f_ncu_ntt_summary.md: math_pipe_throttle is the top stall of every pass, DRAM 37-50 %),
+// so the kernels are built to execute exactly one product per butterfly, in its cheapest form, and nothing else:
 //   * every stage is a Cooley-Tukey butterfly (a, b) -> (a + z*b, a - z*b), natural-order input, bit-reversed
 //     output, with the stage twiddle AND the coset shift merged into one table entry z = Z[2^t + q]
 //     (t = depth, q = sub-problem): no inter-digit twiddle products, no separate coset-scaling product;
 //     the only extra product is the 1/N factor, applied once per coefficient;
-//   * tables: ZI (inverse, N words) and ZF (forward, one N-word table per coset), built on the device once per
-//     (log N, log_blowup, input shift) and cached in the engine; early depths (shared by all tiles) stay in L1,
-//     late depths stream through L2 with 8/16-byte vector loads;
+//   * the product is Shoup's: the table holds (z, floor(z 2^32 / p)) and z*b mod p = b*z - mulhi(b, z')*p -- one IMAD.HI
+//     and two 32-bit IMADs (4 + 2.1 + 2.1 issue cycles) instead of the Montgomery product's IMAD.WIDE + IMAD + IMAD.HI
+//     (4.6 + 2.1 + 4); 2^24 x 256 LDE 97.4 -> 88.8 ms;
+//   * tables: ZI (inverse, N pairs) and ZF (forward, one N-pair table per coset), built on the device once per
+//     (log N, log_blowup, input shift) and cached in the engine; the 2^D - 1 pairs a tile needs are copied to shared memory
+//     with the tile, so the butterfly loops contain no global loads;
 //   * passes: [strided]* -> contiguous for the inverse (coefficients land bit-reversed), then
 //     gather -> [strided]* -> contiguous for the forward transform of each coset. The gather pass reads the
 //     bit-reversed coefficients as contiguous runs and writes natural slots, so no separate permutation pass
@@ -40,27 +43,33 @@ struct TabParams {
     uint32_t g[28];  // g[t] = generator of order 2^(t+1) (forward or inverse)
 };
 
-__global__ void build_table_kernel(uint32_t* z, uint32_t n, TabParams p) {
+// One entry = (w, w') with w the twiddle as a CANONICAL value and w' = floor(w 2^32 / p) (Shoup's precomputed quotient):
+// v w mod p is then  v*w - mulhi(v, w')*p  in [0, 2p) -- one 4-cycle IMAD.HI and two 2-cycle IMADs instead of the
+// Montgomery product's IMAD.WIDE + IMAD + IMAD.HI (4.6 + 2.1 + 4 cycles, profiles/r1j_dispatch_probe.md; the 64-bit forms
+// hold the sub-partition's dispatch, and the r2f capture shows math_pipe_throttle as the top stall of every pass). The data
+// words keep their Montgomery form: the map is linear.
+__global__ void build_table_kernel(uint2* z, uint32_t n, TabParams p) {
     uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= n) return;
-    if (idx == 0) { z[0] = 0; return; }
+    if (idx == 0) { z[0] = make_uint2(0, 0); return; }
     const uint32_t t = 31 - __clz(idx);
     const uint32_t q = idx - (1u << t);
     const uint32_t e = t ? (__brev(q) >> (32 - t)) : 0u;
-    z[idx] = (Fp::raw(p.s[t]) * fp_pow(Fp::raw(p.g[t]), e)).v;
+    const uint32_t w = (Fp::raw(p.s[t]) * fp_pow(Fp::raw(p.g[t]), e)).to_canonical();
+    z[idx] = make_uint2(w, (uint32_t)(((uint64_t)w << 32) / P));
 }
 
 struct TwiddleSet {  // inverse table for one log size
     unsigned logn;
-    uint32_t* zi;
+    uint2* zi;
 };
 struct ScaleSet {    // forward tables (one per coset) for (logn, log_blowup, shift_in)
     unsigned logn, log_blowup;
-    uint32_t* zf;    // [2^b][N]
+    uint2* zf;       // [2^b][N]
     uint32_t ninv;   // 1/N, Montgomery
 };
 
-static void fill_table(b2s_engine* e, uint32_t* z, unsigned logn, Fp base, bool inverse) {
+static void fill_table(b2s_engine* e, uint2* z, unsigned logn, Fp base, bool inverse) {
     TabParams p{};
     for (unsigned t = 0; t < logn; t++) {
         Fp g = two_adic_generator(t + 1);
@@ -78,7 +87,7 @@ static TwiddleSet* get_twiddles(b2s_engine* e, unsigned logn) {
     if (it != e->twiddles.end()) return it->second;
     TwiddleSet* t = new TwiddleSet();
     t->logn = logn;
-    t->zi = (uint32_t*)e->dmalloc((size_t)4 << logn);
+    t->zi = (uint2*)e->dmalloc((size_t)8 << logn);
     fill_table(e, t->zi, logn, Fp::one(), true);
     e->twiddles[logn] = t;
     return t;
@@ -86,7 +95,7 @@ static TwiddleSet* get_twiddles(b2s_engine* e, unsigned logn) {
 
 void free_twiddles(b2s_engine* e) {
     for (auto& kv : e->twiddles) {
-        e->dfree(kv.second->zi, (size_t)4 << kv.second->logn);
+        e->dfree(kv.second->zi, (size_t)8 << kv.second->logn);
         delete kv.second;
     }
     e->twiddles.clear();
@@ -100,7 +109,7 @@ static ScaleSet* get_scales(b2s_engine* e, unsigned logn, unsigned log_blowup, F
     s->logn = logn;
     s->log_blowup = log_blowup;
     const uint32_t B = 1u << log_blowup;
-    s->zf = (uint32_t*)e->dmalloc(((size_t)4 << logn) * B);
+    s->zf = (uint2*)e->dmalloc(((size_t)8 << logn) * B);
     Fp base = Fp::raw(M_GENERATOR) * fp_inv(shift_in);
     Fp wm = two_adic_generator(logn + log_blowup);
     for (uint32_t j = 0; j < B; j++) {
@@ -115,7 +124,7 @@ static ScaleSet* get_scales(b2s_engine* e, unsigned logn, unsigned log_blowup, F
 void free_scales(b2s_engine* e) {
     for (auto& kv : e->scales) {
         ScaleSet* s = kv.second;
-        e->dfree(s->zf, ((size_t)4 << s->logn) << s->log_blowup);
+        e->dfree(s->zf, ((size_t)8 << s->logn) << s->log_blowup);
         delete s;
     }
     e->scales.clear();
@@ -123,35 +132,62 @@ void free_scales(b2s_engine* e) {
 
 // ---- register butterfly block -----------------------------------------------------------------------------
 // 2^E consecutive table words starting at z (aligned to 4 * 2^E bytes)
+// 2^E consecutive words starting at z (aligned to 4 * 2^E bytes), from the tile's twiddles in shared memory
 template <int E>
-B2_D void load_tw(const uint32_t* __restrict__ z, uint32_t (&w)[1 << E]) {
+B2_D void load_tw(const uint32_t* z, uint32_t (&w)[1 << E]) {
     if constexpr (E == 0) {
-        w[0] = __ldg(z);
+        w[0] = z[0];
     } else if constexpr (E == 1) {
-        uint2 a = __ldg(reinterpret_cast<const uint2*>(z));
+        uint2 a = *reinterpret_cast<const uint2*>(z);
         w[0] = a.x; w[1] = a.y;
     } else if constexpr (E == 2) {
-        uint4 a = __ldg(reinterpret_cast<const uint4*>(z));
+        uint4 a = *reinterpret_cast<const uint4*>(z);
         w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w;
     } else {
-        uint4 a = __ldg(reinterpret_cast<const uint4*>(z));
-        uint4 b = __ldg(reinterpret_cast<const uint4*>(z) + 1);
+        uint4 a = *reinterpret_cast<const uint4*>(z);
+        uint4 b = *(reinterpret_cast<const uint4*>(z) + 1);
         w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w;
         w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
     }
 }
 
-template <int R, int E>
-B2_D void ct_stage(Fp (&v)[1 << R], const uint32_t* __restrict__ z, uint32_t idx0) {
+// The 2^D - 1 table entries a tile's D depths use, copied next to the tile: tw[2^k + i] = Z[(root << k) + i] for depth k of the
+// tile, i < 2^k, root = 2^t0 + (sub-problem of the tile); the Shoup companions go to tw[count + ...]. The butterfly loops read
+// their twiddles from shared memory (index (1 << depth) + sub-problem inside the tile); read straight from the table they
+// were L2-latency loads in the middle of the arithmetic (r1e: long_scoreboard 5.6 -> r2f: 1.3).
+B2_D void stage_twiddles(uint32_t* tw, const uint2* __restrict__ z, uint32_t root, uint32_t count, uint32_t tid, uint32_t nthreads) {
+    for (uint32_t i = tid; i < count; i += nthreads) {
+        uint2 v = make_uint2(0, 0);
+        if (i) {
+            const uint32_t k = 31 - __clz(i);
+            v = __ldg(z + ((size_t)root << k) + (i - (1u << k)));
+        }
+        tw[i] = v.x;
+        tw[count + i] = v.y;
+    }
+}
+
+// v * w mod p for a canonical twiddle w with its Shoup companion ws; v in [0, p) in any (linear) representation
+B2_D Fp shoup_mul(Fp v, uint32_t w, uint32_t ws) {
+    const uint32_t q = __umulhi(v.v, ws);
+    const uint32_t r = v.v * w - q * P;       // exact value in [0, 2p), computed mod 2^32
+    const uint32_t c = r - P;
+    return Fp::raw(c < r ? c : r);
+}
+
+// tws = tw + TW_COUNT (the companions): TWC is the number of entries per plane (2^D)
+template <int R, int E, int TWC>
+B2_D void ct_stage(Fp (&v)[1 << R], const uint32_t* z, uint32_t idx0) {
     constexpr int half = 1 << (R - 1 - E);
-    uint32_t w[1 << E];
+    uint32_t w[1 << E], ws[1 << E];
     load_tw<E>(z + ((size_t)idx0 << E), w);
+    load_tw<E>(z + TWC + ((size_t)idx0 << E), ws);
 #pragma unroll
     for (int j = 0; j < (1 << E); j++) {
 #pragma unroll
         for (int k = 0; k < half; k++) {
             const int ia = j * 2 * half + k, ib = ia + half;
-            Fp t = v[ib] * Fp::raw(w[j]);
+            Fp t = shoup_mul(v[ib], w[j], ws[j]);
             Fp a = v[ia];
             v[ia] = a + t;
             v[ib] = a - t;
@@ -160,12 +196,12 @@ B2_D void ct_stage(Fp (&v)[1 << R], const uint32_t* __restrict__ z, uint32_t idx
 }
 
 // R depths on 2^R values; depth e pairs indices differing in bit R-1-e; idx0 = 2^depth + sub-problem
-template <int R>
-B2_D void ct_block(Fp (&v)[1 << R], const uint32_t* __restrict__ z, uint32_t idx0) {
-    ct_stage<R, 0>(v, z, idx0);
-    if constexpr (R >= 2) ct_stage<R, 1>(v, z, idx0);
-    if constexpr (R >= 3) ct_stage<R, 2>(v, z, idx0);
-    if constexpr (R >= 4) ct_stage<R, 3>(v, z, idx0);
+template <int R, int TWC>
+B2_D void ct_block(Fp (&v)[1 << R], const uint32_t* z, uint32_t idx0) {
+    ct_stage<R, 0, TWC>(v, z, idx0);
+    if constexpr (R >= 2) ct_stage<R, 1, TWC>(v, z, idx0);
+    if constexpr (R >= 3) ct_stage<R, 2, TWC>(v, z, idx0);
+    if constexpr (R >= 4) ct_stage<R, 3, TWC>(v, z, idx0);
 }
 
 template <int R>
@@ -182,7 +218,7 @@ struct PassParams {
     const uint32_t* in;
     uint32_t* out;
     uint64_t in_col_stride, out_col_stride;
-    const uint32_t* z;        // table; coset c uses z + c * 2^log_len
+    const uint2* z;           // table of (w, w') pairs; coset c uses z + c * 2^log_len
     uint32_t width;           // columns covered by the launch (contiguous pass: for the run -> column map)
     uint32_t log_len;         // log2 of the transform length n
     uint32_t t0;              // global depth of the first stage of this pass
@@ -202,7 +238,7 @@ struct PassParams {
 
 template <int D, int U, bool GATHER>
 struct K1Rounds {
-    static B2_D void run(uint32_t* x, const uint32_t* __restrict__ z, uint32_t sub0) {
+    static B2_D void run(uint32_t* x, const uint32_t* z, uint32_t sub0) {
         constexpr int R = (U == 0) ? first_radix(D) : 4;
         constexpr int PITCH = GATHER ? 33 : 32;
         constexpr uint32_t NBLK = 1u << (D - R);
@@ -227,7 +263,7 @@ struct K1Rounds {
 #pragma unroll
                 for (int m = 0; m < (1 << R); m++) v[m] = Fp::raw(x[(row0 + m * rs) * PITCH + lane]);
             }
-            ct_block<R>(v, z, idx0);
+            ct_block<R, (1 << D)>(v, z, idx0);
             if constexpr (GATHER) {
 #pragma unroll
                 for (int m = 0; m < (1 << R); m++) x[(row0 + m * rs) * PITCH + lane] = v[brev_c<R>(m)].v;
@@ -242,7 +278,7 @@ struct K1Rounds {
 };
 template <int D, bool GATHER>
 struct K1Rounds<D, D, GATHER> {
-    static B2_D void run(uint32_t*, const uint32_t* __restrict__, uint32_t) {}
+    static B2_D void run(uint32_t*, const uint32_t*, uint32_t) {}
 };
 
 // Tile: rows r in [0, 2^D) at stride 2^(n - t0 - D) inside sub-problem `top` of depth t0, 32 adjacent positions.
@@ -259,7 +295,7 @@ __global__ void __launch_bounds__(K1_THREADS) ntt_strided_kernel(PassParams p) {
     const uint32_t col = blockIdx.y;
     const uint32_t cz = p.coset ? blockIdx.z : 0;
     const uint64_t blk_off = p.coset && p.log_blowup ? ((uint64_t)(__brev(cz) >> (32 - p.log_blowup)) << n) : 0;
-    const uint32_t* __restrict__ z = p.z + ((size_t)cz << n);
+    const uint2* __restrict__ z = p.z + ((size_t)cz << n);
     const uint32_t tid = threadIdx.x;
     const uint32_t* in = p.in + (uint64_t)col * p.in_col_stride + (p.in_block ? blk_off : 0);
     uint32_t* out = p.out + (uint64_t)col * p.out_col_stride + blk_off;
@@ -331,8 +367,10 @@ __global__ void __launch_bounds__(K1_THREADS) ntt_strided_kernel(PassParams p) {
             }
         }
     }
+    uint32_t* tw = x + ((size_t)PITCH << D);
+    stage_twiddles(tw, z, (1u << p.t0) + top, 1u << D, tid, K1_THREADS);
     __syncthreads();
-    K1Rounds<D, 0, GATHER>::run(x, z, (1u << p.t0) + top);
+    K1Rounds<D, 0, GATHER>::run(x, tw, 1u);
     if constexpr (GATHER) {
         const uint64_t base = (uint64_t)chunk << 5;
         for (uint32_t e = tid; e < (8u << D); e += K1_THREADS) {
@@ -366,7 +404,7 @@ B2_D constexpr int pad_off(int m) {
 
 template <int D, int U>
 struct K2Rounds {
-    static B2_D void run(uint32_t* xr, const uint32_t* __restrict__ z, uint32_t sub0, uint32_t tr, bool live) {
+    static B2_D void run(uint32_t* xr, const uint32_t* z, uint32_t sub0, uint32_t tr, bool live) {
         constexpr int R = (U == 0) ? first_radix(D) : 4;
         constexpr int LS = D - U - R;
         constexpr uint32_t NBLK = 1u << (D - R);
@@ -382,7 +420,7 @@ struct K2Rounds {
                 Fp v[1 << R];
 #pragma unroll
                 for (int m = 0; m < (1 << R); m++) v[m] = Fp::raw(xb[pad_off<LS, R>(m)]);
-                ct_block<R>(v, z, (sub0 << U) + hi);
+                ct_block<R, (1 << D)>(v, z, (sub0 << U) + hi);
 #pragma unroll
                 for (int m = 0; m < (1 << R); m++) xb[pad_off<LS, R>(m)] = v[m].v;
             }
@@ -393,7 +431,7 @@ struct K2Rounds {
 };
 template <int D>
 struct K2Rounds<D, D> {
-    static B2_D void run(uint32_t*, const uint32_t* __restrict__, uint32_t, uint32_t, bool) {}
+    static B2_D void run(uint32_t*, const uint32_t*, uint32_t, uint32_t, bool) {}
 };
 
 // One run = 2^D consecutive words of a column = sub-problem `rho` of depth t0 = n - D. Runs are numbered across
@@ -408,7 +446,7 @@ __global__ void __launch_bounds__(K2Cfg<D>::THREADS) ntt_contig_kernel(PassParam
     const uint32_t cz = p.coset ? blockIdx.z : 0;
     const uint64_t blk_off = p.coset && p.log_blowup ? ((uint64_t)(__brev(cz) >> (32 - p.log_blowup)) << n) : 0;
     const uint64_t in_off = p.in_block ? blk_off : 0;
-    const uint32_t* __restrict__ z = p.z + ((size_t)cz << n);
+    const uint2* __restrict__ z = p.z + ((size_t)cz << n);
     const uint32_t tid = threadIdx.x;
     // Runs are numbered column-fastest (g = rho * width + col): the runs of one block, and neighbouring blocks, work on
     // the same sub-problem rho of different columns and therefore read the same twiddles (L1 / L2 hits instead of one
@@ -469,13 +507,23 @@ __global__ void __launch_bounds__(K2Cfg<D>::THREADS) ntt_contig_kernel(PassParam
             }
         }
     }
+    // twiddles of every sub-problem rho this block touches (runs are numbered column-fastest: at most RPC of them, usually
+    // RPC / width + 1), one 2^D-word set each
+    uint32_t* tw = x + (size_t)C::RPC * C::PITCH;
+    {
+        uint32_t nrho = (col0 + C::RPC - 1) / p.width + 1;
+        if (nrho > (uint32_t)C::RPC) nrho = C::RPC;
+        const uint32_t max_rho = 1u << log_rpc;
+        for (uint32_t j = 0; j < nrho && rho0 + j < max_rho; j++)
+            stage_twiddles(tw + ((size_t)j << (D + 1)), z, (1u << p.t0) + rho0 + j, 1u << D, tid, C::THREADS);
+    }
     __syncthreads();
     {
         const uint32_t rs = tid / C::TPR, tr = tid % C::TPR;
         const uint64_t g = run0 + rs;
         uint32_t col, rho;
         locate(rs, col, rho);
-        K2Rounds<D, 0>::run(x + rs * C::PITCH, z, (1u << p.t0) + rho, tr, g < total_runs);
+        K2Rounds<D, 0>::run(x + rs * C::PITCH, tw + ((size_t)(rho - rho0) << (D + 1)), 1u, tr, g < total_runs);
     }
     for (uint32_t e = tid; e < ((uint32_t)C::RPC << (D - LV)); e += C::THREADS) {
         const uint32_t rs = e >> (D - LV), w = (e & ((1u << (D - LV)) - 1)) << LV;
@@ -509,7 +557,7 @@ __global__ void replicate_kernel(const uint32_t* in, uint64_t in_col_stride, uin
 // ---- host side --------------------------------------------------------------------------------------------------
 template <int D, bool GATHER>
 static void launch_strided_t(b2s_engine* e, const PassParams& p, dim3 grid) {
-    constexpr size_t smem = ((size_t)1 << D) * (GATHER ? 33 : 32) * 4;
+    constexpr size_t smem = ((size_t)1 << D) * ((GATHER ? 33 : 32) + 2) * 4;   // tile + its twiddles (w and w')
     if (smem > 48 * 1024) {
         // once per device and instantiation; engines on several host threads share the flags
         static std::once_flag configured[64];
@@ -544,7 +592,16 @@ static void launch_contig_t(b2s_engine* e, const PassParams& p, unsigned cosets)
     const uint64_t total_runs = (uint64_t)p.width << (p.log_len - D);
     const uint64_t blocks = (total_runs + C::RPC - 1) / C::RPC;
     B2_REQUIRE(blocks <= 0x7FFFFFFFull, B2S_ERR_SHAPE, "ntt: too many runs in one launch");
-    ntt_contig_kernel<D><<<dim3((unsigned)blocks, 1, cosets), C::THREADS, (size_t)C::RPC * C::PITCH * 4, e->stream>>>(p);
+    constexpr size_t smem = (size_t)C::RPC * (C::PITCH + (2 << D)) * 4;   // runs + one twiddle set (w, w') per run slot
+    if (smem > 48 * 1024) {
+        static std::once_flag configured[64];
+        cudaError_t err = cudaSuccess;
+        std::call_once(configured[e->device & 63], [&] {
+            err = cudaFuncSetAttribute(ntt_contig_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        });
+        B2_CUDA(err);
+    }
+    ntt_contig_kernel<D><<<dim3((unsigned)blocks, 1, cosets), C::THREADS, smem, e->stream>>>(p);
     B2_CHECK_LAUNCH();
     e->launches[0]++;
 }
@@ -659,9 +716,9 @@ void lde_columns(b2s_engine* e, const uint32_t* in, uint64_t in_col_stride, unsi
     ScaleSet* sc = get_scales(e, logn, log_blowup, shift_in);
     const Plan pl = make_plan(logn);
 
-    // column group: bounded coefficient workspace (512 MiB), large enough that every launch fills the chip several
-    // times over (the passes are multiply-bound, not HBM-bound, so L2 residency of the group does not matter)
-    uint64_t group_elems = (uint64_t)1 << 27;
+    // column group: bounded coefficient workspace (2 GiB). Wider groups share each sub-problem's twiddles between more
+    // columns: 2^24 x 256 LDE 88.8 ms with 2^27-element groups, 83.7 ms with 2^29 (profiles/r2g_lde_shoup.md)
+    uint64_t group_elems = (uint64_t)1 << 29;
     if (const char* env = getenv("B2S_LDE_GROUP_ELEMS")) group_elems = strtoull(env, nullptr, 10);
     uint64_t G = group_elems / N;
     if (G < 1) G = 1;

@@ -1,6 +1,6 @@
 """Host/device timeline of one shape-replay segment proof (B2S_PROVE_TRACE marks from prover.cu)."""
 import os, sys, time
-os.environ.setdefault("B2S_PROVE_TRACE", "1")
+os.environ.setdefault("B2S_PROVE_TRACE", "2")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from openvm_b200 import B2Engine, FriParameters, AirProvingContext, airs as A
 
@@ -11,8 +11,8 @@ air_objs = [A.segment_air(w, perm_cols=pc) for _, w, pc in shapes]
 pk = dev.transport_pk_to_device(A.build_key(air_objs, None, log_up_pow_bits=16))
 ctx = []
 for i, (lh, w, _pc) in enumerate(shapes):
-    parts, pv = A.chain_trace(air_objs[i], 1 << lh, seed=i)
-    ctx.append(AirProvingContext(i, dev.transport_matrix_to_device(parts[-1]), pv))
+    m = dev.alloc_matrix(1 << lh, w)
+    ctx.append(AirProvingContext(i, m, dev.fill_chain(m, 100 + i)))
 for it in range(3):
     print(f"--- proof {it}", file=sys.stderr)
     t = time.perf_counter()
