@@ -307,6 +307,7 @@ void b2s_engine_free(b2s_engine* e) {
     for (auto ev : e->event_pool) cudaEventDestroy(ev);
     cudaStreamSynchronize(e->stream);
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
+    for (auto st : e->aux_streams) cudaStreamDestroy(st);
     if (e->own_stream) cudaStreamDestroy(e->stream);
     delete e;
 }

@@ -67,6 +67,7 @@ struct b2s_engine {
     uint64_t quotient_launches[2] = {0, 0};  // generated kernels, interpreter
     uint64_t permutations = 0;
     cudaStream_t copy_stream = nullptr;                     // host -> device staging of the streaming commit
+    std::vector<cudaStream_t> aux_streams;                  // side streams for the quotient kernels of a proof (qjit.cu)
     std::map<uint64_t, uint32_t*> selector_cache;           // (log height, log quotient degree, blowup) -> 4 planes
     size_t selector_cache_bytes = 0;
     uint32_t pow_override[2] = {0xFFFFFFFFu, 0xFFFFFFFFu};  // [logup, fri]; 0xFFFFFFFF = search for the minimum witness
@@ -232,8 +233,17 @@ bool quotient_jit_enabled();
 size_t quotient_jit_prepare(AirKeyDev& a);
 void quotient_jit_compile(AirKeyDev& a, size_t k);
 std::string quotient_jit_ptx(const AirKeyDev& a);
-void quotient_jit_launch(b2s_engine* e, const AirKeyDev& a, const uint32_t* const* mats, const uint32_t* publics,
+// all quotient kernels of one proof between one fork and one join over the engine's side streams (qjit.cu)
+struct QuotientBatch {
+    struct Finish { const uint32_t* acc; uint32_t K; const uint32_t* sel; uint32_t* out; unsigned n, lq; };
+    b2s_engine* e = nullptr;
+    unsigned next = 0;
+    std::vector<Finish> finishes;
+};
+void quotient_batch_begin(b2s_engine* e, QuotientBatch& qb);
+void quotient_jit_launch(QuotientBatch& qb, const AirKeyDev& a, const uint32_t* const* mats, const uint32_t* publics,
                          const uint32_t* alpha_pows, const uint32_t* ef_consts, uint32_t* acc, uint32_t* out, unsigned n, unsigned lq);
+void quotient_batch_end(QuotientBatch& qb);
 void free_selectors(b2s_engine* e);
 // prover.cu
 b2s_pk* pk_load(b2s_engine* e, const uint32_t* words, size_t n, bool host_only = false, uint32_t log_blowup = 0);

@@ -171,6 +171,56 @@ B2_D void hash_node4(const uint32_t* const* __restrict__ cols, uint32_t ncols, u
     }
 }
 
+// compress(prev[2i], prev[2i+1]) and, when the level has row digests to inject, compress(that, inj[i]); four lanes per node
+// as in hash_node4 (lane `sub` holds state words 4 sub .. 4 sub + 3). The row digests come from rowhash_groups_kernel.
+B2_D void compress_node4(const uint32_t* prev, const uint32_t* inj, uint32_t* out, uint64_t n, uint64_t i, uint32_t sub, bool store) {
+    Fp s[4], diag[4];
+    const uint64_t np = 2 * n, node = 2 * i + (sub >> 1);
+    const uint32_t w0 = 4 * (sub & 1);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        diag[k] = Fp::raw(P2G_DIAG[4 * sub + k]);
+        s[k] = Fp::raw(__ldcg(prev + (uint64_t)(w0 + k) * np + node));
+    }
+    poseidon2_permute4(s, diag, sub);
+    if (inj) {
+        if (sub >= 2) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) s[k] = Fp::raw(__ldcg(inj + (uint64_t)(w0 + k) * n + i));
+        }
+        poseidon2_permute4(s, diag, sub);
+    }
+    if (store && sub < 2) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) out[(uint64_t)(4 * sub + k) * n + i] = s[k].v;
+    }
+}
+
+// Row digests of EVERY height group of a commitment in one launch (groups of at most SUBTREE_MAX_FIRST rows): a sponge over a
+// 3164-column row is 396 dependent permutations (~1 ms) whatever the row count, and a segment's tree has a dozen such groups;
+// hashed level by level inside the tree walk their latencies added up (r2h launch list: tree_subtree_kernel 9 ms of a
+// 44 ms proof). Here they overlap, and the tree walk only compresses.
+constexpr int ROWHASH_MAX_GROUPS = 32;
+constexpr int ROWHASH_THREADS = 256;
+struct RowHashParams {
+    const uint32_t* const* cols[ROWHASH_MAX_GROUPS];
+    uint32_t* out[ROWHASH_MAX_GROUPS];
+    uint32_t ncols[ROWHASH_MAX_GROUPS];
+    uint32_t n[ROWHASH_MAX_GROUPS];
+    uint32_t first_block[ROWHASH_MAX_GROUPS + 1];
+    uint32_t ngroups;
+};
+__global__ void __launch_bounds__(ROWHASH_THREADS) rowhash_groups_kernel(RowHashParams p) {
+    uint32_t g = 0;
+    while (g + 1 < p.ngroups && blockIdx.x >= p.first_block[g + 1]) g++;
+    const uint64_t n = p.n[g];
+    const uint64_t t = (uint64_t)(blockIdx.x - p.first_block[g]) * blockDim.x + threadIdx.x;
+    const uint64_t i = t >> 2;
+    // whole warps past the end leave together; inside a warp idle quads keep the shuffles converged
+    if ((t & ~31ull) >> 2 >= n) return;
+    hash_node4(p.cols[g], p.ncols[g], n, nullptr, p.out[g], 0, i < n ? i : n - 1, (uint32_t)(t & 3), i < n);
+}
+
 // one level of at most COOP_MAX_NODES nodes, four lanes per node (same modes as tree_level_kernel). Above ~2^13 nodes
 // the machine is full and the one-node-per-thread kernel wins (the four-lane form spends ~1.5 x the multiplies: every
 // lane runs the partial-round S-box and the diagonal is a generic product).
@@ -193,8 +243,7 @@ constexpr int SUBTREE_THREADS = 4 * SUBTREE_NODES;
 constexpr int SUBTREE_MAX_LEVELS = 9;
 constexpr uint64_t SUBTREE_MAX_FIRST = 1u << 14;  // one wave of blocks; above this the levels run one launch each
 struct SubtreeParams {
-    const uint32_t* const* cols[SUBTREE_MAX_LEVELS];
-    uint32_t ncols[SUBTREE_MAX_LEVELS];
+    const uint32_t* inj[SUBTREE_MAX_LEVELS];   // row digests injected at level l (rowhash_groups_kernel), or null
     uint32_t* out[SUBTREE_MAX_LEVELS];
     const uint32_t* prev0;
     uint64_t n0;        // nodes of the first level handled here
@@ -212,7 +261,7 @@ __global__ void __launch_bounds__(SUBTREE_THREADS, 1) tree_subtree_kernel(Subtre
         if ((threadIdx.x >> 5) * 8 < w) {
             const bool valid = local < w;
             const uint64_t i = (uint64_t)blockIdx.x * w + (valid ? local : w - 1);
-            hash_node4(p.cols[l], p.ncols[l], n, prev, p.out[l], p.ncols[l] ? 1 : 2, i, sub, valid);
+            compress_node4(prev, p.inj[l], p.out[l], n, i, sub, valid);
         }
         __syncthreads();
         prev = p.out[l];
@@ -520,11 +569,42 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
         }
         B2_CUDA(cudaMemcpyAsync(d_ptrs, flat.data(), total_cols * sizeof(void*), cudaMemcpyHostToDevice, e->stream));
     }
-    // leaves
     d->layers.clear();
     d->layer_nodes.clear();
-    if (leaf_layer) {
-        d->layers.push_back(leaf_layer);
+    // ---- row digests of every group of at most SUBTREE_MAX_FIRST rows, one launch (Poseidon2-BabyBear only)
+    std::map<uint64_t, uint32_t*> inj;           // height -> digest planes (the tallest group's go straight into layer 0)
+    std::vector<std::pair<uint32_t*, size_t>> inj_bufs;
+    uint32_t* small_leaf = nullptr;
+    if (!e->hash_kind) {
+        RowHashParams rp{};
+        uint32_t blocks = 0;
+        for (auto it = groups.rbegin(); it != groups.rend(); ++it) {   // tallest first
+            const uint64_t h = it->first;
+            if (h > SUBTREE_MAX_FIRST || (h == hmax && leaf_layer)) continue;
+            B2_REQUIRE(rp.ngroups < ROWHASH_MAX_GROUPS, B2S_ERR_SHAPE, "mmcs: too many distinct matrix heights");
+            uint32_t* out = (uint32_t*)e->dmalloc(h * 32);
+            if (h == hmax) small_leaf = out;
+            else { inj[h] = out; inj_bufs.push_back({out, h * 32}); }
+            const uint32_t g = rp.ngroups++;
+            rp.cols[g] = group_dev[h];
+            rp.ncols[g] = (uint32_t)it->second.size();
+            rp.n[g] = (uint32_t)h;
+            rp.out[g] = out;
+            rp.first_block[g] = blocks;
+            blocks += (uint32_t)((4 * h + ROWHASH_THREADS - 1) / ROWHASH_THREADS);
+            e->permutations += h * ((rp.ncols[g] + 7) / 8);
+        }
+        rp.first_block[rp.ngroups] = blocks;
+        if (rp.ngroups) {
+            StageScope sc(e, ST_LEAF);
+            rowhash_groups_kernel<<<blocks, ROWHASH_THREADS, 0, e->stream>>>(rp);
+            B2_CHECK_LAUNCH();
+            e->launches[1]++;
+        }
+    }
+    // leaves
+    if (leaf_layer || small_leaf) {
+        d->layers.push_back(leaf_layer ? leaf_layer : small_leaf);
         d->layer_nodes.push_back(hmax);
     } else {
         StageScope sc(e, ST_LEAF);
@@ -541,7 +621,8 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
     while (h > 1) {
         uint64_t nh = h / 2;
         if (!e->hash_kind && nh <= SUBTREE_MAX_FIRST) {
-            // log2(W) + 1 levels in one launch (all remaining ones when nh <= SUBTREE_NODES)
+            // log2(W) + 1 levels in one launch (all remaining ones when nh <= SUBTREE_NODES): compressions only, the row
+            // digests of the groups that join on the way are already there
             StageScope sc(e, ST_COMPRESS);
             SubtreeParams tp{};
             tp.prev0 = d->layers.back();
@@ -550,13 +631,12 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
             uint32_t l = 0;
             uint64_t m = nh;
             for (uint32_t w = tp.w0; w >= 1; w >>= 1, m >>= 1, l++) {
-                auto it = groups.find(m);
-                tp.cols[l] = it != groups.end() ? group_dev[m] : nullptr;
-                tp.ncols[l] = it != groups.end() ? (uint32_t)it->second.size() : 0u;
+                auto it = inj.find(m);
+                tp.inj[l] = it != inj.end() ? it->second : nullptr;
                 tp.out[l] = (uint32_t*)e->dmalloc(m * 32);
                 d->layers.push_back(tp.out[l]);
                 d->layer_nodes.push_back(m);
-                e->permutations += m * (tp.ncols[l] ? (tp.ncols[l] + 7) / 8 + 2 : 1);
+                e->permutations += m * (tp.inj[l] ? 2 : 1);
             }
             tp.levels = l;
             tree_subtree_kernel<<<(unsigned)(nh / tp.w0), SUBTREE_THREADS, 0, e->stream>>>(tp);
@@ -585,6 +665,7 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
         d->layer_nodes.push_back(nh);
         h = nh;
     }
+    for (auto& b : inj_bufs) e->dfree(b.first, b.second);
     e->dfree(d_ptrs, total_cols * sizeof(void*));
 }
 

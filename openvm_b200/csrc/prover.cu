@@ -1149,6 +1149,10 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
         size_t total_chunks = 0;
         for (auto* k : keys) total_chunks += (size_t)1 << k->log_qd;
         chunk_views.reserve(total_chunks);
+        QuotientBatch qbatch;
+        bool any_jit = false;
+        for (auto* k : keys) any_jit |= !k->jit_kernels.empty();
+        if (any_jit) quotient_batch_begin(e, qbatch);
         for (size_t i = 0; i < n_airs; i++) {
             const AirKeyDev& k = *keys[i];
             const unsigned n = logn[i], lq = k.log_qd;
@@ -1205,8 +1209,8 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
                     mats.push_back(after_pcs->mats[pos]->d);
                 }
                 B2_REQUIRE(mats.size() == k.jit_num_mats, B2S_ERR_INTERNAL, "quotient JIT: matrix count mismatch");
-                uint32_t* accbuf = k.jit_kernels.size() > 1 ? scratch.words((size_t)4 << (n + lq)) : nullptr;
-                quotient_jit_launch(e, k, mats.data(), d_pv, d_apow, d_efc, accbuf, qp.out, n, lq);
+                uint32_t* accbuf = k.jit_kernels.size() > 1 ? scratch.words((k.jit_kernels.size() * 4) << (n + lq)) : nullptr;
+                quotient_jit_launch(qbatch, k, mats.data(), d_pv, d_apow, d_efc, accbuf, qp.out, n, lq);
             } else {
                 launch_quotient(e, k.num_slots, k.num_slots_e, qp);
             }
@@ -1220,6 +1224,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
                 sh *= gq;
             }
         }
+        if (any_jit) quotient_batch_end(qbatch);
     }
     trace.mark("quotient eval");
     std::vector<const b2s_matrix*> chunk_ptrs;

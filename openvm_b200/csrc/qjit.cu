@@ -10,8 +10,10 @@
 // code ~7 for a base-field product and 3 for an addition.
 //
 // Long constraint lists are split into several kernels of bounded size (ptxas time grows faster than linearly in the
-// size of a basic block); kernel i > 0 continues the accumulator kernel i-1 left in `acc`, the last one divides by the
-// zerofier and writes the quotient chunks.
+// size of a basic block). The kernels of one AIR are INDEPENDENT: kernel k folds its own constraints (with their own powers
+// of alpha) into partial plane k; a fixed kernel adds the planes, divides by the zerofier and writes the quotient chunks.
+// All quotient kernels of a proof are spread over a few streams between one fork and one join (QuotientBatch): a 128-row
+// AIR with 82 kernels is latency-bound per kernel (~30 us each), so they have to overlap (r2h: 252 launches, 8.4 ms serial).
 #include "common.cuh"
 
 #include <cstdarg>
@@ -355,7 +357,7 @@ static std::vector<std::string> generate_ptx(const AirKeyDev& a, uint32_t& num_m
     const size_t nk = cuts.size() - 1;
     for (size_t i = 0; i < nk; i++)
         mods.push_back(".version 8.8\n.target sm_100a\n.address_size 64\n\n" +
-                       gen_kernel(g, "qk", cuts[i], cuts[i + 1], i == 0, i + 1 == nk));
+                       gen_kernel(g, "qk", cuts[i], cuts[i + 1], true, nk == 1));
     num_mats = g.num_mats;
     return mods;
 }
@@ -470,29 +472,96 @@ void free_selectors(b2s_engine* e) {
     e->selector_cache_bytes = 0;
 }
 
-// Launches the JIT-compiled kernels of `a`. mats: LDE matrices in the order [preprocessed][cached parts][common][after].
-void quotient_jit_launch(b2s_engine* e, const AirKeyDev& a, const uint32_t* const* mats, const uint32_t* publics,
+// adds the K partial planes of an AIR, divides by the zerofier and scatters into the quotient chunk matrices
+// (out[((qi * 4 + c) << n) + row], as the generated single-kernel code does)
+__global__ void quotient_finish_kernel(const uint32_t* __restrict__ acc, uint32_t K, const uint32_t* __restrict__ sel,
+                                       uint32_t* __restrict__ out, uint32_t n, uint32_t b, uint32_t lq) {
+    const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t rows = 1u << (n + lq);
+    if (gid >= rows) return;
+    const uint32_t lm = n + b;
+    const uint32_t Kb = __brev(gid) >> (32 - lm);
+    const uint32_t kq = Kb >> (b - lq);
+    const uint32_t qi = kq & ((1u << lq) - 1), row = kq >> lq;
+    const Fp iz = Fp::raw(sel[3 * (size_t)rows + gid]);
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        Fp sum = Fp::zero();
+        for (uint32_t k = 0; k < K; k++) sum += Fp::raw(acc[((size_t)k * 4 + c) * rows + gid]);
+        out[(((size_t)qi * 4 + c) << n) + row] = (sum * iz).v;
+    }
+}
+
+void quotient_batch_begin(b2s_engine* e, QuotientBatch& qb) {
+    qb.e = e;
+    qb.next = 0;
+    qb.finishes.clear();
+    if (e->aux_streams.empty()) {
+        unsigned ns = 8;
+        if (const char* env = getenv("B2S_QUOTIENT_STREAMS")) ns = (unsigned)std::max(1, std::min(32, atoi(env)));
+        for (unsigned i = 0; i < ns; i++) {
+            cudaStream_t st;
+            B2_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+            e->aux_streams.push_back(st);
+        }
+    }
+}
+
+// Launches the JIT-compiled kernels of `a` on the batch's streams. mats: LDE matrices in the order
+// [preprocessed][cached parts][common][after]. acc: K * 4 * 2^(n + lq) words when the AIR has K > 1 kernels.
+void quotient_jit_launch(QuotientBatch& qb, const AirKeyDev& a, const uint32_t* const* mats, const uint32_t* publics,
                          const uint32_t* alpha_pows, const uint32_t* ef_consts, uint32_t* acc, uint32_t* out, unsigned n, unsigned lq) {
+    b2s_engine* e = qb.e;
     const uint32_t* sel = quotient_selectors(e, n, lq);
     uint32_t un = n, ub = e->params.log_blowup, ulq = lq;
-    std::vector<void*> args;
-    std::vector<const uint32_t*> mat_vals(mats, mats + a.jit_num_mats);
-    for (auto& m : mat_vals) args.push_back((void*)&m);
-    args.push_back((void*)&publics);
-    args.push_back((void*)&alpha_pows);
-    args.push_back((void*)&ef_consts);
-    args.push_back((void*)&sel);
-    args.push_back((void*)&acc);
-    args.push_back((void*)&out);
-    args.push_back((void*)&un);
-    args.push_back((void*)&ub);
-    args.push_back((void*)&ulq);
     const uint32_t rows = 1u << (n + lq);
-    for (void* k : a.jit_kernels) {
-        B2_CUDA(cudaLaunchKernel((const void*)k, dim3((rows + 127) / 128), dim3(128), args.data(), 0, e->stream));
+    const size_t K = a.jit_kernels.size();
+    std::vector<const uint32_t*> mat_vals(mats, mats + a.jit_num_mats);
+    // the side streams this AIR uses start behind everything queued on the engine's stream so far: the committed LDEs, the
+    // allocations, and this AIR's own constant uploads (public values, challenges, column tables)
+    {
+        cudaEvent_t ev = e->get_event();
+        B2_CUDA(cudaEventRecord(ev, e->stream));
+        const size_t ns = std::min(K, e->aux_streams.size());
+        for (size_t j = 0; j < ns; j++) B2_CUDA(cudaStreamWaitEvent(e->aux_streams[(qb.next + j) % e->aux_streams.size()], ev, 0));
+        e->event_pool.push_back(ev);
+    }
+    for (size_t k = 0; k < K; k++) {
+        uint32_t* acc_k = acc ? acc + k * 4 * (size_t)rows : nullptr;
+        std::vector<void*> args;
+        for (auto& m : mat_vals) args.push_back((void*)&m);
+        args.push_back((void*)&publics);
+        args.push_back((void*)&alpha_pows);
+        args.push_back((void*)&ef_consts);
+        args.push_back((void*)&sel);
+        args.push_back((void*)&acc_k);
+        args.push_back((void*)&out);
+        args.push_back((void*)&un);
+        args.push_back((void*)&ub);
+        args.push_back((void*)&ulq);
+        cudaStream_t st = e->aux_streams[qb.next++ % e->aux_streams.size()];
+        B2_CUDA(cudaLaunchKernel((const void*)a.jit_kernels[k], dim3((rows + 127) / 128), dim3(128), args.data(), 0, st));
         e->launches[3]++;
         e->quotient_launches[0]++;
     }
+    if (K > 1) qb.finishes.push_back(QuotientBatch::Finish{acc, (uint32_t)K, sel, out, n, lq});
+}
+
+void quotient_batch_end(QuotientBatch& qb) {
+    b2s_engine* e = qb.e;
+    for (auto st : e->aux_streams) {
+        cudaEvent_t ev = e->get_event();
+        B2_CUDA(cudaEventRecord(ev, st));
+        B2_CUDA(cudaStreamWaitEvent(e->stream, ev, 0));
+        e->event_pool.push_back(ev);
+    }
+    for (auto& f : qb.finishes) {
+        const uint32_t rows = 1u << (f.n + f.lq);
+        quotient_finish_kernel<<<(rows + 127) / 128, 128, 0, e->stream>>>(f.acc, f.K, f.sel, f.out, f.n, e->params.log_blowup, f.lq);
+        B2_CHECK_LAUNCH();
+        e->launches[3]++;
+    }
+    qb.finishes.clear();
 }
 
 }  // namespace b2
