@@ -539,56 +539,95 @@ struct LogupParams {
     uint32_t* row_sums;            // 4 planes x N: sum over chunks of this row's reciprocal sums
     uint32_t n;
 };
-// one thread per trace row (natural order): evaluates message fields and counts, then per chunk
+// blockDim = (rows per block, S): S lanes share a trace row (natural order). Every lane evaluates the row's message fields and
+// counts; chunk c -- one reciprocal-sum column,
 //   perm_c[row] = sum_{i in chunk} (+-count_i) / (alpha + sum_j beta^j field_ij + beta^len_i (bus_i + 1))
+// -- is computed by lane c mod S. An extension-field inversion per interaction makes a 321-interaction row a ~1.4 ms chain
+// for one thread (r2h: logup_kernel<2048> 3 launches, 4.4 ms); short, wide AIRs get S up to 32, tall ones S = 1.
 template <int NSLOT>
-__global__ void __launch_bounds__(128) logup_kernel(LogupParams p) {
-    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(1024) logup_kernel(LogupParams p) {
+    extern __shared__ uint32_t red[];   // [S][4][rows per block], only for S > 1
+    const uint32_t S = blockDim.y, sy = threadIdx.y, rx = threadIdx.x, R = blockDim.x;
+    const uint32_t r = blockIdx.x * R + rx;
     const uint32_t N = 1u << p.n;
-    if (r >= N) return;
-    const uint32_t rows[2] = {r, (r + 1) & (N - 1)};
-    uint32_t slot[NSLOT];
-    Fp4 den = Fp4::zero(), chunk = Fp4::zero(), total = Fp4::zero();
-    uint32_t c = 0;
-    for (uint32_t pc = 0; pc < p.prog_len; pc++) {
-        const uint4 ins = __ldg(p.program + pc);
-        switch (ins.x) {
-            case OP_LOAD: slot[ins.y] = __ldg(p.cols[ins.z] + rows[ins.w]); break;
-            case OP_PUBLIC: slot[ins.y] = __ldg(p.publics + ins.z); break;
-            case OP_CONST: slot[ins.y] = ins.z; break;
-            case OP_FIRST: slot[ins.y] = r == 0 ? R_MOD_P : 0u; break;
-            case OP_LAST: slot[ins.y] = r == N - 1 ? R_MOD_P : 0u; break;
-            case OP_TRANS: slot[ins.y] = r == N - 1 ? 0u : R_MOD_P; break;
-            case OP_ADD: slot[ins.y] = (Fp::raw(slot[ins.z]) + Fp::raw(slot[ins.w])).v; break;
-            case OP_SUB: slot[ins.y] = (Fp::raw(slot[ins.z]) - Fp::raw(slot[ins.w])).v; break;
-            case OP_NEG: slot[ins.y] = (-Fp::raw(slot[ins.z])).v; break;
-            case OP_MUL: slot[ins.y] = (Fp::raw(slot[ins.z]) * Fp::raw(slot[ins.w])).v; break;
-            case OP_IFIELD: den += ld4(p.betas + 4 * ins.w) * Fp::raw(slot[ins.z]); break;
-            default: {  // OP_IEND
-                den += ld4(p.consts + 4 * ins.w);
-                Fp cnt = Fp::raw(slot[ins.z]);
-                if (ins.y & 1) cnt = -cnt;
-                chunk += fp4_inv(den) * cnt;
-                den = Fp4::zero();
-                if (ins.y & 2) {
+    const bool live = r < N;
+    Fp4 total = Fp4::zero();
+    if (live) {
+        const uint32_t rows[2] = {r, (r + 1) & (N - 1)};
+        uint32_t slot[NSLOT];
+        Fp4 den = Fp4::zero(), chunk = Fp4::zero();
+        uint32_t c = 0;
+        bool mine = sy == 0;
+        for (uint32_t pc = 0; pc < p.prog_len; pc++) {
+            const uint4 ins = __ldg(p.program + pc);
+            switch (ins.x) {
+                case OP_LOAD: slot[ins.y] = __ldg(p.cols[ins.z] + rows[ins.w]); break;
+                case OP_PUBLIC: slot[ins.y] = __ldg(p.publics + ins.z); break;
+                case OP_CONST: slot[ins.y] = ins.z; break;
+                case OP_FIRST: slot[ins.y] = r == 0 ? R_MOD_P : 0u; break;
+                case OP_LAST: slot[ins.y] = r == N - 1 ? R_MOD_P : 0u; break;
+                case OP_TRANS: slot[ins.y] = r == N - 1 ? 0u : R_MOD_P; break;
+                case OP_ADD: slot[ins.y] = (Fp::raw(slot[ins.z]) + Fp::raw(slot[ins.w])).v; break;
+                case OP_SUB: slot[ins.y] = (Fp::raw(slot[ins.z]) - Fp::raw(slot[ins.w])).v; break;
+                case OP_NEG: slot[ins.y] = (-Fp::raw(slot[ins.z])).v; break;
+                case OP_MUL: slot[ins.y] = (Fp::raw(slot[ins.z]) * Fp::raw(slot[ins.w])).v; break;
+                case OP_IFIELD:
+                    if (mine) den += ld4(p.betas + 4 * ins.w) * Fp::raw(slot[ins.z]);
+                    break;
+                default: {  // OP_IEND
+                    if (mine) {
+                        den += ld4(p.consts + 4 * ins.w);
+                        Fp cnt = Fp::raw(slot[ins.z]);
+                        if (ins.y & 1) cnt = -cnt;
+                        chunk += fp4_inv(den) * cnt;
+                        den = Fp4::zero();
+                    }
+                    if (ins.y & 2) {
+                        if (mine) {
 #pragma unroll
-                    for (int e = 0; e < 4; e++) p.out[((uint64_t)4 * c + e) * N + r] = chunk.c[e].v;
-                    total += chunk;
-                    chunk = Fp4::zero();
-                    c++;
+                            for (int e = 0; e < 4; e++) p.out[((uint64_t)4 * c + e) * N + r] = chunk.c[e].v;
+                            total += chunk;
+                            chunk = Fp4::zero();
+                        }
+                        c++;
+                        mine = (c & (S - 1)) == sy;
+                    }
                 }
             }
         }
     }
+    if (S > 1) {
 #pragma unroll
-    for (int e = 0; e < 4; e++) p.row_sums[(uint64_t)e * N + r] = total.c[e].v;
+        for (int e = 0; e < 4; e++) red[(sy * 4 + e) * R + rx] = total.c[e].v;
+        __syncthreads();
+        for (uint32_t s = S >> 1; s > 0; s >>= 1) {
+            if (sy < s) {
+#pragma unroll
+                for (int e = 0; e < 4; e++)
+                    red[(sy * 4 + e) * R + rx] = (Fp::raw(red[(sy * 4 + e) * R + rx]) + Fp::raw(red[((sy + s) * 4 + e) * R + rx])).v;
+            }
+            __syncthreads();
+        }
+        if (sy == 0)
+#pragma unroll
+            for (int e = 0; e < 4; e++) total.c[e] = Fp::raw(red[e * R + rx]);
+    }
+    if (live && sy == 0) {
+#pragma unroll
+        for (int e = 0; e < 4; e++) p.row_sums[(uint64_t)e * N + r] = total.c[e].v;
+    }
 }
-static void launch_logup(b2s_engine* e, uint32_t slots, const LogupParams& p) {
+static void launch_logup(b2s_engine* e, uint32_t slots, uint32_t num_chunks, const LogupParams& p) {
     const uint32_t N = 1u << p.n;
-    const dim3 grid((N + 127) / 128);
-    if (slots <= 32) logup_kernel<32><<<grid, 128, 0, e->stream>>>(p);
-    else if (slots <= 256) logup_kernel<256><<<grid, 128, 0, e->stream>>>(p);
-    else if (slots <= 2048) logup_kernel<2048><<<grid, 128, 0, e->stream>>>(p);
+    // lanes per row: a power of two, at most 32, at most the number of chunks, ~2^15 threads per launch for short traces
+    uint32_t S = 1;
+    while (S < 32 && 2 * S <= num_chunks && ((uint64_t)N * 2 * S) <= (1u << 15)) S *= 2;
+    const dim3 block(S == 1 ? 128 : 32, S);
+    const dim3 grid((N + block.x - 1) / block.x);
+    const size_t smem = S > 1 ? (size_t)S * 4 * block.x * 4 : 0;
+    if (slots <= 32) logup_kernel<32><<<grid, block, smem, e->stream>>>(p);
+    else if (slots <= 256) logup_kernel<256><<<grid, block, smem, e->stream>>>(p);
+    else if (slots <= 2048) logup_kernel<2048><<<grid, block, smem, e->stream>>>(p);
     else fail(B2S_ERR_CONSTRAINT_DEGREE, "logup: interaction program needs more than 2048 live values");
     B2_CHECK_LAUNCH();
     e->launches[3]++;
@@ -695,6 +734,58 @@ __global__ void bary_finish_kernel(const uint32_t* __restrict__ partial, uint32_
     *reinterpret_cast<uint4*>(vals + (uint64_t)c * 4) = make_uint4(s.c[0].v, s.c[1].v, s.c[2].v, s.c[3].v);
 }
 
+// All columns of all matrices of one trace height at one point in one launch (a segment opens ~200 (matrix, point) pairs;
+// one launch pair and one read-back each was 400 launches and 200 host waits): column blockIdx.x of the group is described by
+// BaryCol {column base (block 0 of its LDE), where its partial sums go}.
+struct BaryCol {
+    const uint32_t* col;
+    uint32_t partial_off;   // word offset of this column's [splits][4] partial sums
+    uint32_t splits;
+    uint32_t scale_idx;     // which ((z/g)^N - 1) / N factor applies
+    uint32_t pad;
+};
+__global__ void __launch_bounds__(DOT_THREADS) bary_dot_multi_kernel(const BaryCol* __restrict__ cols, const uint32_t* __restrict__ wts,
+                                                                     uint32_t n, uint32_t* __restrict__ partial) {
+    __shared__ uint32_t sm[4][DOT_THREADS];
+    const uint32_t N = 1u << n;
+    const BaryCol bc = cols[blockIdx.x];
+    const uint32_t split = blockIdx.y, splits = gridDim.y;
+    const uint32_t per = (N + splits - 1) / splits;
+    const uint32_t lo = split * per, hi = min(N, lo + per);
+    const uint32_t* __restrict__ colp = bc.col;
+    Fp acc[4];
+    for (uint32_t i = lo + threadIdx.x; i < hi; i += DOT_THREADS) {
+        const Fp v = Fp::raw(colp[i]);
+#pragma unroll
+        for (int c = 0; c < 4; c++) acc[c] += v * Fp::raw(wts[(uint64_t)c * N + i]);
+    }
+#pragma unroll
+    for (int c = 0; c < 4; c++) sm[c][threadIdx.x] = acc[c].v;
+    __syncthreads();
+    for (int s = DOT_THREADS / 2; s > 0; s >>= 1) {
+        if (threadIdx.x < s) {
+#pragma unroll
+            for (int c = 0; c < 4; c++) sm[c][threadIdx.x] = (Fp::raw(sm[c][threadIdx.x]) + Fp::raw(sm[c][threadIdx.x + s])).v;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x < 4) partial[bc.partial_off + split * 4 + threadIdx.x] = sm[threadIdx.x][0];
+}
+// every opened value of the proof: sums a column's partial dot products and applies its barycentric factor
+__global__ void bary_finish_multi_kernel(const BaryCol* __restrict__ cols, uint32_t ncols, const uint32_t* __restrict__ partial,
+                                         const uint32_t* __restrict__ scales, uint32_t* __restrict__ vals) {
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncols) return;
+    const BaryCol bc = cols[c];
+    Fp4 s = Fp4::zero();
+    for (uint32_t sp = 0; sp < bc.splits; sp++) {
+        const uint4 q = *reinterpret_cast<const uint4*>(partial + bc.partial_off + sp * 4);
+        s.c[0] += Fp::raw(q.x); s.c[1] += Fp::raw(q.y); s.c[2] += Fp::raw(q.z); s.c[3] += Fp::raw(q.w);
+    }
+    s = s * ld4(scales + 4 * bc.scale_idx);
+    *reinterpret_cast<uint4*>(vals + (uint64_t)c * 4) = make_uint4(s.c[0].v, s.c[1].v, s.c[2].v, s.c[3].v);
+}
+
 // ---- reduced openings ------------------------------------------------------------------------------------------------
 // All matrices of one LDE height in one launch. Every matrix of height 2^h is opened at zeta and, for trace matrices, at
 // zeta * g_N (quotient chunks: zeta only), so the two inverses 1 / (z_j - x) -- an exponentiation for x and two extension
@@ -739,6 +830,74 @@ __global__ void __launch_bounds__(128) reduced_open_height_kernel(const uint32_t
             acc1 += cf1 * (cz1 - inner);
         }
     }
+    Fp4 acc = acc0 * inv0;
+    if (two_points) acc += acc1 * inv1;
+#pragma unroll
+    for (int c = 0; c < 4; c++) ro[(uint64_t)c * H + row] = acc.c[c].v;
+}
+
+// The same for short LDE heights (< 2^17 rows), where one thread per row leaves the chip empty and a 3164-column row is a
+// 140 us dependent chain: S threads share a row, thread (rx, sy) takes columns sy, sy + S, ... of every matrix (loads stay
+// coalesced across the 32 rows of a warp), the S partial sums meet in shared memory and lane sy = 0 applies the inverses.
+// Sum over matrices of coef * (cz - inner) is linear in inner, so partial inners give partial sums; cz is added by sy = 0.
+constexpr int RO_ROWS = 32;
+__global__ void __launch_bounds__(1024) reduced_open_split_kernel(const uint32_t* __restrict__ descs, uint32_t nmats, uint32_t h,
+                                                                  const uint32_t* __restrict__ alpha_pows, uint32_t* __restrict__ ro,
+                                                                  Fp4 z0, Fp4 z1, uint32_t two_points, uint32_t wh) {
+    extern __shared__ uint32_t red[];   // [S][8][RO_ROWS]
+    const uint32_t S = blockDim.y, rx = threadIdx.x, sy = threadIdx.y;
+    const uint32_t H = 1u << h;
+    const uint32_t row = blockIdx.x * RO_ROWS + rx;
+    const bool live = row < H;
+    Fp4 acc0 = Fp4::zero(), acc1 = Fp4::zero();
+    if (live) {
+#pragma unroll 1
+        for (uint32_t m = 0; m < nmats; m++) {
+            const uint32_t* __restrict__ d = descs + (uint64_t)m * RO_DESC_WORDS;
+            const uint32_t* __restrict__ mat = reinterpret_cast<const uint32_t*>(((uint64_t)__ldg(d + 1) << 32) | __ldg(d));
+            const uint32_t width = __ldg(d + 2), npoints = __ldg(d + 3);
+            if (sy >= width && sy != 0) continue;
+            Fp4 inner = Fp4::zero();
+            for (uint32_t t = sy; t < width; t += S) {
+                const Fp v = Fp::raw(__ldg(mat + (uint64_t)t * H + row));
+                const uint4 ap = __ldg(reinterpret_cast<const uint4*>(alpha_pows) + t);
+                inner.c[0] += v * Fp::raw(ap.x); inner.c[1] += v * Fp::raw(ap.y);
+                inner.c[2] += v * Fp::raw(ap.z); inner.c[3] += v * Fp::raw(ap.w);
+            }
+            const Fp4 cf0(Fp::raw(__ldg(d + 12)), Fp::raw(__ldg(d + 13)), Fp::raw(__ldg(d + 14)), Fp::raw(__ldg(d + 15)));
+            Fp4 term0 = -inner;
+            if (sy == 0) term0 += Fp4(Fp::raw(__ldg(d + 4)), Fp::raw(__ldg(d + 5)), Fp::raw(__ldg(d + 6)), Fp::raw(__ldg(d + 7)));
+            acc0 += cf0 * term0;
+            if (npoints > 1) {
+                const Fp4 cf1(Fp::raw(__ldg(d + 16)), Fp::raw(__ldg(d + 17)), Fp::raw(__ldg(d + 18)), Fp::raw(__ldg(d + 19)));
+                Fp4 term1 = -inner;
+                if (sy == 0) term1 += Fp4(Fp::raw(__ldg(d + 8)), Fp::raw(__ldg(d + 9)), Fp::raw(__ldg(d + 10)), Fp::raw(__ldg(d + 11)));
+                acc1 += cf1 * term1;
+            }
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        red[(sy * 8 + c) * RO_ROWS + rx] = acc0.c[c].v;
+        red[(sy * 8 + 4 + c) * RO_ROWS + rx] = acc1.c[c].v;
+    }
+    __syncthreads();
+    for (uint32_t s = S >> 1; s > 0; s >>= 1) {
+        if (sy < s) {
+#pragma unroll
+            for (int c = 0; c < 8; c++)
+                red[(sy * 8 + c) * RO_ROWS + rx] = (Fp::raw(red[(sy * 8 + c) * RO_ROWS + rx]) + Fp::raw(red[((sy + s) * 8 + c) * RO_ROWS + rx])).v;
+        }
+        __syncthreads();
+    }
+    if (sy != 0 || !live) return;
+#pragma unroll
+    for (int c = 0; c < 4; c++) { acc0.c[c] = Fp::raw(red[c * RO_ROWS + rx]); acc1.c[c] = Fp::raw(red[(4 + c) * RO_ROWS + rx]); }
+    const uint32_t e = h ? (__brev(row) >> (32 - h)) : 0u;
+    const Fp x = Fp::raw(M_GENERATOR) * fp_pow(Fp::raw(wh), e);
+    Fp4 inv0, inv1 = Fp4::zero();
+    if (two_points) fp4_inv_pair(z0 - x, z1 - x, inv0, inv1);
+    else inv0 = fp4_inv(z0 - x);
     Fp4 acc = acc0 * inv0;
     if (two_points) acc += acc1 * inv1;
 #pragma unroll
@@ -1098,7 +1257,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             lp.out = scratch.words((size_t)4 * k.width_after * N);
             lp.row_sums = scratch.words((size_t)4 * N);
             lp.n = n;
-            launch_logup(e, k.islots, lp);
+            launch_logup(e, k.islots, k.num_chunks, lp);
             uint32_t* phi = lp.out + (size_t)4 * k.num_chunks * N;
             scan_planes(e, scratch, lp.row_sums, phi, (uint32_t)N);
             last_rows.push_back(phi);
@@ -1286,48 +1445,74 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             }
             return slot[which];
         };
-        struct Job { size_t r, m, p; uint32_t splits; size_t off, voff; cudaEvent_t done; };
+        // Value order = transcript order (round -> matrix -> point -> column, two_adic_pcs.rs:63-95): global column id c has
+        // its value at vals[4 c]. Columns are then grouped by (trace height, point) for the launches.
+        struct Job { size_t r, m, p; size_t first_col; };
         std::vector<Job> jobs;
-        size_t partial_words = 0, val_words = 0;
+        std::vector<BaryCol> cols;
+        std::vector<uint32_t> scales;
+        std::map<std::pair<unsigned, int>, std::vector<uint32_t>> by_group;   // (log_n, point index) -> column ids
+        size_t partial_words = 0;
+        const Fp ginv = fp_inv(Fp::raw(M_GENERATOR));
         for (size_t r = 0; r < rounds.size(); r++)
             for (size_t m = 0; m < rounds[r].mats.size(); m++)
                 for (size_t p = 0; p < rounds[r].mats[m].points.size(); p++) {
                     const RoundMat& rm = rounds[r].mats[m];
-                    uint32_t splits = (uint32_t)std::min<uint64_t>(64, std::max<uint64_t>(1, ((uint64_t)1 << rm.log_n) / 4096));
-                    jobs.push_back(Job{r, m, p, splits, partial_words, val_words, nullptr});
-                    partial_words += (size_t)rm.lde->width * splits * 4;
-                    val_words += (size_t)rm.lde->width * 4;
+                    const uint32_t splits = (uint32_t)std::min<uint64_t>(64, std::max<uint64_t>(1, ((uint64_t)1 << rm.log_n) / 4096));
+                    const Fp ninv = fp_inv(Fp::from_canonical((uint32_t)(((uint64_t)1 << rm.log_n) % P)));
+                    const Fp4 scale = (fp4_pow2k(rm.points[p] * ginv, rm.log_n) - Fp::one()) * ninv;
+                    const uint32_t scale_idx = (uint32_t)(scales.size() / 4);
+                    for (int c = 0; c < 4; c++) scales.push_back(scale.c[c].v);
+                    jobs.push_back(Job{r, m, p, cols.size()});
+                    auto& grp = by_group[{rm.log_n, (int)p}];
+                    for (uint64_t c = 0; c < rm.lde->width; c++) {
+                        grp.push_back((uint32_t)cols.size());
+                        cols.push_back(BaryCol{rm.lde->d + c * rm.lde->height, (uint32_t)partial_words, splits, scale_idx, 0});
+                        partial_words += (size_t)splits * 4;
+                    }
                 }
-        uint32_t* d_partial = scratch.words(partial_words);
-        uint32_t* d_vals = scratch.words(val_words);
-        // The values come back one (matrix, point) at a time into pinned memory, each behind its own event, in the order
-        // the transcript observes them (round -> matrix -> point -> column, two_adic_pcs.rs:63-95): the host hashes the
-        // values of one matrix while the device is still evaluating the next ones.
-        uint32_t* h_vals = (uint32_t*)e->host_pinned(val_words * 4);
-        const Fp ginv = fp_inv(Fp::raw(M_GENERATOR));
-        for (auto& j : jobs) {
-            const RoundMat& rm = rounds[j.r].mats[j.m];
-            const uint32_t width = (uint32_t)rm.lde->width;
-            uint32_t* w = get_weights(rm.log_n, (int)j.p, rm.points[j.p]);
-            bary_dot_kernel<<<dim3(width, j.splits), DOT_THREADS, 0, e->stream>>>(rm.lde->d, rm.lde->height, w, rm.log_n,
-                                                                                  d_partial + j.off);
-            B2_CHECK_LAUNCH();
-            const Fp ninv = fp_inv(Fp::from_canonical((uint32_t)(((uint64_t)1 << rm.log_n) % P)));
-            const Fp4 scale = (fp4_pow2k(rm.points[j.p] * ginv, rm.log_n) - Fp::one()) * ninv;
-            bary_finish_kernel<<<(width + 127) / 128, 128, 0, e->stream>>>(d_partial + j.off, width, j.splits, scale, d_vals + j.voff);
-            B2_CHECK_LAUNCH();
-            e->launches[3] += 2;
-            B2_CUDA(cudaMemcpyAsync(h_vals + j.voff, d_vals + j.voff, (size_t)width * 16, cudaMemcpyDeviceToHost, e->stream));
-            j.done = e->get_event();
-            B2_CUDA(cudaEventRecord(j.done, e->stream));
+        B2_REQUIRE(partial_words < 0xFFFFFFFFull, B2S_ERR_INTERNAL, "prove: too many opened columns");
+        const size_t ncols = cols.size(), val_words = ncols * 4;
+        // device copies: the column table once in value order (for the finish kernel) and once grouped (for the dot kernels)
+        std::vector<uint32_t> table_words((ncols * 2) * (sizeof(BaryCol) / 4));
+        {
+            BaryCol* t = reinterpret_cast<BaryCol*>(table_words.data());
+            size_t at = 0;
+            for (auto& c : cols) t[at++] = c;
+            for (auto& kv : by_group)
+                for (uint32_t id : kv.second) t[at++] = cols[id];
         }
+        static_assert(sizeof(BaryCol) == 24, "BaryCol layout");
+        const BaryCol* d_cols = reinterpret_cast<const BaryCol*>(scratch.upload(std::move(table_words)));
+        const uint32_t* d_scales = scratch.upload(std::move(scales));
+        uint32_t* d_partial = scratch.words(std::max<size_t>(partial_words, 4));
+        uint32_t* d_vals = scratch.words(std::max<size_t>(val_words, 4));
+        uint32_t* h_vals = (uint32_t*)e->host_pinned(val_words * 4);
+        {
+            size_t at = ncols;
+            for (auto& kv : by_group) {
+                const unsigned n = kv.first.first;
+                const int which = kv.first.second;
+                // every matrix of this height shares the point: zeta (0) or zeta * w_n (1)
+                const Fp4 z = which == 0 ? zeta : zeta * two_adic_generator(n);
+                uint32_t* w = get_weights(n, which, z);
+                const uint32_t splits = cols[kv.second[0]].splits;
+                bary_dot_multi_kernel<<<dim3((unsigned)kv.second.size(), splits), DOT_THREADS, 0, e->stream>>>(d_cols + at, w, n, d_partial);
+                B2_CHECK_LAUNCH();
+                e->launches[3]++;
+                at += kv.second.size();
+            }
+        }
+        bary_finish_multi_kernel<<<(unsigned)((ncols + 127) / 128), 128, 0, e->stream>>>(d_cols, (uint32_t)ncols, d_partial, d_scales, d_vals);
+        B2_CHECK_LAUNCH();
+        e->launches[3]++;
+        B2_CUDA(cudaMemcpyAsync(h_vals, d_vals, val_words * 4, cudaMemcpyDeviceToHost, e->stream));
         trace.mark("ood values enqueued");
+        B2_CUDA(cudaStreamSynchronize(e->stream));
         for (auto& j : jobs) {
             RoundMat& rm = rounds[j.r].mats[j.m];
-            B2_CUDA(cudaEventSynchronize(j.done));
-            e->event_pool.push_back(j.done);
             std::vector<Fp4> vals(rm.lde->width);
-            const uint32_t* src = h_vals + j.voff;
+            const uint32_t* src = h_vals + j.first_col * 4;
             for (uint64_t c = 0; c < rm.lde->width; c++) {
                 vals[c] = Fp4(Fp::raw(src[4 * c]), Fp::raw(src[4 * c + 1]), Fp::raw(src[4 * c + 2]), Fp::raw(src[4 * c + 3]));
                 ch.observe_ext(vals[c]);
@@ -1390,9 +1575,17 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             HeightBatch& hb = kv.second;
             const uint32_t nm = hb.nmats;
             const uint32_t* d_descs = scratch.upload(std::move(hb.descs));
-            reduced_open_height_kernel<<<((1u << h) + 127) / 128, 128, 0, e->stream>>>(
-                d_descs, nm, h, d_apow, ro[h], hb.z[0], hb.npoints > 1 ? hb.z[1] : Fp4::zero(), hb.npoints > 1 ? 1u : 0u,
-                two_adic_generator(h).v);
+            if (h >= 17) {
+                reduced_open_height_kernel<<<((1u << h) + 127) / 128, 128, 0, e->stream>>>(
+                    d_descs, nm, h, d_apow, ro[h], hb.z[0], hb.npoints > 1 ? hb.z[1] : Fp4::zero(), hb.npoints > 1 ? 1u : 0u,
+                    two_adic_generator(h).v);
+            } else {
+                // S threads per row, S = 2^(17 - h) capped at 32: the launch has ~2^17 threads whatever the height
+                const uint32_t S = std::min(32u, 1u << (17 - h));
+                reduced_open_split_kernel<<<((1u << h) + RO_ROWS - 1) / RO_ROWS, dim3(RO_ROWS, S), (size_t)S * 8 * RO_ROWS * 4, e->stream>>>(
+                    d_descs, nm, h, d_apow, ro[h], hb.z[0], hb.npoints > 1 ? hb.z[1] : Fp4::zero(), hb.npoints > 1 ? 1u : 0u,
+                    two_adic_generator(h).v);
+            }
             B2_CHECK_LAUNCH();
             e->launches[3]++;
         }

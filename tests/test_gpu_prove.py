@@ -49,7 +49,8 @@ def gpu_prove(eng, key, inputs, air_objs):
     return proof
 
 
-@pytest.mark.parametrize("n,b,queries,pow_bits", [(32, 1, 4, 3), (8, 2, 3, 0), (1 << 10, 1, 5, 8), (1 << 15, 1, 100, 16)])
+@pytest.mark.parametrize("n,b,queries,pow_bits", [(32, 1, 4, 3), (8, 2, 3, 0), (1 << 10, 1, 5, 8), (1 << 15, 1, 100, 16),
+                                                  (1 << 16, 1, 4, 3)])   # LDE height 2^17: the tall-height kernels
 def test_fibonacci_proof_bytes(orc, n, b, queries, pow_bits):
     air = airs.fibonacci_air()
     key = build_key(orc, [air], b)
