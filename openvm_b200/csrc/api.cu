@@ -308,6 +308,7 @@ void b2s_engine_free(b2s_engine* e) {
     cudaStreamSynchronize(e->stream);
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
     for (auto st : e->aux_streams) cudaStreamDestroy(st);
+    if (e->hash_stream) cudaStreamDestroy(e->hash_stream);
     if (e->own_stream) cudaStreamDestroy(e->stream);
     delete e;
 }

@@ -67,6 +67,7 @@ struct b2s_engine {
     uint64_t quotient_launches[2] = {0, 0};  // generated kernels, interpreter
     uint64_t permutations = 0;
     cudaStream_t copy_stream = nullptr;                     // host -> device staging of the streaming commit
+    cudaStream_t hash_stream = nullptr;                     // row digests of short height groups next to the tall levels (merkle.cu)
     std::vector<cudaStream_t> aux_streams;                  // side streams for the quotient kernels of a proof (qjit.cu)
     std::map<uint64_t, uint32_t*> selector_cache;           // (log height, log quotient degree, blowup) -> 4 planes
     size_t selector_cache_bytes = 0;

@@ -86,6 +86,28 @@ __global__ void __launch_bounds__(HASH_THREADS, HASH_MIN_BLOCKS)
     hash_node(cols, ncols, n, prev, out, mode, i);
 }
 
+// compress(prev[2i], prev[2i+1]), then compress(that, inj[i]): a level above SUBTREE_MAX_FIRST nodes whose row digests were
+// computed by rowhash_groups_kernel (one node per thread)
+__global__ void __launch_bounds__(HASH_THREADS, HASH_MIN_BLOCKS)
+    tree_level_inject_kernel(const uint32_t* __restrict__ prev, const uint32_t* __restrict__ inj, uint32_t* __restrict__ out, uint64_t n) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fp s[16];
+    const uint64_t np = 2 * n;
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        const uint2 lr = __ldcg(reinterpret_cast<const uint2*>(prev + (uint64_t)w * np + 2 * i));
+        s[w] = Fp::raw(lr.x);
+        s[8 + w] = Fp::raw(lr.y);
+    }
+    poseidon2_permute(s);
+#pragma unroll
+    for (int w = 0; w < 8; w++) s[8 + w] = Fp::raw(__ldg(inj + (uint64_t)w * n + i));
+    poseidon2_permute(s);
+#pragma unroll
+    for (int w = 0; w < 8; w++) out[(uint64_t)w * n + i] = s[w].v;
+}
+
 // ---- four lanes per permutation --------------------------------------------------------------------------------------
 // Small levels (the top of every tree, every level of the FRI commit-phase trees) are bound by the LATENCY of one
 // permutation chain per thread (~8 us: 5.7 k dependent-ish instructions), not by throughput. Here four adjacent lanes
@@ -139,6 +161,18 @@ B2_D void hash_node4(const uint32_t* const* __restrict__ cols, uint32_t ncols, u
     const uint32_t chunks = (ncols + 7) >> 3;
     const uint32_t total = chunks + (mode == 0 ? 0u : (mode == 1 ? 2u : 1u));
     const unsigned lane = threadIdx.x & 31u;
+    // the next chunk's words are fetched before the current permutation starts: two dependent loads (pointer table, column)
+    // otherwise sit between every two permutations of a long row (a 3164-column row is 396 of them)
+    uint32_t nxt[4] = {0, 0, 0, 0};
+    auto fetch = [&](uint32_t it) {
+        const uint32_t c = (it << 3) + 4 * sub;
+        if (sub < 2) {
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                if (c + k < ncols) nxt[k] = __ldg(cols[c + k] + i);
+        }
+    };
+    if (chunks) fetch(0);
 #pragma unroll 1
     for (uint32_t it = 0; it < total; it++) {
         if (it < chunks) {
@@ -146,8 +180,9 @@ B2_D void hash_node4(const uint32_t* const* __restrict__ cols, uint32_t ncols, u
             if (sub < 2) {
 #pragma unroll
                 for (int k = 0; k < 4; k++)
-                    if (c + k < ncols) s[k] = Fp::raw(__ldg(cols[c + k] + i));
+                    if (c + k < ncols) s[k] = Fp::raw(nxt[k]);
             }
+            if (it + 1 < chunks) fetch(it + 1);
         } else if (it == chunks && mode != 0) {
             const uint64_t np = 2 * n, node = 2 * i + (sub >> 1);
             const uint32_t w0 = 4 * (sub & 1);
@@ -196,11 +231,12 @@ B2_D void compress_node4(const uint32_t* prev, const uint32_t* inj, uint32_t* ou
     }
 }
 
-// Row digests of EVERY height group of a commitment in one launch (groups of at most SUBTREE_MAX_FIRST rows): a sponge over a
+// Row digests of EVERY height group of a commitment in one launch (groups of at most ROWHASH_MAX_ROWS rows): a sponge over a
 // 3164-column row is 396 dependent permutations (~1 ms) whatever the row count, and a segment's tree has a dozen such groups;
 // hashed level by level inside the tree walk their latencies added up (r2h launch list: tree_subtree_kernel 9 ms of a
 // 44 ms proof). Here they overlap, and the tree walk only compresses.
 constexpr int ROWHASH_MAX_GROUPS = 32;
+constexpr uint64_t ROWHASH_MAX_ROWS = 1u << 18;
 constexpr int ROWHASH_THREADS = 256;
 struct RowHashParams {
     const uint32_t* const* cols[ROWHASH_MAX_GROUPS];
@@ -571,16 +607,20 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
     }
     d->layers.clear();
     d->layer_nodes.clear();
-    // ---- row digests of every group of at most SUBTREE_MAX_FIRST rows, one launch (Poseidon2-BabyBear only)
+    // ---- row digests of every group below the two-pipe kernel's threshold, one launch (Poseidon2-BabyBear only)
     std::map<uint64_t, uint32_t*> inj;           // height -> digest planes (the tallest group's go straight into layer 0)
     std::vector<std::pair<uint32_t*, size_t>> inj_bufs;
     uint32_t* small_leaf = nullptr;
+    cudaEvent_t rowhash_done = nullptr;
     if (!e->hash_kind) {
         RowHashParams rp{};
         uint32_t blocks = 0;
         for (auto it = groups.rbegin(); it != groups.rend(); ++it) {   // tallest first
             const uint64_t h = it->first;
-            if (h > SUBTREE_MAX_FIRST || (h == hmax && leaf_layer)) continue;
+            // every group the multi-level kernel meets (<= SUBTREE_MAX_FIRST rows) needs its digests; taller ones up to the
+            // two-pipe kernel's threshold join the launch so that their sponges overlap the others
+            if (h == hmax && leaf_layer) continue;
+            if (h > SUBTREE_MAX_FIRST && (h > ROWHASH_MAX_ROWS || h >= mixed_min_rows())) continue;
             B2_REQUIRE(rp.ngroups < ROWHASH_MAX_GROUPS, B2S_ERR_SHAPE, "mmcs: too many distinct matrix heights");
             uint32_t* out = (uint32_t*)e->dmalloc(h * 32);
             if (h == hmax) small_leaf = out;
@@ -596,14 +636,29 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
         }
         rp.first_block[rp.ngroups] = blocks;
         if (rp.ngroups) {
-            StageScope sc(e, ST_LEAF);
-            rowhash_groups_kernel<<<blocks, ROWHASH_THREADS, 0, e->stream>>>(rp);
+            // On a side stream: the launch is as long as its longest row (milliseconds for thousands of columns) and uses a
+            // few SMs; the tall levels (two-pipe leaf kernel, big compress levels) run next to it on the engine's stream.
+            if (!e->hash_stream) B2_CUDA(cudaStreamCreateWithFlags(&e->hash_stream, cudaStreamNonBlocking));
+            cudaEvent_t fork = e->get_event();
+            B2_CUDA(cudaEventRecord(fork, e->stream));
+            B2_CUDA(cudaStreamWaitEvent(e->hash_stream, fork, 0));
+            e->event_pool.push_back(fork);
+            rowhash_groups_kernel<<<blocks, ROWHASH_THREADS, 0, e->hash_stream>>>(rp);
             B2_CHECK_LAUNCH();
             e->launches[1]++;
+            rowhash_done = e->get_event();
+            B2_CUDA(cudaEventRecord(rowhash_done, e->hash_stream));
         }
     }
+    auto need_rowhash = [&]() {   // first reader of the row digests on the engine's stream
+        if (!rowhash_done) return;
+        B2_CUDA(cudaStreamWaitEvent(e->stream, rowhash_done, 0));
+        e->event_pool.push_back(rowhash_done);
+        rowhash_done = nullptr;
+    };
     // leaves
     if (leaf_layer || small_leaf) {
+        if (small_leaf) need_rowhash();
         d->layers.push_back(leaf_layer ? leaf_layer : small_leaf);
         d->layer_nodes.push_back(hmax);
     } else {
@@ -639,6 +694,7 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
                 e->permutations += m * (tp.inj[l] ? 2 : 1);
             }
             tp.levels = l;
+            need_rowhash();
             tree_subtree_kernel<<<(unsigned)(nh / tp.w0), SUBTREE_THREADS, 0, e->stream>>>(tp);
             B2_CHECK_LAUNCH();
             e->launches[2]++;
@@ -647,7 +703,15 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
         }
         uint32_t* next = (uint32_t*)e->dmalloc(nh * 32);
         auto it = groups.find(nh);
-        if (it != groups.end()) {
+        auto pre = inj.find(nh);
+        if (pre != inj.end()) {
+            need_rowhash();
+            StageScope sc(e, ST_COMPRESS);
+            tree_level_inject_kernel<<<grid_for(nh, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(d->layers.back(), pre->second, next, nh);
+            B2_CHECK_LAUNCH();
+            e->launches[2]++;
+            e->permutations += 2 * nh;
+        } else if (it != groups.end()) {
             StageScope sc(e, ST_LEAF);
             uint32_t nc = (uint32_t)it->second.size();
             launch_level(e, group_dev[nh], nc, nh, d->layers.back(), next, 1);
@@ -665,6 +729,7 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
         d->layer_nodes.push_back(nh);
         h = nh;
     }
+    need_rowhash();   // (nothing read them: a one-row tree) the buffers are freed on the engine's stream
     for (auto& b : inj_bufs) e->dfree(b.first, b.second);
     e->dfree(d_ptrs, total_cols * sizeof(void*));
 }
