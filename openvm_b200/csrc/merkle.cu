@@ -237,6 +237,7 @@ B2_D void compress_node4(const uint32_t* prev, const uint32_t* inj, uint32_t* ou
 // 44 ms proof). Here they overlap, and the tree walk only compresses.
 constexpr int ROWHASH_MAX_GROUPS = 32;
 constexpr uint64_t ROWHASH_MAX_ROWS = 1u << 18;
+constexpr uint64_t ROWHASH_MAX_PERMS = 1u << 20;   // above SUBTREE_MAX_FIRST rows only groups this cheap join the launch
 constexpr int ROWHASH_THREADS = 256;
 struct RowHashParams {
     const uint32_t* const* cols[ROWHASH_MAX_GROUPS];
@@ -620,7 +621,10 @@ void mmcs_build(b2s_engine* e, b2s_pcs_data* d, uint32_t* leaf_layer) {
             // every group the multi-level kernel meets (<= SUBTREE_MAX_FIRST rows) needs its digests; taller ones up to the
             // two-pipe kernel's threshold join the launch so that their sponges overlap the others
             if (h == hmax && leaf_layer) continue;
-            if (h > SUBTREE_MAX_FIRST && (h > ROWHASH_MAX_ROWS || h >= mixed_min_rows())) continue;
+            // ... unless they are real work: the four-lane sponge spends ~1.5x the multiplies of the one-row-per-thread kernel,
+            // so a tall AND wide group (KeccakVmAir shape: 2^18 x 3164, main commit 33.6 -> 48.8 ms) stays on the throughput path
+            const uint64_t perms = h * ((it->second.size() + 7) / 8);
+            if (h > SUBTREE_MAX_FIRST && (h > ROWHASH_MAX_ROWS || h >= mixed_min_rows() || perms > ROWHASH_MAX_PERMS)) continue;
             B2_REQUIRE(rp.ngroups < ROWHASH_MAX_GROUPS, B2S_ERR_SHAPE, "mmcs: too many distinct matrix heights");
             uint32_t* out = (uint32_t*)e->dmalloc(h * 32);
             if (h == hmax) small_leaf = out;
