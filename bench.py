@@ -192,15 +192,20 @@ class Ctx:
         self.rank = int(os.environ.get("RANK", "0"))
         self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
         self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        if os.environ.get("B2S_BENCH_BACKEND") == "none":   # diagnostic: ranks run as unrelated processes
+            self.world = 1
         self.all_cpus = sorted(os.sched_getaffinity(0))
         self.cpus = self.all_cpus
         self.affinity = "unpinned"
+        self.reduce_device = "cuda"
 
     def pin_cpus(self):
         """Each rank gets a DISJOINT share of the CPUs next to its GPU (NUMA-local pinned buffers; 8 ranks x K proving threads
         no longer compete for the same cores)."""
         torch = self.torch
         near = self.all_cpus
+        if os.environ.get("B2S_BENCH_PIN", "1") == "0":
+            return
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -233,7 +238,7 @@ class Ctx:
     def allmax(self, *vals):
         if self.world == 1:
             return vals if len(vals) > 1 else vals[0]
-        t = self.torch.tensor(list(vals), dtype=self.torch.float64, device="cuda")
+        t = self.torch.tensor(list(vals), dtype=self.torch.float64, device=self.reduce_device)
         self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
         out = [float(x) for x in t.tolist()]
         return out if len(out) > 1 else out[0]
@@ -498,24 +503,37 @@ def leg_segment_throughput(cx, sp0, shapes, b, K, steps):
         sp.generate(1000 * k + cx.rank)
         sp.prove()
         workers.append(sp)
-    nper = max(steps, 4)
+    # every engine proves back to back for a fixed wall time (short fixed counts were +-25 % from run to run: the figure
+    # depends on how the engines' host phases interleave, and start-up and tail effects dominated)
+    duration = max(2.0, 0.25 * steps)
+    counts = [0] * len(workers)
+    t_end = [0.0]
 
-    def work(w):
-        for _ in range(nper):
+    def work(k, w):
+        while time.perf_counter() < t_end[0]:
             w.prove()
-        w.tstream.synchronize()
+            w.tstream.synchronize()
+            counts[k] += 1
 
     cx.barrier()
-    ths = [threading.Thread(target=work, args=(w,)) for w in workers]
+    ths = [threading.Thread(target=work, args=(k, w)) for k, w in enumerate(workers)]
     t0 = time.perf_counter()
+    t_end[0] = t0 + duration
     for th in ths:
         th.start()
     for th in ths:
         th.join()
-    twall = cx.allmax(time.perf_counter() - t0)
+    mine = sum(counts) / (time.perf_counter() - t0)
+    total = mine
+    if cx.world > 1:
+        t = cx.torch.tensor([mine], dtype=cx.torch.float64, device=cx.reduce_device)
+        cx.dist.all_reduce(t, op=cx.dist.ReduceOp.SUM)
+        total = float(t.item())
+    slowest = -cx.allmax(-mine)
     for w in workers[1:]:
         w.close()
-    return {"segments_per_s": cx.world * K * nper / twall, "engines_per_gpu": K, "proofs_timed": cx.world * K * nper}
+    return {"segments_per_s": total, "segments_per_s_slowest_gpu": slowest, "engines_per_gpu": K,
+            "proofs_timed": int(round(total * duration)), "timed_s": duration}
 
 
 def leg_dag(cx, S, K, seg_shapes, agg_shapes, orc):
@@ -698,7 +716,11 @@ def main():
     cx.pin_cpus()
     torch.cuda.set_device(cx.local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", cx.local_rank))
+        if os.environ.get("B2S_BENCH_BACKEND", "nccl") == "gloo":   # diagnostic only
+            dist.init_process_group("gloo")
+            cx.reduce_device = "cpu"
+        else:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", cx.local_rank))
     orc = oracle() if (rank == 0 and "cpu" in legs) else None
     log_h, width, b = args.log_height, args.width, args.log_blowup
     t_start = time.perf_counter()
