@@ -835,8 +835,8 @@ def main():
         butterflies = (1 + (1 << b)) * 0.5 * H * log_h * width
         int_pipe = {
             "modmul_per_s_peak": modmul_peak,
-            "modmul_peak_source": "b2s_bench_modmul: 8 independent Montgomery product chains per thread, state in registers, "
-                                  "2048 threads per SM (the one peak every fraction below uses)",
+            "modmul_peak_source": "b2s_bench_modmul: 8 independent signed-Montgomery squaring chains per thread (the cheapest product "
+                                  "form, the S-box's), state in registers, 2048 threads per SM: the one peak every fraction uses",
             "poseidon2_perm_per_s": perms / (hash_ms * 1e-3),
             "poseidon2_perm_per_s_integer_only_microbench": nthreads * 64 / (pms * 1e-3),
             "hash_products_per_s": perms / (hash_ms * 1e-3) * 564,

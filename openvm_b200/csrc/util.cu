@@ -232,14 +232,20 @@ __global__ void modmul_bench_kernel(uint32_t* sink, uint32_t iters, uint32_t see
     Fp a[ILP], b = Fp::raw(seed % P);
 #pragma unroll
     for (int k = 0; k < ILP; k++) a[k] = Fp::raw((threadIdx.x * 2654435761u + k * 40503u + blockIdx.x) % P);
+    // the cheapest product form this part has: signed Montgomery squarings (IMAD.WIDE + IMAD + IMAD.HI + subtract, no
+    // correction into [0, p)), the form of the Poseidon2 S-box chains; 3.66 T/s against 3.1 T/s for the unsigned a * b form
+    // (profiles/r1g_fp64_pipe.md). This is THE modular-product peak every int_pipe fraction in bench.py is quoted against.
+    int32_t x[ILP];
+#pragma unroll
+    for (int k = 0; k < ILP; k++) x[k] = (int32_t)(a[k] * b).v - (int32_t)(P >> 1);
     for (uint32_t i = 0; i < iters; i++) {
 #pragma unroll
-        for (int k = 0; k < ILP; k++) a[k] = a[k] * b;
+        for (int k = 0; k < ILP; k++) x[k] = smont(x[k], x[k]);
     }
     uint32_t acc = 0;
 #pragma unroll
-    for (int k = 0; k < ILP; k++) acc ^= a[k].v;
-    if (acc == 0xFFFFFFFFu) sink[0] = acc;  // never true for reduced values; keeps the loop alive
+    for (int k = 0; k < ILP; k++) acc ^= (uint32_t)x[k];
+    if (acc == 0x7FFFFFFFu) sink[0] = acc;  // |x| < p: never true; keeps the loop alive
 }
 double bench_modmul(b2s_engine* e, uint64_t threads, uint32_t iters, int ilp) {
     uint32_t* sink = (uint32_t*)e->dmalloc(4);
