@@ -28,6 +28,10 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# Several engines per GPU, each with a dozen streams: with the default 8 hardware queues unrelated streams share a queue and
+# wait on each other's latency-bound kernels (34-AIR segment, 8 engines: 59 -> 64 segments/s with 32). Must be set before CUDA
+# initialises; a deployment sets it the same way.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 # the reference's stage gauges (crates/prof/data/metrics.example.json): six disjoint stages, then the whole proof
 GAUGES = ["main_trace_commit_time_ms", "generate_perm_trace_time_ms", "perm_trace_commit_time_ms",
@@ -684,7 +688,7 @@ def main():
     ap.add_argument("--segment-scale-log", type=int, default=0,
                     help="log2 scale of the segment's heights (0 = the reference's example table; 3 = ALU chips of 2^20 rows)")
     ap.add_argument("--leaf-scale-log", type=int, default=0)
-    ap.add_argument("--proof-engines", type=int, default=8,
+    ap.add_argument("--proof-engines", type=int, default=12,
                     help="engines proving concurrently on each GPU for the segments/s figure (one host thread each)")
     ap.add_argument("--dag-segments", type=int, default=16)
     ap.add_argument("--dag-engines", type=int, default=4)
