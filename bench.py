@@ -202,6 +202,7 @@ class Ctx:
         self.cpus = self.all_cpus
         self.affinity = "unpinned"
         self.reduce_device = "cuda"
+        self.sched = "default"
 
     def pin_cpus(self):
         """Each rank gets a DISJOINT share of the CPUs next to its GPU (NUMA-local pinned buffers; 8 ranks x K proving threads
@@ -514,6 +515,8 @@ def leg_segment_throughput(cx, sp0, shapes, b, K, steps):
     t_end = [0.0]
 
     def work(k, w):
+        # a new host thread starts on device 0: without this, every rank's engine threads open a context on GPU 0
+        cx.torch.cuda.set_device(cx.local_rank)
         while time.perf_counter() < t_end[0]:
             w.prove()
             w.tstream.synchronize()
@@ -562,6 +565,7 @@ def leg_dag(cx, S, K, seg_shapes, agg_shapes, orc):
     logs = [[] for _ in range(K)]
 
     def run(k):
+        cx.torch.cuda.set_device(cx.local_rank)   # threads start on device 0 (see leg_segment_throughput)
         seg, agg = workers[k]
 
         def job(jid, children):
@@ -718,6 +722,21 @@ def main():
     real_stdout = os.dup(1)
     os.dup2(2, 1)
     cx.pin_cpus()
+    # K engine threads per GPU spend most of their time waiting for the device. With the default policy they spin, and once the
+    # host has about as many waiting threads as CPUs (4 ranks x 8-12 engines on 32 CPUs) the spinners starve the threads that
+    # have work: one rank fell to 1.6 proofs/s and every host round trip of the others doubled. cudaDeviceScheduleYield lets a
+    # waiting thread give its slice away (1 GPU, 12 engines on 8 CPUs: 67 segments/s against 65 spinning; blocking waits: 58).
+    sched = os.environ.get("B2S_BENCH_SCHED", "yield")
+    try:
+        import ctypes
+        rt = ctypes.CDLL("libcudart.so.12")
+        flag = {"spin": 1, "yield": 2, "block": 4}.get(sched, 0)
+        if flag:
+            rt.cudaSetDevice(cx.local_rank)
+            rc = rt.cudaSetDeviceFlags(flag)
+            cx.sched = f"{sched} (cudaSetDeviceFlags rc {rc})"
+    except OSError:
+        cx.sched = "default (libcudart not found)"
     torch.cuda.set_device(cx.local_rank)
     if world > 1:
         if os.environ.get("B2S_BENCH_BACKEND", "nccl") == "gloo":   # diagnostic only
@@ -781,13 +800,23 @@ def main():
                             f"metrics.example.json group ecrecover_program, heights x 2^{args.segment_scale_log})",
                             orc, modmul_peak, hbm_peak, cpu_scale_log=-4 if "cpu" in legs else None)
         seg["segments_per_s_single_engine"] = seg.pop("proofs_per_s")
-        if args.proof_engines > 1:
-            seg.update(leg_segment_throughput(cx, sp, seg_shapes, 1, args.proof_engines, args.steps))
+        # engines per GPU: as asked, but no more than two host threads per CPU this rank owns (8 ranks on a 32-CPU host)
+        engines = max(1, min(args.proof_engines, 2 * len(cx.cpus)))
+        if engines > 1:
+            seg.update(leg_segment_throughput(cx, sp, seg_shapes, 1, engines, args.steps))
         else:
             seg["segments_per_s"] = seg["segments_per_s_single_engine"]
         seg["cells_per_s"] = (sp.cells + sp.perm_cells) * seg["segments_per_s"]
         sp.close()
         log(f"segment: {seg['device_ms_per_proof']:.1f} ms/proof, {seg['segments_per_s']:.1f} segments/s")
+    seg_r1 = None
+    if "segment" in legs:
+        # the ten-AIR shape round 1 quoted (19.9 ms, 82.8 segments/s), kept so that the two rounds compare on one workload
+        r1_shapes = [(lh, w, pc, 3) for lh, w, pc in A.segment_shapes(0, legacy=True)]
+        seg_r1, sp = leg_shape(cx, "segment_r1_shape", r1_shapes, 1, args.steps,
+                               "round-1 ten-AIR segment shape (openvm_b200/airs.py segment_shapes(legacy=True))", orc)
+        sp.close()
+        log(f"segment (round-1 shape): {seg_r1['device_ms_per_proof']:.1f} ms/proof")
     if "keccak" in legs:
         keccak, sp = leg_shape(cx, "keccak", [(17, 3164, 322, 3)], 1, max(2, args.steps // 2),
                                "KeccakVmAir shape (config 4): 2^17 rows x 3164 main columns, 322 EF after-challenge columns",
@@ -881,11 +910,11 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
             "data": "synthetic",
-            "config": {"workload": workload_name(log_h, width, b), "segments_per_gpu": 1, "cpu_affinity": cx.affinity,
+            "config": {"workload": workload_name(log_h, width, b), "segments_per_gpu": 1, "cpu_affinity": cx.affinity, "host_wait_policy": cx.sched,
                        "l2": "inputs (16 GiB trace, 32 GiB LDE) are far larger than the 126 MB L2; no flush needed",
                        "fri": {"log_blowup": b}, "legs": sorted(legs)},
             "roofline": roofline, "roofline_lde": roofline_lde, "int_pipe": int_pipe, "cpu_baseline": cpu,
-            "root_checked": root_checked, "e2e": e2e, "commit_b2": commit_b2, "segment_proof": seg, "keccak_proof": keccak,
+            "root_checked": root_checked, "e2e": e2e, "commit_b2": commit_b2, "segment_proof": seg, "segment_proof_r1_shape": seg_r1, "keccak_proof": keccak,
             "leaf_proof": leaf, "continuation_dag": dag, "sharded_commit": sharded_leg,
             "gpu_launches": int(launches), "clocks": base["clocks"],
             "stage_ms_per_step": {"main_trace_commit_time_ms": met["commit_total_ms"] / steps,

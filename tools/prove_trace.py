@@ -6,7 +6,7 @@ from openvm_b200 import B2Engine, FriParameters, AirProvingContext, airs as A
 
 eng = B2Engine.new(FriParameters.standard_with_100_bits_conjectured_security(1))
 dev = eng.device()
-shapes = A.segment_shapes(int(sys.argv[1]) if len(sys.argv) > 1 else 0)
+shapes = A.segment_shapes(int(sys.argv[1]) if len(sys.argv) > 1 else 0, legacy=len(sys.argv) > 2 and sys.argv[2] == "legacy")
 air_objs = [A.segment_air(w, perm_cols=pc) for _, w, pc in shapes]
 pk = dev.transport_pk_to_device(A.build_key(air_objs, None, log_up_pow_bits=16))
 ctx = []
