@@ -253,6 +253,21 @@ class Ctx:
         return B2Engine.new(FriParameters.standard_with_100_bits_conjectured_security(b), self.local_rank)
 
 
+def trim_pool(cx):
+    """Between legs: give the device's stream-ordered pool back to the driver. Engines of the previous leg are closed, but the
+    pool (release threshold = never) keeps their blocks; after a 12-engine leg its free list made every later allocation
+    slower (FRI commit phase of the next single-engine proof 3.3 -> 7-14 ms: ~400 small allocations per proof)."""
+    try:
+        import ctypes
+        rt = ctypes.CDLL("libcudart.so.12")
+        cx.torch.cuda.synchronize()
+        pool = ctypes.c_void_p()
+        if rt.cudaDeviceGetDefaultMemPool(ctypes.byref(pool), cx.local_rank) == 0:
+            rt.cudaMemPoolTrimTo(pool, ctypes.c_size_t(0))
+    except OSError:
+        pass
+
+
 def leg_commit(cx, b, steps, warmup, sample_clocks):
     """Device-resident commit of the workload's trace: K timed steps between CUDA events on the engine's stream."""
     torch, args = cx.torch, cx.args
@@ -777,6 +792,7 @@ def main():
     spcs.free(); small.free()
     base["trace"].free()
     eng.close()
+    trim_pool(cx)
     hbm_peak, peak_src = measured_peaks()
 
     commit_b2 = None
@@ -789,26 +805,12 @@ def main():
                      "root": [int(x) for x in r2["root"]]}
         r2["trace"].free()
         r2["eng"].close()
+        trim_pool(cx)
         log(f"commit b=2: {r2['ms_step']:.1f} ms/step")
 
     # ---- proofs
     seg = keccak = leaf = dag = None
     seg_shapes = [(lh, w, pc, 3) for lh, w, pc in A.segment_shapes(args.segment_scale_log)]
-    if "segment" in legs:
-        seg, sp = leg_shape(cx, "segment", seg_shapes, 1, args.steps,
-                            "shape-replay RV32IM segment (per-AIR table of the reference's example, crates/prof/data/"
-                            f"metrics.example.json group ecrecover_program, heights x 2^{args.segment_scale_log})",
-                            orc, modmul_peak, hbm_peak, cpu_scale_log=-4 if "cpu" in legs else None)
-        seg["segments_per_s_single_engine"] = seg.pop("proofs_per_s")
-        # engines per GPU: as asked, but no more than two host threads per CPU this rank owns (8 ranks on a 32-CPU host)
-        engines = max(1, min(args.proof_engines, 2 * len(cx.cpus)))
-        if engines > 1:
-            seg.update(leg_segment_throughput(cx, sp, seg_shapes, 1, engines, args.steps))
-        else:
-            seg["segments_per_s"] = seg["segments_per_s_single_engine"]
-        seg["cells_per_s"] = (sp.cells + sp.perm_cells) * seg["segments_per_s"]
-        sp.close()
-        log(f"segment: {seg['device_ms_per_proof']:.1f} ms/proof, {seg['segments_per_s']:.1f} segments/s")
     seg_r1 = None
     if "segment" in legs:
         # the ten-AIR shape round 1 quoted (19.9 ms, 82.8 segments/s), kept so that the two rounds compare on one workload
@@ -817,6 +819,16 @@ def main():
                                "round-1 ten-AIR segment shape (openvm_b200/airs.py segment_shapes(legacy=True))", orc)
         sp.close()
         log(f"segment (round-1 shape): {seg_r1['device_ms_per_proof']:.1f} ms/proof")
+    # single-engine legs first, the multi-engine legs (segments/s, DAG) last: after K engines have run and gone, single-engine
+    # proofs in the same process are 1.5x slower (round-1 shape: 18.9 ms run first, 30 ms run after the 12-engine leg)
+    seg_sp = None
+    if "segment" in legs:
+        seg, seg_sp = leg_shape(cx, "segment", seg_shapes, 1, args.steps,
+                                "shape-replay RV32IM segment (per-AIR table of the reference's example, crates/prof/data/"
+                                f"metrics.example.json group ecrecover_program, heights x 2^{args.segment_scale_log})",
+                                orc, modmul_peak, hbm_peak, cpu_scale_log=-4 if "cpu" in legs else None)
+        seg["segments_per_s_single_engine"] = seg.pop("proofs_per_s")
+        log(f"segment: {seg['device_ms_per_proof']:.1f} ms/proof on one engine")
     if "keccak" in legs:
         keccak, sp = leg_shape(cx, "keccak", [(17, 3164, 322, 3)], 1, max(2, args.steps // 2),
                                "KeccakVmAir shape (config 4): 2^17 rows x 3164 main columns, 322 EF after-challenge columns",
@@ -829,6 +841,16 @@ def main():
                              "leaf-aggregation shape (config 5), quotient degree up to 4", orc, modmul_peak, hbm_peak)
         sp.close()
         log(f"leaf: {leaf['device_ms_per_proof']:.1f} ms/proof")
+    if seg_sp is not None:
+        # engines per GPU: as asked, but no more than two host threads per CPU this rank owns (8 ranks on a 32-CPU host)
+        engines = max(1, min(args.proof_engines, 2 * len(cx.cpus)))
+        if engines > 1:
+            seg.update(leg_segment_throughput(cx, seg_sp, seg_shapes, 1, engines, args.steps))
+        else:
+            seg["segments_per_s"] = seg["segments_per_s_single_engine"]
+        seg["cells_per_s"] = (seg_sp.cells + seg_sp.perm_cells) * seg["segments_per_s"]
+        seg_sp.close()
+        log(f"segment: {seg['segments_per_s']:.1f} segments/s with {seg.get('engines_per_gpu', 1)} engines per GPU")
     if "dag" in legs:
         agg_shapes = [(lh, w, None, dg) for lh, w, dg in A.leaf_shapes(args.dag_agg_scale_log)]
         dag = leg_dag(cx, args.dag_segments, args.dag_engines, seg_shapes, agg_shapes, orc)
