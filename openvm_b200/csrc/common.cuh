@@ -241,6 +241,9 @@ struct QuotientBatch {
     unsigned next = 0;
     std::vector<Finish> finishes;
 };
+void ensure_aux_streams(b2s_engine* e);
+cudaStream_t aux_fork(b2s_engine* e, unsigned k);   // side stream k, ordered behind the engine's stream as of now
+void aux_join(b2s_engine* e);                       // the engine's stream waits for every side stream
 void quotient_batch_begin(b2s_engine* e, QuotientBatch& qb);
 void quotient_jit_launch(QuotientBatch& qb, const AirKeyDev& a, const uint32_t* const* mats, const uint32_t* publics,
                          const uint32_t* alpha_pows, const uint32_t* ef_consts, uint32_t* acc, uint32_t* out, unsigned n, unsigned lq);

@@ -1019,9 +1019,8 @@ static void scan_planes(b2s_engine* e, Scratch& scratch, const uint32_t* in, uin
 struct ByteWriter {
     std::vector<uint8_t>& buf;
     void u32(uint32_t x) {  // little-endian host (x86-64 / aarch64): the wire format is the in-memory word
-        const size_t at = buf.size();
-        buf.resize(at + 4);
-        memcpy(buf.data() + at, &x, 4);
+        const uint8_t* b = reinterpret_cast<const uint8_t*>(&x);
+        buf.insert(buf.end(), b, b + 4);
     }
     void f(Fp x) { u32(x.to_canonical()); }
     void ef(const Fp4& e) { for (int i = 0; i < 4; i++) f(e.c[i]); }
@@ -1032,9 +1031,8 @@ struct ByteWriter {
         for (int i = 0; i < 8; i++) f(Fp::raw(d[i]));
     }
     void words(const uint32_t* w, size_t n) {  // already canonical
-        const size_t at = buf.size();
-        buf.resize(at + 4 * n);
-        if (n) memcpy(buf.data() + at, w, 4 * n);
+        const uint8_t* b = reinterpret_cast<const uint8_t*>(w);
+        if (n) buf.insert(buf.end(), b, b + 4 * n);
     }
 };
 
@@ -1226,6 +1224,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
         for (size_t i = 0; i < n_airs; i++) if (keys[i]->width_after) after_of.push_back(i);
         after_views.reserve(after_of.size());
         std::vector<uint32_t*> last_rows;
+        unsigned side_next = 0;
         for (size_t i : after_of) {
             const AirKeyDev& k = *keys[i];
             const unsigned n = logn[i];
@@ -1257,14 +1256,28 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             lp.out = scratch.words((size_t)4 * k.width_after * N);
             lp.row_sums = scratch.words((size_t)4 * N);
             lp.n = n;
-            launch_logup(e, k.islots, k.num_chunks, lp);
+            // every AIR's trace kernel and scan on a side stream: they are short, latency-bound and independent
+            // (34 AIRs: 4.4 ms one after the other). The uploads above are on the engine's stream: fork after them.
             uint32_t* phi = lp.out + (size_t)4 * k.num_chunks * N;
-            scan_planes(e, scratch, lp.row_sums, phi, (uint32_t)N);
+            {
+                cudaStream_t main_stream = e->stream;
+                cudaStream_t side = aux_fork(e, side_next++);
+                e->stream = side;
+                try {
+                    launch_logup(e, k.islots, k.num_chunks, lp);
+                    scan_planes(e, scratch, lp.row_sums, phi, (uint32_t)N);
+                } catch (...) {
+                    e->stream = main_stream;
+                    throw;
+                }
+                e->stream = main_stream;
+            }
             last_rows.push_back(phi);
             b2s_matrix v;
             v.eng = e; v.d = lp.out; v.height = N; v.width = (uint64_t)4 * k.width_after; v.owned = false;
             after_views.push_back(v);
         }
+        aux_join(e);
         trace.mark("  logup: traces enqueued", 2);
         // cumulative sums = last row of each phi column
         {
@@ -1570,11 +1583,18 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
                 hb.descs.insert(hb.descs.end(), d, d + RO_DESC_WORDS);
                 hb.nmats++;
             }
+        // uploads first (engine's stream), then one kernel per height, each on a side stream
+        std::map<unsigned, const uint32_t*> desc_dev;
+        for (auto& kv : batches) desc_dev[kv.first] = scratch.upload(std::move(kv.second.descs));
+        unsigned ro_side = 0;
+        cudaStream_t ro_main = e->stream;
         for (auto& kv : batches) {
             const unsigned h = kv.first;
             HeightBatch& hb = kv.second;
             const uint32_t nm = hb.nmats;
-            const uint32_t* d_descs = scratch.upload(std::move(hb.descs));
+            const uint32_t* d_descs = desc_dev[h];
+            struct Restore { b2s_engine* e; cudaStream_t s; ~Restore() { e->stream = s; } } restore{e, ro_main};
+            e->stream = aux_fork(e, ro_side++);
             if (h >= 17) {
                 reduced_open_height_kernel<<<((1u << h) + 127) / 128, 128, 0, e->stream>>>(
                     d_descs, nm, h, d_apow, ro[h], hb.z[0], hb.npoints > 1 ? hb.z[1] : Fp4::zero(), hb.npoints > 1 ? 1u : 0u,
@@ -1589,6 +1609,7 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
             B2_CHECK_LAUNCH();
             e->launches[3]++;
         }
+        aux_join(e);
     }
 
     trace.mark("reduced openings");

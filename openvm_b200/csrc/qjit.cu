@@ -492,10 +492,7 @@ __global__ void quotient_finish_kernel(const uint32_t* __restrict__ acc, uint32_
     }
 }
 
-void quotient_batch_begin(b2s_engine* e, QuotientBatch& qb) {
-    qb.e = e;
-    qb.next = 0;
-    qb.finishes.clear();
+void ensure_aux_streams(b2s_engine* e) {
     if (e->aux_streams.empty()) {
         unsigned ns = 8;
         if (const char* env = getenv("B2S_QUOTIENT_STREAMS")) ns = (unsigned)std::max(1, std::min(32, atoi(env)));
@@ -505,6 +502,32 @@ void quotient_batch_begin(b2s_engine* e, QuotientBatch& qb) {
             e->aux_streams.push_back(st);
         }
     }
+}
+// aux stream k starts behind everything queued on the engine's stream so far
+cudaStream_t aux_fork(b2s_engine* e, unsigned k) {
+    ensure_aux_streams(e);
+    cudaStream_t st = e->aux_streams[k % e->aux_streams.size()];
+    cudaEvent_t ev = e->get_event();
+    B2_CUDA(cudaEventRecord(ev, e->stream));
+    B2_CUDA(cudaStreamWaitEvent(st, ev, 0));
+    e->event_pool.push_back(ev);
+    return st;
+}
+// the engine's stream continues behind everything queued on the aux streams
+void aux_join(b2s_engine* e) {
+    for (auto st : e->aux_streams) {
+        cudaEvent_t ev = e->get_event();
+        B2_CUDA(cudaEventRecord(ev, st));
+        B2_CUDA(cudaStreamWaitEvent(e->stream, ev, 0));
+        e->event_pool.push_back(ev);
+    }
+}
+
+void quotient_batch_begin(b2s_engine* e, QuotientBatch& qb) {
+    qb.e = e;
+    qb.next = 0;
+    qb.finishes.clear();
+    ensure_aux_streams(e);
 }
 
 // Launches the JIT-compiled kernels of `a` on the batch's streams. mats: LDE matrices in the order
@@ -549,12 +572,7 @@ void quotient_jit_launch(QuotientBatch& qb, const AirKeyDev& a, const uint32_t* 
 
 void quotient_batch_end(QuotientBatch& qb) {
     b2s_engine* e = qb.e;
-    for (auto st : e->aux_streams) {
-        cudaEvent_t ev = e->get_event();
-        B2_CUDA(cudaEventRecord(ev, st));
-        B2_CUDA(cudaStreamWaitEvent(e->stream, ev, 0));
-        e->event_pool.push_back(ev);
-    }
+    aux_join(e);
     for (auto& f : qb.finishes) {
         const uint32_t rows = 1u << (f.n + f.lq);
         quotient_finish_kernel<<<(rows + 127) / 128, 128, 0, e->stream>>>(f.acc, f.K, f.sel, f.out, f.n, e->params.log_blowup, f.lq);
