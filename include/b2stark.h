@@ -107,7 +107,10 @@ int32_t b2s_engine_hash(const b2s_engine* e);
 /* message for the last non-zero status returned on this engine (or globally when e == NULL) */
 const char* b2s_last_error(const b2s_engine* e);
 /* the CUDA stream all work of this engine is ordered on (cudaStream_t as void*); set lets a caller that
- * already owns a stream (e.g. the reference's tracegen) share it. */
+ * already owns a stream (e.g. the reference's tracegen) share it. Latency-bound parts of a commit or proof (LDEs of
+ * short matrices, row digests of short height groups, quotient / LogUp / reduced-opening kernels) run on internal
+ * side streams that fork from and join back into this stream with events: for the caller everything is ordered on
+ * this one stream. With several engines per GPU set CUDA_DEVICE_MAX_CONNECTIONS=32 before CUDA initialises. */
 void* b2s_engine_stream(const b2s_engine* e);
 int32_t b2s_engine_set_stream(b2s_engine* e, void* cuda_stream);
 int32_t b2s_engine_synchronize(b2s_engine* e);

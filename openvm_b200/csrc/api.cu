@@ -225,7 +225,7 @@ b2s_pcs_data* commit_matrices(b2s_engine* e, const b2s_matrix* const* mats, cons
     d->eng = e;
     try {
         const uint32_t lb = e->params.log_blowup;
-
+        bool any_side = false;
         for (size_t i = 0; i < n; i++) {
             const b2s_matrix* in = mats[i];
             B2_REQUIRE(in != nullptr, B2S_ERR_BAD_ARG, "null matrix");
@@ -234,10 +234,16 @@ b2s_pcs_data* commit_matrices(b2s_engine* e, const b2s_matrix* const* mats, cons
             b2s_matrix* lde = new_matrix(e, in->height << lb, in->width);
             d->mats.push_back(lde);
             d->owns.push_back(true);
+            // Short matrices are a handful of latency-bound launches each (a segment commits 34 to 68 of them): when there
+            // are several, each goes to a side stream and they overlap; tall ones fill the chip alone and stay in order.
+            const bool side = n > 1 && (in->height << lb) * in->width <= ((uint64_t)1 << 24);
+            struct Restore { b2s_engine* e; cudaStream_t s; ~Restore() { e->stream = s; } } restore{e, e->stream};
+            if (side) { e->stream = aux_fork(e, (unsigned)i); any_side = true; }
             StageScope sc(e, ST_LDE);
             lde_columns(e, in->d, in->height, log2_exact(in->height), in->width, lb, shifts ? shifts[i] : Fp::one(), lde->d,
                         lde->height);
         }
+        if (any_side) aux_join(e);
         mmcs_build(e, d);
     } catch (...) {
         free_pcs(d);

@@ -89,6 +89,8 @@ static TwiddleSet* get_twiddles(b2s_engine* e, unsigned logn) {
     t->logn = logn;
     t->zi = (uint2*)e->dmalloc((size_t)8 << logn);
     fill_table(e, t->zi, logn, Fp::one(), true);
+    // built once per engine: complete before any other stream of the engine (side-stream LDEs of one commit) can find it cached
+    B2_CUDA(cudaStreamSynchronize(e->stream));
     e->twiddles[logn] = t;
     return t;
 }
@@ -117,6 +119,7 @@ static ScaleSet* get_scales(b2s_engine* e, unsigned logn, unsigned log_blowup, F
         base *= wm;
     }
     s->ninv = fp_inv(Fp::from_canonical((uint32_t)(((uint64_t)1 << logn) % P))).v;
+    B2_CUDA(cudaStreamSynchronize(e->stream));   // as for the inverse table
     e->scales[key] = s;
     return s;
 }

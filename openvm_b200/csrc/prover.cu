@@ -1024,7 +1024,19 @@ struct ByteWriter {
     }
     void f(Fp x) { u32(x.to_canonical()); }
     void ef(const Fp4& e) { for (int i = 0; i < 4; i++) f(e.c[i]); }
-    void efs(const std::vector<Fp4>& v) { u32((uint32_t)v.size()); for (auto& e : v) ef(e); }
+    void efs(const std::vector<Fp4>& v) {   // one growth per vector: the opened values are ~10^5 elements of a segment proof
+        const size_t at = buf.size();
+        buf.resize(at + 4 + 16 * v.size());
+        uint32_t tmp = (uint32_t)v.size();
+        memcpy(buf.data() + at, &tmp, 4);
+        size_t pos = at + 4;
+        for (auto& e : v)
+            for (int i = 0; i < 4; i++) {
+                tmp = e.c[i].to_canonical();
+                memcpy(buf.data() + pos, &tmp, 4);
+                pos += 4;
+            }
+    }
     bool raw_digests = false;  // root configuration: a digest is already the canonical limbs of its scalar
     void digest_monty(const uint32_t* d) {
         if (raw_digests) return words(d, 8);
@@ -1546,9 +1558,11 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
         for (auto& r : rounds) for (auto& m : r.mats) max_w = std::max<uint64_t>(max_w, m.lde->width);
         // alpha^t for t up to the widest matrix; the host copy lives in the scratch until the proof is done
         std::vector<uint32_t> apw((max_w + 1) * 4);
+        std::vector<Fp4> ap_host(max_w + 1);
         {
             Fp4 pw = Fp4::one();
             for (uint64_t t = 0; t <= max_w; t++) {
+                ap_host[t] = pw;
                 for (int c = 0; c < 4; c++) apw[4 * t + c] = pw.c[c].v;
                 pw = pw * fri_alpha;
             }
@@ -1572,11 +1586,10 @@ void prove(b2s_engine* e, const b2s_pk* pk, const b2s_air_ctx* airs, size_t n_ai
                 }
                 const uint64_t mp = (uint64_t)(uintptr_t)m.lde->d;
                 uint32_t d[RO_DESC_WORDS] = {(uint32_t)mp, (uint32_t)(mp >> 32), (uint32_t)m.lde->width, (uint32_t)m.points.size()};
-                Fp4 aw = Fp4::one();
-                for (uint64_t t = 0; t < m.lde->width; t++) aw = aw * fri_alpha;
+                const Fp4 aw = ap_host[m.lde->width];
                 for (size_t j = 0; j < m.points.size(); j++) {
-                    Fp4 cz = Fp4::zero(), ap = Fp4::one();
-                    for (auto& v : m.values[j]) { cz += v * ap; ap = ap * fri_alpha; }
+                    Fp4 cz = Fp4::zero();
+                    for (size_t t = 0; t < m.values[j].size(); t++) cz += m.values[j][t] * ap_host[t];
                     for (int c = 0; c < 4; c++) { d[4 + 4 * j + c] = cz.c[c].v; d[12 + 4 * j + c] = alpha_pow[h].c[c].v; }
                     alpha_pow[h] = alpha_pow[h] * aw;
                 }
