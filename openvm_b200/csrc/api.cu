@@ -19,12 +19,24 @@ void set_global_error(const std::string& msg) { g_last_error = msg; }
 void* b2s_engine::dmalloc(size_t bytes) {
     if (bytes == 0) bytes = 4;
     void* p = nullptr;
-    cudaError_t err = cudaMallocAsync(&p, bytes, stream);
-    if (err == cudaErrorMemoryAllocation) {
-        cudaGetLastError();
-        fail(B2S_ERR_OOM, "device allocation of " + std::to_string(bytes) + " bytes failed");
+    auto it = block_cache.find({stream, bytes});
+    if (it != block_cache.end() && !it->second.empty()) {
+        p = it->second.back();
+        it->second.pop_back();
+        cache_bytes -= bytes;
+    } else {
+        cudaError_t err = cudaMallocAsync(&p, bytes, stream);
+        if (err == cudaErrorMemoryAllocation) {   // give the cached blocks back and try once more
+            cudaGetLastError();
+            flush_cache();
+            err = cudaMallocAsync(&p, bytes, stream);
+        }
+        if (err == cudaErrorMemoryAllocation) {
+            cudaGetLastError();
+            fail(B2S_ERR_OOM, "device allocation of " + std::to_string(bytes) + " bytes failed");
+        }
+        B2_CUDA(err);
     }
-    B2_CUDA(err);
     mem_in_use += bytes;
     if (mem_in_use > mem_peak) mem_peak = mem_in_use;
     return p;
@@ -32,8 +44,16 @@ void* b2s_engine::dmalloc(size_t bytes) {
 void b2s_engine::dfree(void* p, size_t bytes) {
     if (!p) return;
     if (bytes == 0) bytes = 4;
-    cudaFreeAsync(p, stream);
     mem_in_use -= bytes;
+    block_cache[{stream, bytes}].push_back(p);
+    cache_bytes += bytes;
+    if (cache_bytes > cache_cap) flush_cache();
+}
+void b2s_engine::flush_cache() {
+    for (auto& kv : block_cache)
+        for (void* q : kv.second) cudaFreeAsync(q, kv.first.first);
+    block_cache.clear();
+    cache_bytes = 0;
 }
 void* b2s_engine::host_pinned(size_t bytes) {
     if (bytes > pinned_bytes) {
@@ -310,6 +330,7 @@ void b2s_engine_free(b2s_engine* e) {
         free_selectors(e);
     } catch (...) {
     }
+    e->flush_cache();
     for (auto ev : e->event_pool) cudaEventDestroy(ev);
     cudaStreamSynchronize(e->stream);
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
@@ -336,6 +357,7 @@ int32_t b2s_engine_set_stream(b2s_engine* e, void* cuda_stream) {
     if (!e) return B2S_ERR_BAD_ARG;
     return guarded(e, [&] {
         B2_CUDA(cudaStreamSynchronize(e->stream));
+        e->flush_cache();   // cached blocks are keyed by the stream they were freed on
         if (e->own_stream) B2_CUDA(cudaStreamDestroy(e->stream));
         e->stream = (cudaStream_t)cuda_stream;
         e->own_stream = false;

@@ -60,6 +60,13 @@ struct b2s_engine {
     bool own_stream = false;
     std::string last_error;
     uint64_t mem_in_use = 0, mem_peak = 0;
+    // Freed device blocks, kept per (stream they were freed on, size) and handed out again for the same stream and size: a
+    // proof makes ~1000 allocations of the same sizes every time, and every cudaMallocAsync / cudaFreeAsync is a driver call
+    // under the context lock that K engines share. Reuse on the same stream keeps the stream-ordered semantics of
+    // cudaFreeAsync (api.cu). Flushed when it exceeds cache_cap, when the stream changes, and with the engine.
+    std::map<std::pair<cudaStream_t, size_t>, std::vector<void*>> block_cache;
+    size_t cache_bytes = 0, cache_cap = (size_t)48 << 30;
+    void flush_cache();
     bool metrics_enabled = true;
     b2::StageTimer timers[b2::ST_COUNT];
     std::vector<cudaEvent_t> event_pool;
