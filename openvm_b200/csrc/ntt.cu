@@ -391,6 +391,104 @@ __global__ void __launch_bounds__(K1_THREADS) ntt_strided_kernel(PassParams p) {
     }
 }
 
+// ---- strided pass, asynchronous variant (experiment, B2S_NTT_ASYNC=1) ---------------------------------------------------
+// Persistent blocks, two tile buffers: the 16-byte pieces of the block's NEXT tile travel global -> shared with cp.async
+// (LDGSTS: no registers, no LDG/STS pair) while the butterflies of the current tile run; its twiddle pair sits in two
+// registers per thread meanwhile. This is the cp.async form of the TMA / mbarrier double buffer (a 2-D TMA box of 32 words x
+// 2^D rows would move the same bytes): what it can gain is load latency hidden inside one block, what it costs is shared
+// memory (2 tiles -> 3 blocks per SM instead of 5-6). Measured in profiles/r3b_ntt_async.md.
+B2_D void cp_async16(uint32_t* smem_dst, const uint32_t* gsrc) {
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gsrc));
+}
+B2_D void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+B2_D void cp_async_wait_all_but_one() { asm volatile("cp.async.wait_group 1;\n" ::: "memory"); }
+
+template <int D>
+__global__ void __launch_bounds__(K1_THREADS) ntt_strided_async_kernel(PassParams p, uint32_t log_tiles_x, uint32_t total_tiles) {
+    extern __shared__ uint32_t smem[];
+    constexpr uint32_t TILE = 32u << D, TWW = 2u << D, COUNT = 1u << D;
+    constexpr uint32_t TOTAL = 8u << D;                                  // 16-byte pieces per tile
+    constexpr int NB = TOTAL / K1_THREADS ? TOTAL / K1_THREADS : 1;
+    constexpr int NT = (COUNT + K1_THREADS - 1) / K1_THREADS;            // twiddle pairs per thread
+    const uint32_t n = p.log_len;
+    const uint32_t low_bits = n - p.t0 - D;
+    const uint32_t tid = threadIdx.x;
+    struct Tile {
+        uint32_t chunk, top;
+        const uint32_t* in;
+        uint32_t* out;
+        const uint2* z;
+    };
+    auto decode = [&](uint32_t T) {
+        Tile tl;
+        const uint32_t xi = T & ((1u << log_tiles_x) - 1), rest = T >> log_tiles_x;
+        const uint32_t col = rest % p.width, cz = rest / p.width;
+        tl.chunk = xi & ((1u << (low_bits - 5)) - 1);
+        tl.top = xi >> (low_bits - 5);
+        const uint64_t blk_off = p.coset && p.log_blowup ? ((uint64_t)(__brev(cz) >> (32 - p.log_blowup)) << n) : 0;
+        tl.z = p.z + ((size_t)cz << n);
+        tl.in = p.in + (uint64_t)col * p.in_col_stride + (p.in_block ? blk_off : 0);
+        tl.out = p.out + (uint64_t)col * p.out_col_stride + blk_off;
+        return tl;
+    };
+    uint2 twr[NT];
+    auto issue = [&](const Tile& tl, uint32_t* xb) {
+        const uint64_t base = ((uint64_t)tl.top << (n - p.t0)) + ((uint64_t)tl.chunk << 5);
+#pragma unroll
+        for (int k = 0; k < NB; k++) {
+            const uint32_t e = k * K1_THREADS + tid;
+            const uint32_t q = (e & 7) << 2, r = e >> 3;
+            if (e < TOTAL) cp_async16(xb + r * 32 + q, tl.in + base + ((uint64_t)r << low_bits) + q);
+        }
+        const uint32_t root = (1u << p.t0) + tl.top;
+#pragma unroll
+        for (int k = 0; k < NT; k++) {
+            const uint32_t i = k * K1_THREADS + tid;
+            twr[k] = make_uint2(0, 0);
+            if (i && i < COUNT) {
+                const uint32_t lv = 31 - __clz(i);
+                twr[k] = __ldg(tl.z + ((size_t)root << lv) + (i - (1u << lv)));
+            }
+        }
+    };
+    uint32_t T = blockIdx.x, buf = 0;
+    Tile cur{};
+    if (T < total_tiles) {
+        cur = decode(T);
+        issue(cur, smem);
+    }
+    cp_async_commit();
+    while (T < total_tiles) {
+        uint32_t* xb = smem + buf * (TILE + TWW);
+        uint32_t* tw = xb + TILE;
+#pragma unroll
+        for (int k = 0; k < NT; k++) {
+            const uint32_t i = k * K1_THREADS + tid;
+            if (i < COUNT) { tw[i] = twr[k].x; tw[COUNT + i] = twr[k].y; }
+        }
+        const uint32_t Tn = T + gridDim.x;
+        Tile nxt{};
+        if (Tn < total_tiles) {
+            nxt = decode(Tn);
+            issue(nxt, smem + (buf ^ 1) * (TILE + TWW));
+        }
+        cp_async_commit();            // possibly empty: the wait below then still covers the current tile's group
+        cp_async_wait_all_but_one();
+        __syncthreads();
+        K1Rounds<D, 0, false>::run(xb, tw, 1u);
+        const uint64_t base = ((uint64_t)cur.top << (n - p.t0)) + ((uint64_t)cur.chunk << 5);
+        for (uint32_t e = tid; e < TOTAL; e += K1_THREADS) {
+            const uint32_t q = (e & 7) << 2, r = e >> 3;
+            *reinterpret_cast<uint4*>(cur.out + base + ((uint64_t)r << low_bits) + q) = *reinterpret_cast<const uint4*>(xb + r * 32 + q);
+        }
+        __syncthreads();
+        T = Tn;
+        cur = nxt;
+        buf ^= 1;
+    }
+}
+
 // ---- contiguous pass ------------------------------------------------------------------------------------------
 template <int D>
 struct K2Cfg {
@@ -558,8 +656,35 @@ __global__ void replicate_kernel(const uint32_t* in, uint64_t in_col_stride, uin
 }
 
 // ---- host side --------------------------------------------------------------------------------------------------
+static bool ntt_async_enabled() {
+    static const bool v = [] { const char* s = getenv("B2S_NTT_ASYNC"); return s && s[0] == '1'; }();
+    return v;
+}
+template <int D>
+static void launch_strided_async_t(b2s_engine* e, const PassParams& p, dim3 grid) {
+    constexpr size_t smem = 2 * ((size_t)(32u << D) + (2u << D)) * 4;
+    static std::once_flag configured[64];
+    static unsigned resident[64];
+    cudaError_t err = cudaSuccess;
+    std::call_once(configured[e->device & 63], [&] {
+        err = cudaFuncSetAttribute(ntt_strided_async_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        int per_sm = 0;
+        if (err == cudaSuccess) err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ntt_strided_async_kernel<D>, K1_THREADS, smem);
+        resident[e->device & 63] = (unsigned)(e->num_sms * (per_sm < 1 ? 1 : per_sm));
+    });
+    B2_CUDA(err);
+    const uint64_t total = (uint64_t)grid.x * grid.y * grid.z;
+    B2_REQUIRE(total <= 0xFFFFFFFFull && (grid.x & (grid.x - 1)) == 0, B2S_ERR_SHAPE, "ntt: too many tiles in one launch");
+    const unsigned blocks = (unsigned)std::min<uint64_t>(total, resident[e->device & 63]);
+    ntt_strided_async_kernel<D><<<blocks, K1_THREADS, smem, e->stream>>>(p, log2_exact(grid.x), (uint32_t)total);
+    B2_CHECK_LAUNCH();
+    e->launches[0]++;
+}
 template <int D, bool GATHER>
 static void launch_strided_t(b2s_engine* e, const PassParams& p, dim3 grid) {
+    if constexpr (!GATHER && D >= 5 && D <= 8) {
+        if (ntt_async_enabled()) return launch_strided_async_t<D>(e, p, grid);
+    }
     constexpr size_t smem = ((size_t)1 << D) * ((GATHER ? 33 : 32) + 2) * 4;   // tile + its twiddles (w and w')
     if (smem > 48 * 1024) {
         // once per device and instantiation; engines on several host threads share the flags

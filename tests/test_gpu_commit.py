@@ -209,3 +209,21 @@ def test_streamed_host_commit_at_shipped_threshold(engine, orc):
         del os.environ["B2S_COMMIT_HOST_GROUP_COLS"]
     assert np.array_equal(root, orc.commit([m], 1))
     pcs.free()
+
+
+def test_async_ntt_variant_gives_the_oracle_roots(orc):
+    """B2S_NTT_ASYNC=1 routes the strided NTT passes through the cp.async double-buffered persistent kernel (an experiment
+    kept in the tree with its measurement, profiles/r3b_ntt_async.md): same roots as the oracle on heights whose plans have
+    strided passes of 5 to 8 bits (2^14 ... 2^21 rows)."""
+    import os, subprocess, sys
+    shapes = [[(1 << 14, 5)], [(1 << 16, 9), (1 << 15, 3)], [(1 << 18, 4)], [(1 << 21, 2)]]
+    root_dir = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, B2S_NTT_ASYNC="1")
+    r = subprocess.run([sys.executable, "-c", _LEAF_PATH_SCRIPT.format(root=root_dir, shapes=shapes)], env=env,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    got = [[int(x) for x in part.split()] for part in r.stdout.strip().splitlines()[-1].split("|")]
+    rng2 = np.random.default_rng(77)
+    for group, g in zip(shapes, got):
+        ms = [rng2.integers(0, P, size=(h, w), dtype=np.uint64).astype(np.uint32) for h, w in group]
+        assert g == [int(x) for x in orc.commit(ms, 1)], group
