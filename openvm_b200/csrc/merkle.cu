@@ -10,7 +10,10 @@
 //                     (coalesced: adjacent threads read adjacent rows of the same column), optionally fused with
 //                     the compress-and-inject step of the level the group joins the tree at; or a plain 2-to-1
 //                     compression of the previous digest layer
-//   tree_level_coop_kernel / tree_subtree_kernel  small levels, four lanes per permutation; up to nine levels per launch
+//   rowhash_groups_kernel row digests of EVERY short height group of a commitment in one launch on a side stream, four lanes
+//                     per permutation (a sponge over thousands of columns is a latency chain whatever the row count)
+//   tree_subtree_kernel / tree_level_inject_kernel  the tree walk over precomputed row digests: compressions only; up to nine
+//                     levels per launch below 2^14 nodes
 // Digest layers are stored as 8 word-planes (word w of node i at [w*n + i]) so both kernels read and
 // write fully coalesced.
 #include "common.cuh"
@@ -256,19 +259,6 @@ __global__ void __launch_bounds__(ROWHASH_THREADS) rowhash_groups_kernel(RowHash
     // whole warps past the end leave together; inside a warp idle quads keep the shuffles converged
     if ((t & ~31ull) >> 2 >= n) return;
     hash_node4(p.cols[g], p.ncols[g], n, nullptr, p.out[g], 0, i < n ? i : n - 1, (uint32_t)(t & 3), i < n);
-}
-
-// one level of at most COOP_MAX_NODES nodes, four lanes per node (same modes as tree_level_kernel). Above ~2^13 nodes
-// the machine is full and the one-node-per-thread kernel wins (the four-lane form spends ~1.5 x the multiplies: every
-// lane runs the partial-round S-box and the diagonal is a generic product).
-constexpr uint64_t COOP_MAX_NODES = 1u << 13;
-constexpr int COOP_THREADS = 256;
-__global__ void __launch_bounds__(COOP_THREADS)
-    tree_level_coop_kernel(const uint32_t* const* __restrict__ cols, uint32_t ncols, uint64_t n,
-                           const uint32_t* __restrict__ prev, uint32_t* __restrict__ out, int mode) {
-    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const uint64_t i = t >> 2;
-    hash_node4(cols, ncols, n, prev, out, mode, i < n ? i : n - 1, (uint32_t)(t & 3), i < n);
 }
 
 // Several consecutive levels in one launch: block b owns the sub-tree over nodes [b*W, (b+1)*W) of the first level
@@ -563,15 +553,13 @@ void leaf_absorb(b2s_engine* e, const uint32_t* base, uint32_t ncols, uint64_t n
     e->permutations += n * ((ncols + 7) / 8);
 }
 
-// one tree level: throughput kernel (one node per thread) for big levels, latency kernel (four lanes per node) below
+// one tree level above the multi-level kernel's range: the two-pipe persistent kernel from 2^19 nodes, else one node per thread
 static void launch_level(b2s_engine* e, const uint32_t* const* cols, uint32_t ncols, uint64_t n, const uint32_t* prev,
                          uint32_t* out, int mode) {
     if (e->hash_kind)
         bn_launch_level(e, cols, ncols, n, prev, out, mode);
     else if (n >= mixed_min_rows() && mixed_int_warps() >= 0)
         launch_mixed(e, ColTable{cols}, ncols, n, nullptr, nullptr, out, mode == 0 ? nullptr : prev);
-    else if (n <= COOP_MAX_NODES)
-        tree_level_coop_kernel<<<grid_for(4 * n, COOP_THREADS), COOP_THREADS, 0, e->stream>>>(cols, ncols, n, prev, out, mode);
     else
         tree_level_kernel<<<grid_for(n, HASH_THREADS), HASH_THREADS, 0, e->stream>>>(cols, ncols, n, prev, out, mode);
 }

@@ -14,7 +14,7 @@
 //   quotient_kernel       interprets the AIR's register-allocated constraint program on every row of the quotient
 //                         domain (= the first N*qd rows of the bit-reversed LDE), folds with alpha, divides by Z_H
 //   bary_weights_kernel   x_i / (z - x_i) for the N points of LDE block 0, once per (height, point)
-//   bary_dot_kernel       per column sum_i p(x_i) * weight_i  -> p(z)          (block per column x split)
+//   bary_dot_multi_kernel per column sum_i p(x_i) * weight_i  -> p(z); all columns of one (height, point) per launch
 //   reduced_open_height_kernel   ro_h[row] = sum over the matrices of height h of alpha^o * (sum_t alpha^t p_t(z) - sum_t alpha^t p_t(x)) / (z - x)
 //   fri_pack / fri_fold   commit-phase leaves (2 EF = 8 words per row) and the arity-2 fold with beta^2 roll-in
 //   pow_grind_kernel      parallel search for the minimum proof-of-work witness
@@ -690,50 +690,6 @@ __global__ void bary_weights_kernel(uint32_t* __restrict__ wts, uint32_t n, Fp4 
 }
 
 constexpr int DOT_THREADS = 256;
-// grid (column, split): partial[(col * splits + split) * 4 + c] = sum over the split's rows of col[i] * wts[c][i]
-__global__ void __launch_bounds__(DOT_THREADS) bary_dot_kernel(const uint32_t* __restrict__ mat, uint64_t col_stride,
-                                                               const uint32_t* __restrict__ wts, uint32_t n,
-                                                               uint32_t* __restrict__ partial) {
-    __shared__ uint32_t sm[4][DOT_THREADS];
-    const uint32_t N = 1u << n;
-    const uint32_t col = blockIdx.x, split = blockIdx.y, splits = gridDim.y;
-    const uint32_t per = (N + splits - 1) / splits;
-    const uint32_t lo = split * per, hi = min(N, lo + per);
-    const uint32_t* __restrict__ colp = mat + (uint64_t)col * col_stride;
-    Fp acc[4];
-    for (uint32_t i = lo + threadIdx.x; i < hi; i += DOT_THREADS) {
-        const Fp v = Fp::raw(colp[i]);
-#pragma unroll
-        for (int c = 0; c < 4; c++) acc[c] += v * Fp::raw(wts[(uint64_t)c * N + i]);
-    }
-#pragma unroll
-    for (int c = 0; c < 4; c++) sm[c][threadIdx.x] = acc[c].v;
-    __syncthreads();
-    for (int s = DOT_THREADS / 2; s > 0; s >>= 1) {
-        if (threadIdx.x < s) {
-#pragma unroll
-            for (int c = 0; c < 4; c++) sm[c][threadIdx.x] = (Fp::raw(sm[c][threadIdx.x]) + Fp::raw(sm[c][threadIdx.x + s])).v;
-        }
-        __syncthreads();
-    }
-    if (threadIdx.x < 4) partial[((uint64_t)col * splits + split) * 4 + threadIdx.x] = sm[threadIdx.x][0];
-}
-
-// p(z) for every column of one (matrix, point): sums the splits' partial dot products and applies the barycentric factor
-// ((z/g)^N - 1) / N, so that the host receives finished values (it only hashes them into the transcript)
-__global__ void bary_finish_kernel(const uint32_t* __restrict__ partial, uint32_t width, uint32_t splits, Fp4 scale,
-                                   uint32_t* __restrict__ vals) {
-    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= width) return;
-    Fp4 s = Fp4::zero();
-    for (uint32_t sp = 0; sp < splits; sp++) {
-        const uint4 q = *reinterpret_cast<const uint4*>(partial + ((uint64_t)c * splits + sp) * 4);
-        s.c[0] += Fp::raw(q.x); s.c[1] += Fp::raw(q.y); s.c[2] += Fp::raw(q.z); s.c[3] += Fp::raw(q.w);
-    }
-    s = s * scale;
-    *reinterpret_cast<uint4*>(vals + (uint64_t)c * 4) = make_uint4(s.c[0].v, s.c[1].v, s.c[2].v, s.c[3].v);
-}
-
 // All columns of all matrices of one trace height at one point in one launch (a segment opens ~200 (matrix, point) pairs;
 // one launch pair and one read-back each was 400 launches and 200 host waits): column blockIdx.x of the group is described by
 // BaryCol {column base (block 0 of its LDE), where its partial sums go}.
