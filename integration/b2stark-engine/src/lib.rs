@@ -71,6 +71,24 @@ impl Engine {
         self.check(unsafe { ffi::b2s_get_metrics(self.raw(), &mut m) })?;
         Ok(m)
     }
+    /// The reference's stage gauges (crates/prof/data/metrics.example.json, emitted around crates/vm/src/arch/vm.rs:1328-1399)
+    /// as (name, milliseconds) pairs: the first six are disjoint intervals of the proofs since the last reset, the seventh is
+    /// their total. A shim forwards each pair to `metrics::gauge!(name).set(ms)` where the reference emits it.
+    pub fn stage_gauges(&self) -> Result<[(&'static str, f64); 7]> {
+        let m = self.metrics()?;
+        Ok([
+            ("main_trace_commit_time_ms", m.main_trace_commit_time_ms),
+            ("generate_perm_trace_time_ms", m.generate_perm_trace_time_ms),
+            ("perm_trace_commit_time_ms", m.perm_trace_commit_time_ms),
+            ("quotient_poly_compute_time_ms", m.quotient_poly_compute_time_ms),
+            ("quotient_poly_commit_time_ms", m.quotient_poly_commit_time_ms),
+            ("pcs_opening_time_ms", m.pcs_opening_time_ms),
+            ("stark_prove_excluding_trace_time_ms", m.stark_prove_excluding_trace_time_ms),
+        ])
+    }
+    pub fn reset_metrics(&self) -> Result<()> {
+        self.check(unsafe { ffi::b2s_reset_metrics(self.raw()) })
+    }
 
     /// transport_matrix_to_device: `words` is a RowMajorMatrix<BabyBear> viewed as u32 (Plonky3's BabyBear is a
     /// repr(transparent) Montgomery word: pass `monty = true`) or canonical values.
@@ -132,6 +150,17 @@ impl Engine {
 }
 
 /// proof.write() of the next aggregation layer's verifier program (recursion/src/hints.rs:272-316): vectors of words.
+/// Merkle root of one already-extended device matrix with NO allocation (digest layers in a static device array): for callers
+/// under CUDA graph capture or in loops that must not call cudaMalloc. At most `B2S_STATIC_MAX_ROWS` rows; calls that overlap
+/// on the GPU race on the shared scratch. `d_root8` is device memory for 8 canonical words. No counterpart in the reference.
+pub unsafe fn merkle_root_static(d_matrix: *const u32, height: u64, width: u64, d_root8: *mut u32,
+                                 cuda_stream: *mut std::os::raw::c_void) -> std::result::Result<(), i32> {
+    match ffi::b2s_merkle_root_static(d_matrix, height, width, d_root8, cuda_stream) {
+        0 => Ok(()),
+        st => Err(st),
+    }
+}
+
 pub fn proof_hint_stream(proof: &[u8]) -> Result<Vec<Vec<u32>>> {
     let (mut words, mut n) = (ptr::null_mut(), 0usize);
     let st = unsafe { ffi::b2s_proof_hint_stream(ptr::null_mut(), proof.as_ptr(), proof.len(), &mut words, &mut n) };
