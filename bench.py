@@ -567,7 +567,14 @@ def leg_dag(cx, S, K, seg_shapes, agg_shapes, orc):
     from openvm_b200 import scheduler
     dist = cx.dist
     kinds, deps = scheduler.aggregation_dag(S)
-    store = dist.distributed_c10d._get_default_store() if cx.world > 1 else dist.HashStore()
+    if cx.world > 1:
+        try:
+            store = dist.distributed_c10d._get_default_store()
+        except Exception:   # private accessor gone: a store of our own next to the rendezvous port
+            store = dist.TCPStore(os.environ.get("MASTER_ADDR", "127.0.0.1"), int(os.environ.get("MASTER_PORT", "29500")) + 17,
+                                  cx.world, cx.rank == 0)
+    else:
+        store = dist.HashStore()
     fifo = scheduler.DagFifo(store, deps, tag=f"dag{S}")
     workers = []
     for k in range(K):

@@ -266,6 +266,9 @@ b2s_pcs_data* commit_matrices(b2s_engine* e, const b2s_matrix* const* mats, cons
         if (any_side) aux_join(e);
         mmcs_build(e, d);
     } catch (...) {
+        // nothing on a side stream may still be writing into the matrices that are about to be released
+        for (auto st : e->aux_streams) cudaStreamSynchronize(st);
+        if (e->hash_stream) cudaStreamSynchronize(e->hash_stream);
         free_pcs(d);
         throw;
     }

@@ -168,3 +168,31 @@ def test_dag_fifo_shared_by_two_ranks_over_gloo():
         for k in d:
             assert done_at[k][1] <= done_at[j][0] + 1e-3, (j, k)
     assert set(ran_on.values()) == {0, 1}
+
+
+def test_dag_fifo_in_one_process_with_a_hash_store():
+    """world size 1 (bench.py at N = 1): the same FIFO over a torch HashStore, four engine threads"""
+    import threading
+    import time
+    kinds, deps = scheduler.aggregation_dag(5)
+    fifo = scheduler.DagFifo(dist.HashStore(), deps, tag="solo")
+    logs, lock = [], threading.Lock()
+
+    def fn(jid, args):
+        assert [int(a) for a in args] == deps[jid]
+        time.sleep(0.001)
+        return str(jid).encode()
+
+    def run():
+        out = fifo.work(fn, clock=time.time)
+        with lock:
+            logs.extend(out)
+
+    ths = [threading.Thread(target=run) for _ in range(4)]
+    for t in ths: t.start()
+    for t in ths: t.join()
+    assert sorted(j for j, *_ in logs) == list(range(len(deps)))
+    done = {j: t2 for j, _, _, t2 in logs}
+    ready = {j: t1 for j, _, t1, _ in logs}
+    assert all(done[k] <= ready[j] + 1e-3 for j, d in enumerate(deps) for k in d)
+    assert fifo.result(len(deps) - 1) == str(len(deps) - 1).encode()
