@@ -892,6 +892,10 @@ def main():
             "achieved": lde_bytes / (lde_ms_step * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
             "frac": lde_bytes / (lde_ms_step * 1e-3) / 1e9 / hbm_peak, "ms_per_step": lde_ms_step,
             "launches_per_step": met["lde_launches"] / steps, "share_of_step": lde_ms_step / ms_step,
+            # dram__bytes_read.sum + dram__bytes_write.sum of the six passes of one 32-column group (38.8 GB) x 8 groups, from the
+            # ncu --set full capture profiles/r2g_lde_shoup.md: three HBM round trips per transform for 51.5 GB algorithmic
+            "traffic": 310.4e9 if (log_h, width, b) == (24, 256, 1) else None,
+            "traffic_source": "one ncu --set full capture of these kernels at this shape (profiles/r2g_lde_shoup.md), not re-measured per run",
         }
         hash_ms = (met["leaf_hash_ms"] + met["compress_ms"]) / steps
         butterflies = (1 + (1 << b)) * 0.5 * H * log_h * width
