@@ -24,6 +24,7 @@
 #include "poseidon2.cuh"
 
 #include <algorithm>
+#include <exception>
 #include <array>
 #include <chrono>
 #include <deque>
@@ -921,7 +922,8 @@ __global__ void __launch_bounds__(128) pow_grind_kernel(PowParams p, uint32_t co
 // ---- host-side helpers ----------------------------------------------------------------------------------------------------
 struct Scratch {  // device buffers released when the proof is done (or abandoned)
     b2s_engine* e;
-    std::vector<std::pair<void*, size_t>> bufs;
+    struct Buf { void* p; size_t bytes; cudaStream_t stream; };
+    std::vector<Buf> bufs;   // with the stream each was allocated on: it goes back to that stream's cache (side-stream scans)
     std::vector<b2s_pcs_data*> pcs;
     std::deque<std::vector<uint32_t>> host_words;        // sources of asynchronous uploads, alive until the proof is done
     std::deque<std::vector<const uint32_t*>> host_ptrs;
@@ -943,17 +945,29 @@ struct Scratch {  // device buffers released when the proof is done (or abandone
     }
     uint32_t* words(size_t n) {
         void* p = e->dmalloc(n * 4);
-        bufs.push_back({p, n * 4});
+        bufs.push_back({p, n * 4, e->stream});
         return (uint32_t*)p;
     }
     void* bytes(size_t n) {
         void* p = e->dmalloc(n);
-        bufs.push_back({p, n});
+        bufs.push_back({p, n, e->stream});
         return p;
     }
     ~Scratch() {
+        if (std::uncaught_exceptions() > 0) {   // a failed proof: nothing may still be running on any stream of the engine
+            for (auto st : e->aux_streams) cudaStreamSynchronize(st);
+            if (e->hash_stream) cudaStreamSynchronize(e->hash_stream);
+            cudaStreamSynchronize(e->stream);
+        }
         for (auto* d : pcs) free_pcs(d);
-        for (auto& b : bufs) e->dfree(b.first, b.second);
+        // by now every side stream has joined the engine's stream and the proof has synchronised (or failed and synchronised
+        // below): a buffer returns to the cache of the stream that allocated it, where the next proof asks for it again
+        cudaStream_t main_stream = e->stream;
+        for (auto& b : bufs) {
+            e->stream = b.stream;
+            e->dfree(b.p, b.bytes);
+        }
+        e->stream = main_stream;
     }
 };
 
