@@ -396,7 +396,7 @@ __global__ void __launch_bounds__(K1_THREADS) ntt_strided_kernel(PassParams p) {
 // (LDGSTS: no registers, no LDG/STS pair) while the butterflies of the current tile run; its twiddle pair sits in two
 // registers per thread meanwhile. This is the cp.async form of the TMA / mbarrier double buffer (a 2-D TMA box of 32 words x
 // 2^D rows would move the same bytes): what it can gain is load latency hidden inside one block, what it costs is shared
-// memory (2 tiles -> 3 blocks per SM instead of 5-6). Measured in profiles/r3b_ntt_async.md.
+// memory (2 tiles -> 3 blocks per SM instead of 5-6). Measured in profiles/r2zb_ntt_async.md.
 B2_D void cp_async16(uint32_t* smem_dst, const uint32_t* gsrc) {
     const unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gsrc));

@@ -213,7 +213,7 @@ def test_streamed_host_commit_at_shipped_threshold(engine, orc):
 
 def test_async_ntt_variant_gives_the_oracle_roots(orc):
     """B2S_NTT_ASYNC=1 routes the strided NTT passes through the cp.async double-buffered persistent kernel (an experiment
-    kept in the tree with its measurement, profiles/r3b_ntt_async.md): same roots as the oracle on heights whose plans have
+    kept in the tree with its measurement, profiles/r2zb_ntt_async.md): same roots as the oracle on heights whose plans have
     strided passes of 5 to 8 bits (2^14 ... 2^21 rows)."""
     import os, subprocess, sys
     shapes = [[(1 << 14, 5)], [(1 << 16, 9), (1 << 15, 3)], [(1 << 18, 4)], [(1 << 21, 2)]]
